@@ -1,0 +1,211 @@
+/*
+ * maniac_gpu.h -- C ABI of libmaniacgpu.so, the B200 (sm_100a) replacement for MANIAC's
+ * per-move energy-difference path (reference: maniac-mc/maniac-mc @ 961f5c9).
+ *
+ * The reference has no FFI boundary; the path sits behind Fortran module procedures working
+ * on module globals.  This header defines the boundary at the edge between the Monte Carlo
+ * move code (translation.f90, rotation.f90, create_molecule.f90, delete_molecule.f90,
+ * monte_carlo_utils.f90) and the energy routines (energy_utils.f90, ewald_phase.f90,
+ * ewald_energy.f90, ewald_kvectors.f90, tabulated_utils.f90).  Every entry point names the
+ * reference routine(s) it replaces.  The Fortran side binds these through ISO_C_BINDING
+ * (fortran/maniac_gpu_iface.f90).
+ *
+ * Conventions
+ *  - plain C types only; the caller owns its buffers, the library copies at the call.
+ *  - residue (molecule type) and molecule indices are 0-based here; the Fortran wrapper
+ *    subtracts 1.
+ *  - every function returns 0 on success, non-zero on error; mmc_last_error() gives the text
+ *    (the Fortran wrapper maps it to AbortRun, output_utils.f90:535).
+ *  - energies are in Kelvin exactly as in the reference (energy_utils.f90:440, ewald_energy.f90:272).
+ *  - an energy vector is double[6] = {non_coulomb, coulomb, recip_coulomb, ewald_self,
+ *    intra_coulomb, total}  (type energy_state, simulation_state.f90:74-82).
+ *  - one handle may hold many independent chains (pressure points x replicas) that share the
+ *    framework, the LJ table and the k-vector set; chain 0 is "the" system in strict mode.
+ *  - calls on one handle must be serialised by the caller (the reference is single threaded).
+ *  - there is NO CPU fallback: without a CUDA device mmc_init fails.
+ */
+#ifndef MANIAC_GPU_H
+#define MANIAC_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MMC_MAX_MOL_ATOMS 16 /* max atoms of a movable (active) molecule */
+#define MMC_NE 6             /* components of an energy vector */
+
+/* move types, parameters.f90:35-38 */
+enum { MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4 };
+
+/* quirk switches: defaults reproduce the reference */
+enum { MMC_INIT_SK_ZERO = 0, MMC_INIT_SK_FULL = 1 };           /* Q1 */
+enum { MMC_DELETION_REFERENCE = 0, MMC_DELETION_PHYSICAL = 1 }; /* Q2 */
+
+enum { MMC_E_NONCOUL = 0, MMC_E_COUL = 1, MMC_E_RECIP = 2, MMC_E_SELF = 3, MMC_E_INTRA = 4, MMC_E_TOTAL = 5 };
+
+/* System description handed over once after PrecomputeTable (main.f90:26).
+ * Packed layouts (the Fortran shim packs them from the strided simulation_state arrays):
+ *   charges[r*max_atoms + a], types[r*max_atoms + a]   <- primary%atom_charges/atom_types(r,a)
+ *   sigma/epsilon[(ti-1)*ntypes + (tj-1)]              <- coeff%sigma/epsilon compacted by atom type
+ *   com[3*M], offsets[3*A]: molecules in (residue, molecule) order, atoms in (residue, molecule,
+ *   atom) order                                        <- primary%mol_com / primary%site_offset
+ */
+typedef struct mmc_desc {
+    int nres;              /* nb%type_residue */
+    int max_atoms;         /* leading dimension of charges/types (>= max natoms) */
+    int ntypes;            /* primary%num_atomtypes */
+    int n_chains;          /* independent chains sharing this description (>=1) */
+    const int* natoms;     /* [nres] nb%atom_in_residue */
+    const int* is_active;  /* [nres] input%is_active */
+    const int* count;      /* [nres] primary%num_residues */
+    const int* capacity;   /* [nres] slots per active type (<= NB_MAX_MOLECULE, parameters.f90:8) */
+    const double* charges; /* [nres*max_atoms] */
+    const int* types;      /* [nres*max_atoms] 1-based atom types */
+    const double* sigma;   /* [ntypes*ntypes] Angstrom */
+    const double* epsilon; /* [ntypes*ntypes] Kelvin (parameters_parser.f90:82) */
+    const double* com;     /* [3 * sum(count)] */
+    const double* offsets; /* [3 * sum(count*natoms)] */
+    double box_lo[3];      /* primary%bounds(:,1) */
+    double box_len[3];     /* primary%matrix(d,d); orthorhombic boxes only (box%type 1,2) */
+    double alpha;          /* ewald%alpha */
+    double cutoff;         /* input%real_space_cutoff */
+    double temperature;    /* input%temp_K */
+    const double* fugacity;/* [nres] already converted to 1/A^3 (prepare_utils.f90:68) */
+    int kmax[3];           /* ewald%kmax */
+    double translation_step; /* input%translation_step */
+    double rotation_step;    /* input%rotation_step_angle */
+    double p_translation;    /* proba%translation */
+    double p_rotation;       /* proba%rotation */
+    int init_sk;           /* MMC_INIT_SK_* */
+    int deletion_mode;     /* MMC_DELETION_* */
+    int use_table;         /* 0: direct erfc/LJ (reference behaviour, parameters.f90:42); 1: tabulated_utils.f90 tables */
+    int device;            /* CUDA device ordinal */
+} mmc_desc;
+
+/* One record per trial move of a batched run (optional output). */
+typedef struct mmc_move_record {
+    int32_t kind;     /* MMC_* move type, 0 = no move happened (e.g. translation with N==0) */
+    int32_t res;      /* residue type */
+    int32_t mol;      /* molecule slot */
+    int32_t accepted; /* 1/0 */
+    double old_e[MMC_NE];
+    double new_e[MMC_NE];
+    double prob;      /* acceptance probability */
+} mmc_move_record;
+
+/* counter_type, simulation_state.f90:19-31 (swap omitted: no swap move exists, monte_carlo.f90:50-75) */
+typedef struct mmc_counters {
+    int64_t translations, rotations, creations, deletions;
+    int64_t trial_translations, trial_rotations, trial_creations, trial_deletions;
+} mmc_counters;
+
+typedef struct mmc_handle mmc_t;
+
+/* ---- set-up ------------------------------------------------------------------------------ */
+
+/* Ewald parameters from cut-off and tolerance: replaces ComputeEwaldParameters and
+ * ComputeFourierIndices (prepare_utils.f90:169-214).  Host-only arithmetic (runs once). */
+int mmc_ewald_setup(double cutoff, double tolerance, const double box_len[3],
+                    double* alpha, int kmax[3], int* num_kvectors);
+
+/* Build the device-resident state: SoA coordinates/charges/types, LJ table, k-vector set
+ * (PrecomputeValidReciprocalVectors, ewald_kvectors.f90:44), weights W(k)
+ * (ComputeReciprocalWeights, ewald_kvectors.f90:225), optional tables (PrecomputeTable,
+ * tabulated_utils.f90:10).  Replaces AllocateArray (prepare_utils.f90:220). */
+int mmc_init(mmc_t** handle, const mmc_desc* desc);
+void mmc_destroy(mmc_t* handle);
+const char* mmc_last_error(void);
+
+int mmc_num_kvectors(const mmc_t* handle);
+/* copies of the k-set: kx,ky,kz,form_factor (ewald%kvectors, ewald%form_factor) and W(k)
+ * (ewald%recip_constants); any pointer may be NULL */
+int mmc_get_kvectors(mmc_t* handle, int* kx, int* ky, int* kz, double* weight, double* form);
+
+/* per-chain thermodynamic state (isotherm sweeps): fugacity[nres] in 1/A^3, temperature in K */
+int mmc_set_chain_params(mmc_t* handle, int chain, const double* fugacity, double temperature);
+/* overwrite / read back one chain's guests: count[nres], packed com/offsets as in mmc_desc */
+int mmc_set_chain_state(mmc_t* handle, int chain, const int* count, const double* com, const double* offsets);
+int mmc_get_chain_state(mmc_t* handle, int chain, int* count, double* com, double* offsets);
+/* step sizes (input%translation_step / rotation_step_angle; AdjustMoveStepSizes stays on the host) */
+int mmc_set_step_sizes(mmc_t* handle, int chain, double translation_step, double rotation_step);
+
+/* ---- single-point energy ----------------------------------------------------------------- */
+
+/* ComputeSystemEnergy (energy_utils.f90:18): pair sweep i<j with intra-molecular exclusion,
+ * Ewald self, full S(k) + reciprocal energy, intra-residue correction of active residues.
+ * Stores the result as the chain's tracked `energy` and, with MMC_INIT_SK_FULL, the tracked
+ * A(k) := S(k) (with MMC_INIT_SK_ZERO it is zeroed, the reference's de-facto behaviour). */
+int mmc_system_energy(mmc_t* handle, int chain, double out[MMC_NE]);
+
+/* ---- strict mode: one trial move per call, host draws the random numbers -------------------- */
+
+/* SaveMoleculeState + ComputeOldEnergy + <proposal applied by the host> + ComputeNewEnergy
+ * (monte_carlo_utils.f90:444,347,275) in one fused device pass.
+ *   kind = MMC_TRANSLATION / MMC_ROTATION: mol is the moved slot, com_new/offs_new its proposed
+ *          geometry (3 and 3*natoms doubles).
+ *   kind = MMC_CREATION: mol must equal the current count (new last slot).
+ *   kind = MMC_DELETION: com_new/offs_new ignored (may be NULL).
+ * Nothing is committed; old_e/new_e receive type(energy_state) old and new. */
+int mmc_trial_energy(mmc_t* handle, int chain, int kind, int res, int mol,
+                     const double* com_new, const double* offs_new,
+                     double old_e[MMC_NE], double new_e[MMC_NE]);
+
+/* AcceptMove / AcceptCreationMove / AcceptDeletionMove (accept=1) or RejectMoleculeMove /
+ * RejectCreationMove / RejectDeletionMove (accept=0) for the pending trial
+ * (monte_carlo_utils.f90:410,485; create_molecule.f90:96,141; delete_molecule.f90:126,178).
+ * A(k) is double buffered: accept flips the buffer, reject costs nothing
+ * (replaces Save/RestoreSingleMolFourier, ewald_phase.f90:134,205). */
+int mmc_trial_commit(mmc_t* handle, int chain, int accept);
+
+/* once per block (PrintStatus / UpdateFiles, monte_carlo.f90:82-84): tracked energies,
+ * counts and packed coordinates of one chain */
+int mmc_sync_to_host(mmc_t* handle, int chain, int* count, double* com, double* offsets,
+                     double energies[MMC_NE]);
+/* tracked A(k) as (re,im) pairs, 2*K doubles (ewald%recip_amplitude) */
+int mmc_get_sk(mmc_t* handle, int chain, double* sk);
+
+/* ---- batched mode: the inner `do current_step` loop of MonteCarloLoop on the device ------- */
+
+/* Runs n_steps Monte Carlo steps (monte_carlo.f90:42-76) on EVERY chain, all chains advancing
+ * one step per launch group, the step sequence captured in a CUDA graph.
+ * Random numbers: if tape != NULL chain c reads its uniforms sequentially from
+ * tape[c*tape_stride ...] (strict replay of a recorded stream, draw order of SURVEY 3.8);
+ * otherwise Philox4x32-10 keyed by seed with counter (step, chain, draw).
+ * records (optional, may be NULL): n_chains*n_steps entries, chain-major.
+ * counters (optional): n_chains entries, accumulated since mmc_init. */
+int mmc_run_batch(mmc_t* handle, int64_t n_steps, uint64_t seed,
+                  const double* tape, int64_t tape_stride,
+                  mmc_move_record* records, mmc_counters* counters);
+/* same, but only enqueues on the handle's stream (device-resident benchmarking);
+ * pair with mmc_synchronize. records are left on the device. */
+int mmc_run_batch_async(mmc_t* handle, int64_t n_steps, uint64_t seed);
+int mmc_synchronize(mmc_t* handle);
+/* number of uniforms chain consumed from its tape in the last mmc_run_batch */
+int64_t mmc_tape_used(mmc_t* handle, int chain);
+
+/* ---- kernel-level entry points for parity tests (mmc_dbg_*) -------------------------------- */
+
+/* ComputePairInteractionEnergy_singlemol (energy_utils.f90:374) at the current geometry */
+int mmc_dbg_pair_singlemol(mmc_t* handle, int chain, int res, int mol, double* e_non_coulomb, double* e_coulomb);
+/* ComputeEwaldSelfInteractionSingleMol (ewald_energy.f90:308) */
+int mmc_dbg_self_singlemol(mmc_t* handle, int res, double* e_self);
+/* ComputeIntraResidueRealCoulombEnergySingleMol (ewald_energy.f90:371) */
+int mmc_dbg_intra_singlemol(mmc_t* handle, int chain, int res, int mol, double* e_intra);
+/* LookupTabulated (tabulated_utils.f90:87) evaluated on the device: which = 0 erfc(alpha r)/r, 1 r^6, 2 r^12 */
+int mmc_dbg_table_lookup(mmc_t* handle, int which, const double* r, int n, double* out);
+/* device erfc used by the pair sweep, for accuracy tests */
+int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
+/* timing of the last pair / recip sweeps in a batched run is taken by the caller with
+ * CUDA events on this stream */
+void* mmc_stream(mmc_t* handle);
+/* kernel launches issued by this handle since init (bench.py's gpu_launches) */
+int64_t mmc_launch_count(const mmc_t* handle);
+/* FP64 FMA peak micro-benchmark (register-resident DFMA chains): returns TFLOP/s */
+int mmc_measure_fp64_peak(int device, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MANIAC_GPU_H */

@@ -1,0 +1,42 @@
+"""Converts the reference's shipped fixture systems (mc-topology submodule) into the packed
+``System`` .npz files under tests/golden/, and records the reference's own known answers.
+
+Run in the build container only (needs /root/reference); the GPU box uses the committed files.
+    python tools/make_golden.py
+"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from maniac_mc_b200 import builders  # noqa: E402
+
+REF = "/root/reference/mc-topology"
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+CASES = {
+    # name: (dir, maniac, data, inc, capacity)
+    "lj_gas": ("testcase-energy/LJ-gas", "input.maniac", "topology.data", "parameters.inc", 256),
+    "h2o_gas": ("testcase-energy/H2O-gas", "input.maniac", "topology.data", "parameters.inc", 512),
+    "h2o_ads": ("testcase-adsorption/H2O", "input.maniac", "topology.data", "parameters.inc", 512),
+    "zif8_h2o": ("testcase-adsorption/ZIF8-H2O", "zif8-water.maniac", "zif8-water.data", "zif8-water.inc", 512),
+}
+
+# Known answers held by the reference's own tests (kcal/mol):
+#   tests/integration/energy/LJ-gas/run-test.sh:18 parses TotEng from
+#   mc-topology/testcase-energy/LJ-gas/log.lammps:79-80  ("0 -38.589253 -0.40707303 49.708669 -87.890849")
+#   tests/integration/energy/H2O-gas/run-test.sh:15-16   (ref_energy=-32.822927, tolerance=0.01)
+KAT = {
+    "lj_gas": {"TotEng": -38.589253, "E_vdwl": -0.40707303, "E_coul": 49.708669, "E_long": -87.890849, "tolerance": 0.01},
+    "h2o_gas": {"TotEng": -32.822927, "tolerance": 0.01},
+}
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    for name, (d, m, t, p, cap) in CASES.items():
+        s = builders.from_files(*(os.path.join(REF, d, f) for f in (m, t, p)), capacity=cap)
+        s.save(os.path.join(OUT, name + ".npz"))
+        print(name, "counts", s.count.tolist(), "natoms", s.natoms.tolist(), "alpha %.6f" % s.alpha, "kmax", s.kmax,
+              "K", s.num_kvectors, "L", s.box_len.tolist())
+    with open(os.path.join(OUT, "reference_kat.json"), "w") as fh:
+        json.dump(KAT, fh, indent=1)
