@@ -1,0 +1,173 @@
+// common.cuh -- device-side data layout and helpers of libmaniacgpu (sm_100a).
+//
+// HBM layout (see DESIGN.md "Data layout"):
+//   shared, read-only : framework SoA fx/fy/fz/fq (double) + ftype/fmol (int), LJ table
+//                       lj[ti*ntypes+tj] = {sigma, 4*epsilon}, k-vector list kvec (int4: kx,ky,kz,0),
+//                       fw[k] = form_factor(k) * W(k)
+//   per chain, mutable: guest SoA gx/gy/gz (absolute positions, slot-major), gcom/goff (COM + site
+//                       offsets, the reference's mol_com/site_offset), count, A(k) double-buffered
+//                       (double2, 2*K per chain) with a parity bit, tracked energies, counters,
+//                       one Trial descriptor.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/maniac_gpu.h"
+
+#define MMC_MAX_RES 8
+#define PAIR_THREADS 256
+#define RECIP_THREADS 256
+#define TAIL_THREADS 128
+
+// constants.f90:7-20
+#define MMC_PI 3.14159265358979323846
+#define MMC_TWOPI (2.0 * MMC_PI)
+#define MMC_EPS0_INV_eVA 14.40198
+#define MMC_KB_eVK 8.6173852e-5
+#define MMC_ERR 1.0e-10
+#define MMC_PROB_CREATE_DELETE 0.5  // parameters.f90:21
+
+struct DevConst {
+    int nres, ntypes, n_chains, n_active;
+    int natoms[MMC_MAX_RES], is_active[MMC_MAX_RES], cap[MMC_MAX_RES], active_list[MMC_MAX_RES];
+    int g_atom_base[MMC_MAX_RES];  // first guest-atom index of residue r inside a chain's guest arrays
+    int g_mol_base[MMC_MAX_RES];   // first guest-molecule slot of residue r
+    int g_atoms, g_mols;           // per-chain guest capacities (atoms, molecules)
+    int n_fw;                      // framework atoms (all inactive residues, flattened)
+    int n_pair_tiles;              // ceil((n_fw + g_atoms) / PAIR_THREADS)
+    int n_k_tiles;                 // ceil(nk / RECIP_THREADS)
+    int nk, kmax[3], kstride;      // kstride = max(kmax)+1 : row length of a 1-D phase table
+    int deletion_mode, use_table;
+    double q[MMC_MAX_RES][MMC_MAX_MOL_ATOMS];  // active residues only
+    int type[MMC_MAX_RES][MMC_MAX_MOL_ATOMS];  // 0-based atom types
+    double self_e[MMC_MAX_RES];                // ComputeEwaldSelfInteractionSingleMol per residue (K)
+    double lo[3], L[3], invL[3], volume;
+    double alpha, rc, coul_const, recip_const;  // coul_const = EPS0_INV_eVA/KB_eVK ; recip_const = coul_const*2pi/V
+    double p_translation, p_rotation;
+    // pointers
+    const double *fx, *fy, *fz, *fq;
+    const int *ftype, *fmol;
+    const double2* lj;
+    const int4* kvec;
+    const double* fw;
+    const double *tab_erfc, *tab_r6, *tab_r12;  // tabulated_utils.f90 tables (5001 points each)
+    double tab_dx;
+};
+
+// one pending trial move of one chain
+struct Trial {
+    int kind, res, mol, nat;
+    int do_old, do_new;    // real-space sweeps wanted (ComputeOldEnergy / ComputeNewEnergy pair calls)
+    int r_plus, r_minus;   // reciprocal update: A' = A + sum q phi(plus) - sum q phi(minus)
+    int excl;              // 1: exclude slot (res, mol) from the sweep
+    int accepted, error, draw;
+    double prob;
+    double q[MMC_MAX_MOL_ATOMS];
+    int type[MMC_MAX_MOL_ATOMS];
+    double p_old[MMC_MAX_MOL_ATOMS][3];   // absolute positions, old geometry
+    double p_new[MMC_MAX_MOL_ATOMS][3];   // absolute positions, proposed geometry
+    double p_plus[MMC_MAX_MOL_ATOMS][3];  // positions whose phases are added (== p_new except deletion/reference)
+    double com_new[3];
+    double off_new[MMC_MAX_MOL_ATOMS][3];
+    double old_e[MMC_NE], new_e[MMC_NE];
+};
+
+struct ChainState {
+    int* count;        // [C][MMC_MAX_RES]
+    double *gx, *gy, *gz;  // [C][g_atoms]
+    double* gcom;      // [C][g_mols][3]
+    double* goff;      // [C][g_atoms][3]
+    double2* A;        // [C][2][nk]
+    int* cur;          // [C] which A buffer is current
+    double* energy;    // [C][MMC_NE]
+    double* fug;       // [C][MMC_MAX_RES]
+    double* temp;      // [C]
+    double* tstep;     // [C]
+    double* rstep;     // [C]
+    mmc_counters* counters;  // [C]
+    Trial* trial;      // [C]
+    double2* phase;    // [C][2 sets][3 axes][MMC_MAX_MOL_ATOMS][kstride]  (set 0 = plus, 1 = minus)
+    double* pair_part; // [C][n_pair_tiles][4]  (lj_old, coul_old, lj_new, coul_new)
+    double* recip_part;// [C][n_k_tiles][2]     (sum fW|A|^2, sum fW|A'|^2)
+    long long* tape_pos;  // [C]
+    int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)
+};
+
+struct RngSrc {
+    const double* tape;  // device pointer or nullptr
+    long long tape_stride;
+    unsigned long long seed;
+    unsigned long long step;  // step index of this launch
+};
+
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int i = 0; i < 10; i++) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+        uint32_t n0 = hi1 ^ c[1] ^ k0, n1 = lo1, n2 = hi0 ^ c[3] ^ k1, n3 = lo0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+// draw d of step s of chain c: same definition as oracle/maniac_oracle.c:orc_philox_uniform
+__device__ __forceinline__ double philox_uniform(unsigned long long seed, uint32_t chain, unsigned long long step, uint32_t draw) {
+    uint32_t c[4] = {(uint32_t)step, (uint32_t)(step >> 32), chain, draw >> 1};
+    philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+    uint32_t lo = c[2 * (draw & 1)], hi = c[2 * (draw & 1) + 1];
+    unsigned long long bits = (((unsigned long long)hi << 32) | lo) >> 11;
+    return (double)bits * (1.0 / 9007199254740992.0);
+}
+
+// gfortran modulo(a, p), p > 0 (geometry_utils.f90:190,389): exact remainder in [0, p)
+__device__ __forceinline__ double f_modulo(double a, double p, double invp) {
+    double n = floor(a * invp);
+    double r = fma(-n, p, a);
+    if (r < 0.0) r += p;
+    else if (r >= p) r -= p;
+    return r;
+}
+// ComputeDistance geometry_utils.f90:385-393, one axis
+__device__ __forceinline__ double min_image(double d, double L, double invL) {
+    return f_modulo(d + 0.5 * L, L, invL) - 0.5 * L;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+// deterministic block sum of NV values per thread; result valid in thread 0
+template <int NV, int NT>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * NT/32 */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        v[i] = warp_sum(v[i]);
+        if (lane == 0) smem[i * (NT / 32) + w] = v[i];
+    }
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            double x = (lane < NT / 32) ? smem[i * (NT / 32) + lane] : 0.0;
+            v[i] = warp_sum(x);
+        }
+    }
+    __syncthreads();
+}
+
+// erfc used by the real-space sweeps.  Accuracy contract (tests/test_gpu_parity.py::test_erfc):
+// |device - glibc| <= 2e-15 absolute and <= 1e-13 relative on [0, 6].
+__device__ __forceinline__ double mmc_erfc(double x) { return erfc(x); }
+
+// LookupTabulated tabulated_utils.f90:87-113
+__device__ __forceinline__ double table_lookup(const double* f, double dx, double r) {
+    const int n = 5000;  // TABULATED_POINTS parameters.f90:41
+    if (r <= 0.0) return f[0];
+    if (r >= n * dx) return 0.0;
+    int i = (int)(r / dx);
+    double f1 = f[i], f2 = f[i + 1];
+    double t = (r - i * dx) / dx;
+    return (1.0 - t) * f1 + t * f2;
+}

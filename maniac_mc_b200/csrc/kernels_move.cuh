@@ -1,0 +1,505 @@
+// kernels_move.cuh -- the per-move hot path: proposal, real-space pair sweep, reciprocal
+// Delta-S(k) sweep, and the accept/commit tail.  One launch serves all chains (grid.y = chain).
+#pragma once
+#include "common.cuh"
+
+// ----------------------------------------------------------------------------------------------
+// small helpers on chain-local guest storage
+__device__ __forceinline__ double* g_com(const DevConst& dc, const ChainState& cs, int c, int r, int m) {
+    return cs.gcom + ((size_t)c * dc.g_mols + dc.g_mol_base[r] + m) * 3;
+}
+__device__ __forceinline__ size_t g_atom(const DevConst& dc, int c, int r, int m, int a) {
+    return (size_t)c * dc.g_atoms + dc.g_atom_base[r] + (size_t)m * dc.natoms[r] + a;
+}
+
+struct Rng {
+    const RngSrc* src; ChainState cs; int c; int draw;
+    __device__ double next() {
+        if (src->tape) { long long p = cs.tape_pos[c]++; return src->tape[(size_t)c * src->tape_stride + p]; }
+        return philox_uniform(src->seed, (uint32_t)c, src->step, (uint32_t)draw++);
+    }
+};
+
+// RotationMatrix helper_utils.f90:39-77 + matmul of ApplyRandomRotation monte_carlo_utils.f90:63-64
+__device__ inline void rotate_offsets(int axis, double theta, int nat, const double (*in)[3], double (*out)[3]) {
+    double s, c; sincos(theta, &s, &c);
+    double R[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    if (axis == 1) { R[1][1] = c; R[1][2] = -s; R[2][1] = s; R[2][2] = c; }
+    else if (axis == 2) { R[0][0] = c; R[0][2] = s; R[2][0] = -s; R[2][2] = c; }
+    else { R[0][0] = c; R[0][1] = -s; R[1][0] = s; R[1][1] = c; }
+    for (int a = 0; a < nat; a++) {
+        double v0 = in[a][0], v1 = in[a][1], v2 = in[a][2];
+        for (int i = 0; i < 3; i++) out[a][i] = R[i][0] * v0 + R[i][1] * v1 + R[i][2] * v2;
+    }
+}
+
+// Fills the Trial of chain c for a move of `kind` on (res, mol) with proposed geometry
+// com_new/off_new (ignored for deletion).  Mirrors which sweeps ComputeOldEnergy /
+// ComputeNewEnergy (monte_carlo_utils.f90:347,275) request for each move type.  Single thread.
+__device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int c, int kind, int r, int m,
+                                   const double* com_new, const double (*off_new)[3]) {
+    Trial& t = cs.trial[c];
+    const int nat = dc.natoms[r];
+    t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.accepted = 0; t.prob = 0.0;
+    for (int a = 0; a < nat; a++) { t.q[a] = dc.q[r][a]; t.type[a] = dc.type[r][a]; }
+    const int cnt = cs.count[c * MMC_MAX_RES + r];
+    if (kind != MMC_CREATION) {  // old geometry of the selected slot
+        const double* com = g_com(dc, cs, c, r, m);
+        for (int a = 0; a < nat; a++) {
+            const double* off = cs.goff + g_atom(dc, c, r, m, a) * 3;
+            for (int d = 0; d < 3; d++) t.p_old[a][d] = com[d] + off[d];
+        }
+    }
+    if (kind != MMC_DELETION) {
+        for (int d = 0; d < 3; d++) t.com_new[d] = com_new[d];
+        for (int a = 0; a < nat; a++)
+            for (int d = 0; d < 3; d++) {
+                t.off_new[a][d] = off_new[a][d];
+                t.p_new[a][d] = com_new[d] + off_new[a][d];
+                t.p_plus[a][d] = t.p_new[a][d];
+            }
+    }
+    switch (kind) {
+        case MMC_TRANSLATION: case MMC_ROTATION:
+            t.do_old = 1; t.do_new = 1; t.r_plus = 1; t.r_minus = 1; t.excl = 1; break;
+        case MMC_CREATION:
+            // the new molecule sits in slot `cnt`, outside the swept range, so nothing to exclude
+            t.do_old = 0; t.do_new = 1; t.r_plus = 1; t.r_minus = 0; t.excl = 0;
+            // like the reference (create_molecule.f90:180-199) the geometry is written into the slot at
+            // proposal time and stays there even if the move is rejected
+            {
+                double* com = g_com(dc, cs, c, r, m);
+                for (int d = 0; d < 3; d++) com[d] = com_new[d];
+                for (int a = 0; a < nat; a++) {
+                    size_t ia = g_atom(dc, c, r, m, a);
+                    for (int d = 0; d < 3; d++) cs.goff[ia * 3 + d] = off_new[a][d];
+                    cs.gx[ia] = t.p_new[a][0]; cs.gy[ia] = t.p_new[a][1]; cs.gz[ia] = t.p_new[a][2];
+                }
+            }
+            break;
+        case MMC_DELETION:
+            t.do_old = 1; t.do_new = 0; t.excl = 1;
+            if (dc.deletion_mode == MMC_DELETION_REFERENCE) {
+                // Q2: ComputeNewEnergy passes is_creation=deletion_flag (monte_carlo_utils.f90:308), so the
+                // phases of the molecule now in this slot (the former last one, delete_molecule.f90:107-114)
+                // are ADDED
+                t.r_plus = 1; t.r_minus = 0;
+                const int last = cnt - 1;
+                const double* com = g_com(dc, cs, c, r, last);
+                for (int a = 0; a < nat; a++) {
+                    const double* off = cs.goff + g_atom(dc, c, r, last, a) * 3;
+                    for (int d = 0; d < 3; d++) t.p_plus[a][d] = com[d] + off[d];
+                }
+            } else {  // physical: subtract the deleted molecule (is_deletion branch, ewald_energy.f90:246-250)
+                t.r_plus = 0; t.r_minus = 1;
+            }
+            break;
+    }
+}
+
+// 1-D phase tables e^{i k theta}, k = 0..kmax, by direct cos/sin(k*theta)
+// (ComputeAtomPhase + ComputePhaseFactors1D, ewald_phase.f90:41-109).  All threads of the block.
+__device__ inline void build_phase_tables(const DevConst& dc, const ChainState& cs, int c) {
+    const Trial& t = cs.trial[c];
+    if (t.kind <= 0) return;
+    const int ks = dc.kstride;
+    double2* ph = cs.phase + (size_t)c * 2 * 3 * MMC_MAX_MOL_ATOMS * ks;
+    const int per_set = 3 * t.nat * ks;
+    for (int i = threadIdx.x; i < 2 * per_set; i += blockDim.x) {
+        const int set = i / per_set, j = i % per_set;
+        const int ax = j / (t.nat * ks), a = (j / ks) % t.nat, k = j % ks;
+        if (k > dc.kmax[ax]) continue;
+        if ((set == 0 && !t.r_plus) || (set == 1 && !t.r_minus)) continue;
+        const double pos = set == 0 ? t.p_plus[a][ax] : t.p_old[a][ax];
+        const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
+        double s, co; sincos((double)k * theta, &s, &co);
+        ph[((size_t)(set * 3 + ax) * MMC_MAX_MOL_ATOMS + a) * ks + k] = make_double2(co, s);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// strict mode: the host made the proposal (Fortran RandomTranslation / ApplyRandomRotation /
+// InsertAndOrientMolecule); arguments by value, no H2D copy.
+struct HostTrial { int chain, kind, res, mol; double com[3]; double off[MMC_MAX_MOL_ATOMS][3]; };
+
+__global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
+    if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, ht.kind, ht.res, ht.mol, ht.com, ht.off);
+    __syncthreads();
+    build_phase_tables(dc, cs, ht.chain);
+}
+
+// batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
+// proposal geometry, draw order as in SURVEY 3.8.  Single thread per chain.
+__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c) {
+    Trial& t = cs.trial[c];
+    t.kind = 0; t.error = 0; t.accepted = 0;
+    for (int i = 0; i < MMC_NE; i++) { t.old_e[i] = 0.0; t.new_e[i] = 0.0; }
+    Rng rng{&rs, cs, c, 0};
+    if (dc.n_active == 0) { t.draw = 0; return; }
+    // PickRandomResidueType monte_carlo_utils.f90:136-164
+    const int r = dc.active_list[(int)(rng.next() * dc.n_active)];
+    const int cnt = cs.count[c * MMC_MAX_RES + r];
+    const int nat = dc.natoms[r];
+    // PickRandomMoleculeIndex :170-182
+    int m = -1;
+    if (cnt != 0) { m = (int)(rng.next() * cnt); if (m > cnt - 1) m = cnt - 1; }
+    const double draw = rng.next();
+    mmc_counters& ctr = cs.counters[c];
+    double com_new[3]; double off_new[MMC_MAX_MOL_ATOMS][3];
+    if (draw <= dc.p_translation) {
+        if (m >= 0) {  // Translation translation.f90:36-112
+            ctr.trial_translations++;
+            const double* com = g_com(dc, cs, c, r, m);
+            const double step = cs.tstep[c];
+            double u[3]; for (int d = 0; d < 3; d++) u[d] = rng.next() - 0.5;
+            for (int d = 0; d < 3; d++) {
+                double x = com[d] + u[d] * step;
+                com_new[d] = dc.lo[d] + f_modulo(x - dc.lo[d], dc.L[d], dc.invL[d]);  // ApplyPBC
+            }
+            for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_new[a][d] = cs.goff[g_atom(dc, c, r, m, a) * 3 + d];
+            build_trial(dc, cs, c, MMC_TRANSLATION, r, m, com_new, off_new);
+        }
+    } else if (draw <= dc.p_rotation + dc.p_translation) {
+        if (nat != 1 && m >= 0) {  // Rotation rotation.f90:34-75
+            ctr.trial_rotations++;
+            const double theta = (rng.next() - 0.5) * cs.rstep[c];  // ChooseRotationAngle
+            const int axis = (int)(rng.next() * 3.0) + 1;
+            double off_old[MMC_MAX_MOL_ATOMS][3];
+            for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_old[a][d] = cs.goff[g_atom(dc, c, r, m, a) * 3 + d];
+            rotate_offsets(axis, theta, nat, off_old, off_new);
+            const double* com = g_com(dc, cs, c, r, m);
+            for (int d = 0; d < 3; d++) com_new[d] = com[d];
+            build_trial(dc, cs, c, MMC_ROTATION, r, m, com_new, off_new);
+        }
+    } else {
+        if (rng.next() <= MMC_PROB_CREATE_DELETE) {  // CreateMolecule create_molecule.f90:41-207
+            m = cnt;
+            if (m >= dc.cap[r]) { t.error = 1; }  // CheckMoleculeIndex -> AbortRun in the reference
+            else {
+                ctr.trial_creations++;
+                for (int d = 0; d < 3; d++) com_new[d] = dc.lo[d] + dc.L[d] * rng.next();
+                double tmpl[MMC_MAX_MOL_ATOMS][3];  // geometry of slot 1 of this type (Q9)
+                for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) tmpl[a][d] = cs.goff[g_atom(dc, c, r, 0, a) * 3 + d];
+                if (nat != 1) {
+                    const double theta = rng.next() * MMC_TWOPI;
+                    const int axis = (int)(rng.next() * 3.0) + 1;
+                    rotate_offsets(axis, theta, nat, tmpl, off_new);
+                } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
+                build_trial(dc, cs, c, MMC_CREATION, r, m, com_new, off_new);
+            }
+        } else if (cnt != 0) {  // DeleteMolecule delete_molecule.f90:41-199
+            ctr.trial_deletions++;
+            build_trial(dc, cs, c, MMC_DELETION, r, m, nullptr, nullptr);
+        }
+    }
+    t.draw = rng.draw;
+}
+
+// ----------------------------------------------------------------------------------------------
+// Real-space sweep: ComputePairInteractionEnergy_singlemol (energy_utils.f90:374-442) for the old
+// and the proposed geometry of the moved molecule in ONE pass over all other atoms.
+// grid = (n_pair_tiles, n_chains), block = PAIR_THREADS; thread j owns one "other" atom
+// (framework atoms are shared by all chains and stay L2 resident; guest atoms are per chain).
+// LJ only inside the cut-off, erfc-Coulomb for every minimum-image pair (Q3), charges below
+// 1e-10 skipped.  FP64 throughout.  Partial sums per block, summed in fixed order by the tail.
+struct PairSmem {
+    double px_o[MMC_MAX_MOL_ATOMS], py_o[MMC_MAX_MOL_ATOMS], pz_o[MMC_MAX_MOL_ATOMS];
+    double px_n[MMC_MAX_MOL_ATOMS], py_n[MMC_MAX_MOL_ATOMS], pz_n[MMC_MAX_MOL_ATOMS];
+    double q[MMC_MAX_MOL_ATOMS];
+    int type[MMC_MAX_MOL_ATOMS];
+    int nat, do_old, do_new, kind;
+    double red[4 * PAIR_THREADS / 32];
+};
+
+__device__ __forceinline__ void pair_eval(const DevConst& dc, double dx, double dy, double dz, double qa, double qj,
+                                          double2 lj, bool charged, double& e_lj, double& e_c) {
+    dx = min_image(dx, dc.L[0], dc.invL[0]);
+    dy = min_image(dy, dc.L[1], dc.invL[1]);
+    dz = min_image(dz, dc.L[2], dc.invL[2]);
+    const double r2 = dx * dx + dy * dy + dz * dz;
+    const double r = sqrt(r2);
+    if (r < dc.rc && lj.y != 0.0) {
+        const double sr = lj.x / r;
+        const double sr2 = sr * sr;
+        const double r6 = sr2 * sr2 * sr2;
+        e_lj += lj.y * (r6 * r6 - r6);
+    }
+    if (charged) e_c += qa * qj * mmc_erfc(dc.alpha * r) / r;
+}
+
+__global__ void __launch_bounds__(PAIR_THREADS) k_pair_sweep(DevConst dc, ChainState cs, int chain0) {
+    __shared__ PairSmem sm;
+    const int c = blockIdx.y + chain0;
+    const Trial& t = cs.trial[c];
+    if (t.kind <= 0 || (!t.do_old && !t.do_new)) return;  // uniform per block
+    if (threadIdx.x < t.nat) {
+        const int a = threadIdx.x;
+        sm.px_o[a] = t.p_old[a][0]; sm.py_o[a] = t.p_old[a][1]; sm.pz_o[a] = t.p_old[a][2];
+        sm.px_n[a] = t.p_new[a][0]; sm.py_n[a] = t.p_new[a][1]; sm.pz_n[a] = t.p_new[a][2];
+        sm.q[a] = t.q[a]; sm.type[a] = t.type[a];
+    }
+    if (threadIdx.x == 0) { sm.nat = t.nat; sm.do_old = t.do_old; sm.do_new = t.do_new; sm.kind = t.kind; }
+    __syncthreads();
+    const int j = blockIdx.x * PAIR_THREADS + threadIdx.x;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    bool valid = false; double xj = 0, yj = 0, zj = 0, qj = 0; int tj = 0;
+    if (j < dc.n_fw) {
+        valid = true; xj = dc.fx[j]; yj = dc.fy[j]; zj = dc.fz[j]; qj = dc.fq[j]; tj = dc.ftype[j];
+    } else if (j < dc.n_fw + dc.g_atoms) {
+        const int g = j - dc.n_fw;
+        // which active residue / slot does guest atom g belong to
+        int r = 0;
+#pragma unroll 1
+        for (int i = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (g >= dc.g_atom_base[rr]) r = rr; }
+        const int na = dc.natoms[r];
+        const int m = (g - dc.g_atom_base[r]) / na, a = (g - dc.g_atom_base[r]) % na;
+        if (m < cs.count[c * MMC_MAX_RES + r] && !(t.excl && r == t.res && m == t.mol)) {
+            valid = true;
+            const size_t ia = (size_t)c * dc.g_atoms + g;
+            xj = cs.gx[ia]; yj = cs.gy[ia]; zj = cs.gz[ia]; qj = dc.q[r][a]; tj = dc.type[r][a];
+        }
+    }
+    if (valid) {
+        const bool qj_ok = fabs(qj) >= MMC_ERR;
+        const int nat = sm.nat;
+        for (int a = 0; a < nat; a++) {
+            const double qa = sm.q[a];
+            const bool charged = qj_ok && fabs(qa) >= MMC_ERR;
+            const double2 lj = dc.lj[sm.type[a] * dc.ntypes + tj];
+            // ComputeDistance: delta = pos(other) - pos(moved)
+            if (sm.do_old) pair_eval(dc, xj - sm.px_o[a], yj - sm.py_o[a], zj - sm.pz_o[a], qa, qj, lj, charged, acc[0], acc[1]);
+            if (sm.do_new) pair_eval(dc, xj - sm.px_n[a], yj - sm.py_n[a], zj - sm.pz_n[a], qa, qj, lj, charged, acc[2], acc[3]);
+        }
+    }
+    block_sum<4, PAIR_THREADS>(acc, sm.red);
+    if (threadIdx.x == 0) {
+        double* out = cs.pair_part + ((size_t)c * dc.n_pair_tiles + blockIdx.x) * 4;
+        out[0] = acc[0]; out[1] = acc[1]; out[2] = acc[2]; out[3] = acc[3];
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Reciprocal sweep: ComputeRecipEnergySingleMol (ewald_energy.f90:191-274), parallel over k.
+// grid = (n_k_tiles, n_chains), block = RECIP_THREADS; one k-vector per thread.  Reads the current
+// A(k), writes A'(k) into the other half of the double buffer (replaces the K-length copies of
+// Save/RestoreSingleMolFourier, ewald_phase.f90:179-181,249-251) and accumulates both
+// sum f W |A|^2 (the reference's "old" call, a no-op update) and sum f W |A'|^2.
+// The moved molecule's 1-D phase tables (built once per trial by build_phase_tables) are staged in
+// shared memory.  HBM traffic per k-eval: 16 B read + 16 B write + 8 B fW + 16 B kvec.
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ double2 ph_at(const double2* tab, int k) {  // negative k by conjugation (ewald_phase.f90:105-107)
+    double2 v = tab[k < 0 ? -k : k];
+    if (k < 0) v.y = -v.y;
+    return v;
+}
+
+__global__ void __launch_bounds__(RECIP_THREADS) k_recip_sweep(DevConst dc, ChainState cs, int chain0) {
+    extern __shared__ double2 s_ph[];  // [2][3][nat][kstride]
+    __shared__ double red[2 * RECIP_THREADS / 32];
+    const int c = blockIdx.y + chain0;
+    const Trial& t = cs.trial[c];
+    if (t.kind <= 0) return;
+    const int nat = t.nat, ks = dc.kstride;
+    const bool plus = t.r_plus, minus = t.r_minus;
+    const double2* gph = cs.phase + (size_t)c * 2 * 3 * MMC_MAX_MOL_ATOMS * ks;
+    for (int i = threadIdx.x; i < 2 * 3 * nat * ks; i += blockDim.x) {
+        const int k = i % ks, a = (i / ks) % nat, sa = i / (ks * nat);  // sa = set*3+axis
+        s_ph[i] = gph[((size_t)sa * MMC_MAX_MOL_ATOMS + a) * ks + k];
+    }
+    __syncthreads();
+    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
+    double acc[2] = {0.0, 0.0};
+    if (ik < dc.nk) {
+        const int cur = cs.cur[c];
+        const double2* A = cs.A + ((size_t)c * 2 + cur) * dc.nk;
+        double2* An = cs.A + ((size_t)c * 2 + (cur ^ 1)) * dc.nk;
+        const int4 kv = dc.kvec[ik];
+        double sre = 0.0, sim = 0.0;
+        for (int a = 0; a < nat; a++) {
+            double2 pn = make_double2(0.0, 0.0), po = make_double2(0.0, 0.0);
+            if (plus) pn = cmul(cmul(ph_at(s_ph + ((0 * 3 + 0) * nat + a) * ks, kv.x), ph_at(s_ph + ((0 * 3 + 1) * nat + a) * ks, kv.y)),
+                                ph_at(s_ph + ((0 * 3 + 2) * nat + a) * ks, kv.z));
+            if (minus) po = cmul(cmul(ph_at(s_ph + ((1 * 3 + 0) * nat + a) * ks, kv.x), ph_at(s_ph + ((1 * 3 + 1) * nat + a) * ks, kv.y)),
+                                 ph_at(s_ph + ((1 * 3 + 2) * nat + a) * ks, kv.z));
+            const double q = t.q[a];
+            sre += q * (pn.x - po.x); sim += q * (pn.y - po.y);
+        }
+        const double2 a0 = A[ik];
+        const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
+        An[ik] = a1;
+        const double w = dc.fw[ik];
+        acc[0] = w * (a0.x * a0.x + a0.y * a0.y);  // amplitude_squared helper_utils.f90:125
+        acc[1] = w * (a1.x * a1.x + a1.y * a1.y);
+    }
+    block_sum<2, RECIP_THREADS>(acc, red);
+    if (threadIdx.x == 0) {
+        double* out = cs.recip_part + ((size_t)c * dc.n_k_tiles + blockIdx.x) * 2;
+        out[0] = acc[0]; out[1] = acc[1];
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// ComputeIntraResidueRealCoulombEnergySingleMol ewald_energy.f90:371-411 on explicit positions
+__device__ inline double intra_energy(const DevConst& dc, int nat, const double* q, const double (*p)[3]) {
+    double e = 0.0;
+    for (int a1 = 0; a1 < nat - 1; a1++)
+        for (int a2 = a1 + 1; a2 < nat; a2++) {
+            const double dx = min_image(p[a2][0] - p[a1][0], dc.L[0], dc.invL[0]);
+            const double dy = min_image(p[a2][1] - p[a1][1], dc.L[1], dc.invL[1]);
+            const double dz = min_image(p[a2][2] - p[a1][2], dc.L[2], dc.invL[2]);
+            const double r = sqrt(dx * dx + dy * dy + dz * dz);
+            if (r > MMC_ERR) e += q[a1] * q[a2] * (erfc(dc.alpha * r) - 1.0) / r;
+        }
+    return e * dc.coul_const;
+}
+
+// Sums the per-block partials in a fixed order and assembles type(energy_state) old/new exactly as
+// ComputeOldEnergy / ComputeNewEnergy do for each move type (monte_carlo_utils.f90:275-396).
+// All threads of the block participate; results land in the Trial (thread 0).
+__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, double* red) {
+    Trial& t = cs.trial[c];
+    if (t.kind <= 0) return;
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    if (t.do_old || t.do_new) {
+        const double* pp = cs.pair_part + (size_t)c * dc.n_pair_tiles * 4;
+        for (int i = threadIdx.x; i < dc.n_pair_tiles; i += TAIL_THREADS) {
+            v[0] += pp[i * 4 + 0]; v[1] += pp[i * 4 + 1]; v[2] += pp[i * 4 + 2]; v[3] += pp[i * 4 + 3];
+        }
+    }
+    const double* rp = cs.recip_part + (size_t)c * dc.n_k_tiles * 2;
+    for (int i = threadIdx.x; i < dc.n_k_tiles; i += TAIL_THREADS) { v[4] += rp[i * 2 + 0]; v[5] += rp[i * 2 + 1]; }
+    block_sum<6, TAIL_THREADS>(v, red);
+    if (threadIdx.x != 0) return;
+    const double lj_o = v[0], c_o = v[1] * dc.coul_const, lj_n = v[2], c_n = v[3] * dc.coul_const;
+    const double rec_o = v[4] * dc.recip_const, rec_n = v[5] * dc.recip_const;
+    double* o = t.old_e; double* n = t.new_e;
+    const double e_recip_tracked = cs.energy[c * MMC_NE + MMC_E_RECIP];
+    if (t.kind == MMC_CREATION) {
+        o[0] = 0; o[1] = 0; o[3] = 0; o[4] = 0; o[2] = e_recip_tracked;
+        o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
+        n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res]; n[4] = intra_energy(dc, t.nat, t.q, t.p_new);
+        n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
+    } else if (t.kind == MMC_DELETION) {
+        o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
+        o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
+        n[0] = 0; n[1] = 0; n[3] = 0; n[4] = 0; n[2] = rec_n;
+        n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
+    } else {
+        o[2] = rec_o; o[0] = lj_o; o[1] = c_o; o[3] = 0; o[4] = 0; o[5] = o[0] + o[1] + o[2];
+        n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = 0; n[4] = 0; n[5] = n[0] + n[1] + n[2];
+    }
+    // mc_acceptance_probability monte_carlo_utils.f90:184-221; N is read after the count update
+    const int cnt = cs.count[c * MMC_MAX_RES + t.res];
+    const double V = dc.volume, phi = cs.fug[c * MMC_MAX_RES + t.res], T = cs.temp[c];
+    const double de = n[5] - o[5];
+    if (t.kind == MMC_CREATION) t.prob = fmin(1.0, (phi * V / (double)(cnt + 1)) * exp(-de / T));
+    else if (t.kind == MMC_DELETION) t.prob = fmin(1.0, (((double)(cnt - 1) + 1.0) / (phi * V)) * exp(-de / T));
+    else t.prob = fmin(1.0, exp(-de / T));
+}
+
+// AcceptMove / AcceptCreationMove / AcceptDeletionMove (monte_carlo_utils.f90:410, create_molecule.f90:96,
+// delete_molecule.f90:126).  Rejection needs no work: coordinates are only written here and A(k) is
+// double buffered.  Single thread.
+__device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, int c, int accept) {
+    Trial& t = cs.trial[c];
+    if (t.kind <= 0) return;
+    t.accepted = accept;
+    if (!accept) { t.kind = -t.kind; return; }  // negative kind = finished trial (cannot be committed twice)
+    double* E = cs.energy + c * MMC_NE;
+    const double* o = t.old_e; const double* n = t.new_e;
+    mmc_counters& ctr = cs.counters[c];
+    const int r = t.res, m = t.mol, nat = t.nat;
+    int& cnt = cs.count[c * MMC_MAX_RES + r];
+    if (t.kind == MMC_TRANSLATION || t.kind == MMC_ROTATION) {
+        E[MMC_E_RECIP] = E[MMC_E_RECIP] + n[2] - o[2];
+        E[MMC_E_NONCOUL] = E[MMC_E_NONCOUL] + n[0] - o[0];
+        E[MMC_E_COUL] = E[MMC_E_COUL] + n[1] - o[1];
+        E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
+        if (t.kind == MMC_TRANSLATION) ctr.translations++; else ctr.rotations++;
+        double* com = g_com(dc, cs, c, r, m);
+        for (int d = 0; d < 3; d++) com[d] = t.com_new[d];
+        for (int a = 0; a < nat; a++) {
+            const size_t ia = g_atom(dc, c, r, m, a);
+            for (int d = 0; d < 3; d++) cs.goff[ia * 3 + d] = t.off_new[a][d];
+            cs.gx[ia] = t.p_new[a][0]; cs.gy[ia] = t.p_new[a][1]; cs.gz[ia] = t.p_new[a][2];
+        }
+    } else {
+        E[MMC_E_RECIP] = n[2];
+        E[MMC_E_NONCOUL] = E[MMC_E_NONCOUL] + n[0] - o[0];
+        E[MMC_E_COUL] = E[MMC_E_COUL] + n[1] - o[1];
+        E[MMC_E_SELF] = E[MMC_E_SELF] + n[3] - o[3];
+        E[MMC_E_INTRA] = E[MMC_E_INTRA] + n[4] - o[4];
+        E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
+        if (t.kind == MMC_CREATION) { ctr.creations++; cnt = cnt + 1; }  // geometry already in the slot
+        else {
+            ctr.deletions++;
+            const int last = cnt - 1;  // RemoveMolecule delete_molecule.f90:99-118: slot[m] <- slot[last]
+            if (m != last) {
+                double* com = g_com(dc, cs, c, r, m); const double* cl = g_com(dc, cs, c, r, last);
+                for (int d = 0; d < 3; d++) com[d] = cl[d];
+                for (int a = 0; a < nat; a++) {
+                    const size_t ia = g_atom(dc, c, r, m, a), il = g_atom(dc, c, r, last, a);
+                    for (int d = 0; d < 3; d++) cs.goff[ia * 3 + d] = cs.goff[il * 3 + d];
+                    cs.gx[ia] = cs.gx[il]; cs.gy[ia] = cs.gy[il]; cs.gz[ia] = cs.gz[il];
+                }
+            }
+            cnt = cnt - 1;
+        }
+    }
+    cs.cur[c] ^= 1;  // A'(k) becomes A(k)
+    t.kind = -t.kind;
+}
+
+// strict mode: sums -> Trial.old_e/new_e ; the host reads them and decides
+__global__ void __launch_bounds__(TAIL_THREADS) k_finalize(DevConst dc, ChainState cs, int chain, double* out /* 13 doubles */) {
+    __shared__ double red[6 * TAIL_THREADS / 32];
+    finalize_trial(dc, cs, chain, red);
+    if (threadIdx.x == 0 && out) {
+        const Trial& t = cs.trial[chain];
+        for (int i = 0; i < MMC_NE; i++) { out[i] = t.old_e[i]; out[MMC_NE + i] = t.new_e[i]; }
+        out[2 * MMC_NE] = t.prob;
+    }
+}
+__global__ void k_commit(DevConst dc, ChainState cs, int chain, int accept) {
+    if (threadIdx.x == 0) commit_trial(dc, cs, chain, accept);
+}
+
+// batched mode tail: finalize step s-1 (Metropolis test, commit, record), then propose step s.
+// grid = n_chains blocks.  first = 1: only propose (start of a chunk); last = 1: only finish.
+struct BatchCtl { RngSrc rng; mmc_move_record* recs; long long rec_stride; long long rec_base; };
+
+__global__ void __launch_bounds__(TAIL_THREADS) k_step_tail(DevConst dc, ChainState cs, const BatchCtl* ctl, int s, int first, int last) {
+    __shared__ double red[6 * TAIL_THREADS / 32];
+    const int c = blockIdx.x;
+    RngSrc rs = ctl->rng;
+    rs.step += (unsigned long long)s;
+    if (!first) {
+        finalize_trial(dc, cs, c, red);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            Trial& t = cs.trial[c];
+            const int kind = t.kind;
+            if (kind > 0) {
+                RngSrc prev = rs; prev.step = rs.step - 1;  // the accept draw belongs to the step being finished
+                Rng rng{&prev, cs, c, t.draw};
+                const double u = rng.next();
+                commit_trial(dc, cs, c, u <= t.prob ? 1 : 0);
+            }
+            if (ctl->recs) {
+                mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + s - 1];
+                rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
+                rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
+                for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
+            }
+        }
+        __syncthreads();
+    }
+    if (last) return;
+    if (threadIdx.x == 0) {
+        propose_move(dc, cs, rs, c);
+        if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
+    }
+    __syncthreads();
+    build_phase_tables(dc, cs, c);
+}
+__global__ void k_advance(BatchCtl* ctl, int g) { ctl->rng.step += (unsigned long long)g; ctl->rec_base += g; }

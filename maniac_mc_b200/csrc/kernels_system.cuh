@@ -1,0 +1,250 @@
+// kernels_system.cuh -- single-point energy ComputeSystemEnergy (energy_utils.f90:18-35) on the device:
+// total real-space pair energy (i<j, intra-molecular pairs excluded, Q13), full structure factor
+// S(k) + reciprocal energy, Ewald self term and intra-residue correction.  Runs once per chain at
+// start-up (and in tests as the consistency check of the tracked energies).
+#pragma once
+#include "common.cuh"
+
+#define SYS_THREADS 256
+#define SK_CHUNK 32
+
+struct SysScratch {
+    double *x, *y, *z, *q;   // [N] flat atoms of one chain: framework then guest slots
+    int *type, *mol;         // mol = -1 for an empty guest slot
+    int *tile_min, *tile_max;  // molecule-id range per tile of SYS_THREADS atoms
+    int n, n_tiles;
+    double* part;            // partial sums
+    double2* sk_part;        // [n_super][nk]
+    int n_super;
+    double* result;          // [8]
+};
+
+__global__ void k_sys_gather(DevConst dc, ChainState cs, SysScratch ss, int c, int n_fw_mols) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= ss.n) return;
+    int mol = -1;
+    if (j < dc.n_fw) {
+        ss.x[j] = dc.fx[j]; ss.y[j] = dc.fy[j]; ss.z[j] = dc.fz[j]; ss.q[j] = dc.fq[j]; ss.type[j] = dc.ftype[j];
+        mol = dc.fmol[j];
+    } else {
+        const int g = j - dc.n_fw;
+        int r = 0;
+        for (int i = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (g >= dc.g_atom_base[rr]) r = rr; }
+        const int na = dc.natoms[r];
+        const int m = (g - dc.g_atom_base[r]) / na, a = (g - dc.g_atom_base[r]) % na;
+        const size_t ia = (size_t)c * dc.g_atoms + g;
+        ss.x[j] = cs.gx[ia]; ss.y[j] = cs.gy[ia]; ss.z[j] = cs.gz[ia]; ss.q[j] = dc.q[r][a]; ss.type[j] = dc.type[r][a];
+        if (m < cs.count[c * MMC_MAX_RES + r]) mol = n_fw_mols + dc.g_mol_base[r] + m;
+    }
+    ss.mol[j] = mol;
+    if (mol >= 0) { atomicMin(&ss.tile_min[j / SYS_THREADS], mol); atomicMax(&ss.tile_max[j / SYS_THREADS], mol); }
+}
+
+// LennardJonesEnergy energy_utils.f90:192-218 and CoulombEnergy :225-256 (with the optional table branch)
+__device__ __forceinline__ void sys_pair_eval(const DevConst& dc, double r, double2 lj, double qi, double qj, double& e_lj, double& e_c) {
+    if (r < dc.rc) {
+        double r6, r12;
+        if (dc.use_table) {
+            const double s2 = lj.x * lj.x, s6 = s2 * s2 * s2;
+            r6 = s6 / table_lookup(dc.tab_r6, dc.tab_dx, r);
+            r12 = s6 * s6 / table_lookup(dc.tab_r12, dc.tab_dx, r);
+        } else { const double sr = lj.x / r, sr2 = sr * sr; r6 = sr2 * sr2 * sr2; r12 = r6 * r6; }
+        e_lj += lj.y * (r12 - r6);
+    }
+    if (fabs(qi) >= MMC_ERR && fabs(qj) >= MMC_ERR && r >= MMC_ERR) {
+        if (dc.use_table) e_c += qi * qj * table_lookup(dc.tab_erfc, dc.tab_dx, r);
+        else e_c += qi * qj * erfc(dc.alpha * r) / r;
+    }
+}
+
+// grid = (n_tiles, n_tiles); block (bi, bj) with bj >= bi evaluates tile_i x tile_j, pair (i, j) kept if j > i
+__global__ void __launch_bounds__(SYS_THREADS) k_sys_pair(DevConst dc, SysScratch ss) {
+    __shared__ double sx[SYS_THREADS], sy[SYS_THREADS], sz[SYS_THREADS], sq[SYS_THREADS];
+    __shared__ int st[SYS_THREADS], smol[SYS_THREADS];
+    __shared__ double red[2 * SYS_THREADS / 32];
+    const int bi = blockIdx.x, bj = blockIdx.y;
+    double acc[2] = {0.0, 0.0};
+    double* out = ss.part + ((size_t)bi * ss.n_tiles + bj) * 2;
+    bool skip = bj < bi;
+    if (!skip) {
+        const int a0 = ss.tile_min[bi], a1 = ss.tile_max[bi], b0 = ss.tile_min[bj], b1 = ss.tile_max[bj];
+        if (a1 < 0 || b1 < 0) skip = true;                          // a tile of empty slots
+        else if (a0 == a1 && b0 == b1 && a0 == b0) skip = true;     // both inside one molecule (framework)
+    }
+    if (skip) { if (threadIdx.x == 0) { out[0] = 0.0; out[1] = 0.0; } return; }
+    const int j0 = bj * SYS_THREADS + threadIdx.x;
+    if (j0 < ss.n) { sx[threadIdx.x] = ss.x[j0]; sy[threadIdx.x] = ss.y[j0]; sz[threadIdx.x] = ss.z[j0]; sq[threadIdx.x] = ss.q[j0];
+                     st[threadIdx.x] = ss.type[j0]; smol[threadIdx.x] = ss.mol[j0]; }
+    else smol[threadIdx.x] = -1;
+    __syncthreads();
+    const int i = bi * SYS_THREADS + threadIdx.x;
+    if (i < ss.n && ss.mol[i] >= 0) {
+        const double xi = ss.x[i], yi = ss.y[i], zi = ss.z[i], qi = ss.q[i];
+        const int ti = ss.type[i], mi = ss.mol[i];
+        for (int jj = 0; jj < SYS_THREADS; jj++) {
+            const int j = bj * SYS_THREADS + jj;
+            if (j <= i || smol[jj] < 0 || smol[jj] == mi) continue;
+            const double dx = min_image(sx[jj] - xi, dc.L[0], dc.invL[0]);
+            const double dy = min_image(sy[jj] - yi, dc.L[1], dc.invL[1]);
+            const double dz = min_image(sz[jj] - zi, dc.L[2], dc.invL[2]);
+            const double r = sqrt(dx * dx + dy * dy + dz * dz);
+            sys_pair_eval(dc, r, dc.lj[ti * dc.ntypes + st[jj]], qi, sq[jj], acc[0], acc[1]);
+        }
+    }
+    block_sum<2, SYS_THREADS>(acc, red);
+    if (threadIdx.x == 0) { out[0] = acc[0]; out[1] = acc[1]; }
+}
+
+// deterministic sum of n rows of `width` doubles -> out[width]; one block
+__global__ void __launch_bounds__(SYS_THREADS) k_sum_rows(const double* part, long long n, int width, double* out, double scale0, double scale1) {
+    __shared__ double red[2 * SYS_THREADS / 32];
+    double v[2] = {0.0, 0.0};
+    for (long long i = threadIdx.x; i < n; i += SYS_THREADS) { v[0] += part[i * width]; if (width > 1) v[1] += part[i * width + 1]; }
+    block_sum<2, SYS_THREADS>(v, red);
+    if (threadIdx.x == 0) { out[0] = v[0] * scale0; if (width > 1) out[1] = v[1] * scale1; }
+}
+
+// Full structure factor (ComputeAllFourierTerms ewald_phase.f90:340 + ComputeRecipAmplitude ewald_energy.f90:40):
+// grid = (n_k_tiles, n_super); each block walks its share of atom chunks, builds the chunk's 1-D phase
+// tables in shared memory (direct cos/sin(k*theta) as ComputePhaseFactors1D) and accumulates
+// sum_atoms q * phix(kx) phiy(ky) phiz(kz) for its k-vectors.
+__global__ void __launch_bounds__(RECIP_THREADS) k_sys_sk(DevConst dc, SysScratch ss, int chunk) {
+    extern __shared__ double2 s_tab[];  // [chunk][3][kstride]
+    const int ks = dc.kstride;
+    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
+    int4 kv = make_int4(0, 0, 0, 0);
+    if (ik < dc.nk) kv = dc.kvec[ik];
+    double are = 0.0, aim = 0.0;
+    const int n_chunks = (ss.n + chunk - 1) / chunk;
+    const int per = (n_chunks + gridDim.y - 1) / gridDim.y;
+    for (int ch = blockIdx.y * per; ch < min(n_chunks, (int)(blockIdx.y + 1) * per); ch++) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < chunk * 3 * ks; i += blockDim.x) {
+            const int k = i % ks, ax = (i / ks) % 3, a = i / (3 * ks);
+            const int j = ch * chunk + a;
+            double2 v = make_double2(0.0, 0.0);
+            if (j < ss.n && k <= dc.kmax[ax] && ss.mol[j] >= 0) {
+                const double pos = ax == 0 ? ss.x[j] : ax == 1 ? ss.y[j] : ss.z[j];
+                const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
+                double s, co; sincos((double)k * theta, &s, &co);
+                v = make_double2(co, s);
+            }
+            s_tab[i] = v;
+        }
+        __syncthreads();
+        if (ik < dc.nk) {
+            for (int a = 0; a < chunk; a++) {
+                const int j = ch * chunk + a;
+                if (j >= ss.n) break;
+                if (ss.mol[j] < 0) continue;
+                const double2* tb = s_tab + (size_t)a * 3 * ks;
+                double2 px = tb[kv.x];
+                double2 py = tb[ks + abs(kv.y)]; if (kv.y < 0) py.y = -py.y;
+                double2 pz = tb[2 * ks + abs(kv.z)]; if (kv.z < 0) pz.y = -pz.y;
+                const double2 pxy = make_double2(px.x * py.x - px.y * py.y, px.x * py.y + px.y * py.x);
+                const double2 p = make_double2(pxy.x * pz.x - pxy.y * pz.y, pxy.x * pz.y + pxy.y * pz.x);
+                const double q = ss.q[j];
+                are += q * p.x; aim += q * p.y;
+            }
+        }
+    }
+    if (ik < dc.nk) ss.sk_part[(size_t)blockIdx.y * dc.nk + ik] = make_double2(are, aim);
+}
+
+// sums the super-chunk partials in order -> S(k); energy partial per block (ComputeReciprocalEnergy
+// ewald_energy.f90:105-148); stores S(k) as the tracked A(k) (init_sk=full) or zeros it (Q1 default)
+__global__ void __launch_bounds__(RECIP_THREADS) k_sys_sk_reduce(DevConst dc, ChainState cs, SysScratch ss, int c, int store) {
+    __shared__ double red[2 * RECIP_THREADS / 32];
+    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
+    double v[2] = {0.0, 0.0};
+    if (ik < dc.nk) {
+        double are = 0.0, aim = 0.0;
+        for (int s = 0; s < ss.n_super; s++) { const double2 p = ss.sk_part[(size_t)s * dc.nk + ik]; are += p.x; aim += p.y; }
+        v[0] = dc.fw[ik] * (are * are + aim * aim);
+        double2* A = cs.A + ((size_t)c * 2 + cs.cur[c]) * dc.nk;
+        A[ik] = store ? make_double2(are, aim) : make_double2(0.0, 0.0);
+    }
+    block_sum<2, RECIP_THREADS>(v, red);
+    if (threadIdx.x == 0) { ss.part[blockIdx.x * 2] = v[0]; ss.part[blockIdx.x * 2 + 1] = 0.0; }
+}
+
+// ComputeEwaldSelf energy_utils.f90:307-330 (framework part: -alpha/sqrt(pi) sum q^2 over all inactive
+// atoms) and ComputeTotalIntraResidueCoulombEnergy :55-81 (active residues only).  One block.
+__global__ void __launch_bounds__(SYS_THREADS) k_sys_self_intra(DevConst dc, ChainState cs, int c, double* out /* [2] */) {
+    __shared__ double red[2 * SYS_THREADS / 32];
+    double v[2] = {0.0, 0.0};
+    const double f = dc.alpha / sqrt(MMC_PI);
+    for (int j = threadIdx.x; j < dc.n_fw; j += SYS_THREADS) { const double q = dc.fq[j]; if (fabs(q) >= MMC_ERR) v[0] -= f * (q * q); }
+    for (int i = 0; i < dc.n_active; i++) {
+        const int r = dc.active_list[i], nat = dc.natoms[r], cnt = cs.count[c * MMC_MAX_RES + r];
+        for (int m = threadIdx.x; m < cnt; m += SYS_THREADS) {
+            double p[MMC_MAX_MOL_ATOMS][3];
+            for (int a = 0; a < nat; a++) {
+                const size_t ia = (size_t)c * dc.g_atoms + dc.g_atom_base[r] + (size_t)m * nat + a;
+                p[a][0] = cs.gx[ia]; p[a][1] = cs.gy[ia]; p[a][2] = cs.gz[ia];
+            }
+            double e = 0.0;
+            for (int a1 = 0; a1 < nat - 1; a1++)
+                for (int a2 = a1 + 1; a2 < nat; a2++) {
+                    const double dx = min_image(p[a2][0] - p[a1][0], dc.L[0], dc.invL[0]);
+                    const double dy = min_image(p[a2][1] - p[a1][1], dc.L[1], dc.invL[1]);
+                    const double dz = min_image(p[a2][2] - p[a1][2], dc.L[2], dc.invL[2]);
+                    const double rr = sqrt(dx * dx + dy * dy + dz * dz);
+                    if (rr > MMC_ERR) e += dc.q[r][a1] * dc.q[r][a2] * (erfc(dc.alpha * rr) - 1.0) / rr;
+                }
+            v[1] += e * dc.coul_const;
+        }
+    }
+    block_sum<2, SYS_THREADS>(v, red);
+    if (threadIdx.x == 0) {
+        double self = v[0] * dc.coul_const;
+        for (int i = 0; i < dc.n_active; i++) { const int r = dc.active_list[i]; self += dc.self_e[r] * cs.count[c * MMC_MAX_RES + r]; }
+        out[0] = self; out[1] = v[1];
+    }
+}
+
+// W(k) = exp(-k^2 / 4 alpha^2) / k^2 (ComputeReciprocalWeights ewald_kvectors.f90:225-246) times the
+// symmetry form factor (ComputeSymmetryFormFactor :167); k^2 from ComputeCartesianKSquared :134
+__global__ void k_init_weights(DevConst dc, double* fw, double* w_only) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= dc.nk) return;
+    const int4 kv = dc.kvec[i];
+    const double vx = (double)kv.x * (MMC_TWOPI * dc.invL[0]), vy = (double)kv.y * (MMC_TWOPI * dc.invL[1]),
+                 vz = (double)kv.z * (MMC_TWOPI * dc.invL[2]);
+    const double k2 = vx * vx + vy * vy + vz * vz;
+    const double w = exp(-k2 / (4.0 * (dc.alpha * dc.alpha))) / k2;
+    w_only[i] = w;
+    fw[i] = (kv.x == 0 ? 1.0 : 2.0) * w;
+}
+
+// tabulated_utils.f90:19-83 : tables of erfc(alpha r)/r, r^6, r^12 on [0, rc], 5001 points
+__global__ void k_init_tables(double alpha, double rc, double* t_erfc, double* t_r6, double* t_r12) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > 5000) return;
+    const double dx = rc / 5000.0, r = i * dx;
+    if (r < MMC_ERR) { t_erfc[i] = 2.0 * alpha / sqrt(MMC_PI); t_r6[i] = 0.0; t_r12[i] = 0.0; }
+    else {
+        t_erfc[i] = erfc(alpha * r) / r;
+        const double r2 = r * r, r6 = r2 * r2 * r2;
+        t_r6[i] = r6; t_r12[i] = r6 * r6;
+    }
+}
+__global__ void k_table_lookup(DevConst dc, int which, const double* r, int n, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = table_lookup(which == 0 ? dc.tab_erfc : which == 1 ? dc.tab_r6 : dc.tab_r12, dc.tab_dx, r[i]);
+}
+__global__ void k_erfc_test(const double* x, int n, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = mmc_erfc(x[i]);
+}
+
+// FP64 peak: 8 independent DFMA chains per thread, register resident
+__global__ void k_fp64_peak(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, b = 1e-7;
+    for (int i = 0; i < iters; i++) {
+        a0 = fma(a0, m, b); a1 = fma(a1, m, b); a2 = fma(a2, m, b); a3 = fma(a3, m, b);
+        a4 = fma(a4, m, b); a5 = fma(a5, m, b); a6 = fma(a6, m, b); a7 = fma(a7, m, b);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}

@@ -1,0 +1,695 @@
+// maniac_gpu.cu -- handle management and the C ABI of libmaniacgpu.so (include/maniac_gpu.h).
+// Host code here only packs descriptions, owns device buffers, and enqueues kernels; every energy
+// is computed on the device.  There is no CPU fallback.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels_move.cuh"
+#include "kernels_system.cuh"
+
+static thread_local std::string g_err;
+static int fail(const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_err = buf;
+    return 1;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define CHECK_CHAIN(h, c) do { if (!(h)) return fail("null handle"); if ((c) < 0 || (c) >= (h)->dc.n_chains) return fail("chain %d out of range [0,%d)", (c), (h)->dc.n_chains); } while (0)
+
+struct mmc_handle {
+    DevConst dc;
+    ChainState cs;
+    SysScratch ss;
+    cudaStream_t stream = nullptr;
+    int device = 0;
+    int init_sk = 0;
+    int n_fw_mols = 0;
+    int sk_chunk = SK_CHUNK;
+    size_t recip_smem = 0, sk_smem = 0;
+    std::vector<void*> allocs;
+    std::vector<int> h_res_is_fw;          // per residue: 1 = inactive (framework)
+    std::vector<int> h_kx, h_ky, h_kz;
+    double* d_w = nullptr;                 // W(k) without the form factor (mmc_get_kvectors)
+    double* d_out = nullptr;               // 16 doubles of results
+    double* h_out = nullptr;               // pinned mirror
+    void* h_stage = nullptr;               // pinned staging for state transfers
+    size_t h_stage_bytes = 0;
+    double* d_tape = nullptr; size_t tape_cap = 0;
+    mmc_move_record* d_recs = nullptr; size_t recs_cap = 0;
+    long long* h_tape_pos = nullptr;
+    // cached CUDA graph of one batched step
+    cudaGraphExec_t graph = nullptr; int graph_steps = 0;
+    BatchCtl* d_ctl = nullptr;
+    std::vector<int> h_count;              // host mirror of count[C][MMC_MAX_RES]
+    int pending_kind = 0, pending_res = 0;
+    int64_t launches = 0;
+    unsigned long long steps_done = 0;     // Philox step counter across batches
+    int pending_chain = -1;
+};
+
+template <typename T>
+static cudaError_t dalloc(mmc_handle* h, T** p, size_t n) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, (n ? n : 1) * sizeof(T));
+    if (e == cudaSuccess) { h->allocs.push_back(q); e = cudaMemsetAsync(q, 0, (n ? n : 1) * sizeof(T), h->stream); }
+    *p = (T*)q;
+    return e;
+}
+
+extern "C" const char* mmc_last_error(void) { return g_err.c_str(); }
+
+// ComputeEwaldParameters / ComputeFourierIndices, prepare_utils.f90:169-214
+static bool valid_k(int kx, int ky, int kz, const int kmax[3]) {
+    const double a = (double)kx / (double)kmax[0], b = (double)ky / (double)kmax[1], c = (double)kz / (double)kmax[2];
+    const double k2 = a * a + b * b + c * c;
+    return std::fabs(k2) >= MMC_ERR && k2 <= 1.0;  // CheckValidReciprocalVector ewald_kvectors.f90:199
+}
+extern "C" int mmc_ewald_setup(double cutoff, double tolerance, const double box_len[3], double* alpha, int kmax[3], int* nk) {
+    if (cutoff <= 0 || !box_len || !alpha || !kmax || !nk) return fail("mmc_ewald_setup: bad arguments");
+    const double tol = std::fmin(std::fabs(tolerance), 0.5);
+    const double s = std::sqrt(std::fabs(std::log(tol * cutoff)));
+    const double a = std::sqrt(std::fabs(std::log(tol * cutoff * s))) / cutoff;
+    const double p = std::sqrt(-std::log(tol * cutoff * (2.0 * s * a) * (2.0 * s * a)));
+    for (int d = 0; d < 3; d++) kmax[d] = (int)std::lround(0.25 + box_len[d] * a * p / MMC_PI);
+    int n = 0;
+    for (int kx = 0; kx <= kmax[0]; kx++)
+        for (int ky = -kmax[1]; ky <= kmax[1]; ky++)
+            for (int kz = -kmax[2]; kz <= kmax[2]; kz++)
+                if (!(kx == 0 && ky == 0 && kz == 0) && valid_k(kx, ky, kz, kmax)) n++;
+    *alpha = a; *nk = n;
+    return 0;
+}
+
+extern "C" void mmc_destroy(mmc_t* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->graph) cudaGraphExecDestroy(h->graph);
+    for (void* p : h->allocs) cudaFree(p);
+    if (h->d_tape) cudaFree(h->d_tape);
+    if (h->d_recs) cudaFree(h->d_recs);
+    if (h->h_out) cudaFreeHost(h->h_out);
+    if (h->h_stage) cudaFreeHost(h->h_stage);
+    if (h->h_tape_pos) cudaFreeHost(h->h_tape_pos);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+static int ensure_stage(mmc_handle* h, size_t bytes) {
+    if (bytes <= h->h_stage_bytes) return 0;
+    if (h->h_stage) cudaFreeHost(h->h_stage);
+    h->h_stage = nullptr; h->h_stage_bytes = 0;
+    CK(cudaMallocHost(&h->h_stage, bytes));
+    h->h_stage_bytes = bytes;
+    return 0;
+}
+
+// uploads guests of one chain from packed (residue, molecule[, atom]) arrays that also contain the
+// inactive residues (their entries are skipped)
+static int upload_chain(mmc_handle* h, int c, const int* count, const double* com, const double* offsets) {
+    const DevConst& dc = h->dc;
+    const size_t nb = ((size_t)dc.g_mols * 3 + (size_t)dc.g_atoms * 6) * sizeof(double) + MMC_MAX_RES * sizeof(int);
+    if (ensure_stage(h, nb)) return 1;
+    CK(cudaStreamSynchronize(h->stream));
+    double* s_com = (double*)h->h_stage; double* s_off = s_com + (size_t)dc.g_mols * 3;
+    double* s_x = s_off + (size_t)dc.g_atoms * 3; double* s_y = s_x + dc.g_atoms; double* s_z = s_y + dc.g_atoms;
+    int* s_cnt = (int*)(s_z + dc.g_atoms);
+    memset(h->h_stage, 0, nb);
+    size_t mo = 0, ao = 0;
+    for (int r = 0; r < dc.nres; r++) {
+        const int na = dc.natoms[r], n = count[r];
+        if (dc.is_active[r]) {
+            if (n > dc.cap[r]) return fail("residue %d: count %d exceeds capacity %d", r, n, dc.cap[r]);
+            s_cnt[r] = n;
+            for (int m = 0; m < n; m++) {
+                const double* cm = com + (mo + m) * 3;
+                for (int d = 0; d < 3; d++) s_com[((size_t)dc.g_mol_base[r] + m) * 3 + d] = cm[d];
+                for (int a = 0; a < na; a++) {
+                    const double* of = offsets + (ao + (size_t)m * na + a) * 3;
+                    const size_t ia = dc.g_atom_base[r] + (size_t)m * na + a;
+                    for (int d = 0; d < 3; d++) s_off[ia * 3 + d] = of[d];
+                    s_x[ia] = cm[0] + of[0]; s_y[ia] = cm[1] + of[1]; s_z[ia] = cm[2] + of[2];
+                }
+            }
+        }
+        mo += n; ao += (size_t)n * na;
+    }
+    cudaStream_t st = h->stream;
+    CK(cudaMemcpyAsync(h->cs.gcom + (size_t)c * dc.g_mols * 3, s_com, (size_t)dc.g_mols * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.goff + (size_t)c * dc.g_atoms * 3, s_off, (size_t)dc.g_atoms * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.gx + (size_t)c * dc.g_atoms, s_x, (size_t)dc.g_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.gy + (size_t)c * dc.g_atoms, s_y, (size_t)dc.g_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.gz + (size_t)c * dc.g_atoms, s_z, (size_t)dc.g_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.count + (size_t)c * MMC_MAX_RES, s_cnt, MMC_MAX_RES * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    if (h->h_count.size() != (size_t)dc.n_chains * MMC_MAX_RES) h->h_count.assign((size_t)dc.n_chains * MMC_MAX_RES, 0);
+    for (int r = 0; r < MMC_MAX_RES; r++) h->h_count[(size_t)c * MMC_MAX_RES + r] = s_cnt[r];
+    return 0;
+}
+
+extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
+    if (!out || !d) return fail("mmc_init: null argument");
+    *out = nullptr;
+    if (d->nres < 1 || d->nres > MMC_MAX_RES) return fail("mmc_init: nres=%d outside [1,%d]", d->nres, MMC_MAX_RES);
+    if (d->n_chains < 1) return fail("mmc_init: n_chains must be >= 1");
+    for (int k = 0; k < 3; k++) {
+        if (!(d->box_len[k] > 0.0)) return fail("mmc_init: box_len[%d] must be positive (orthorhombic boxes only)", k);
+        if (d->kmax[k] < 1) return fail("mmc_init: kmax[%d] must be >= 1", k);
+    }
+    if (!(d->alpha > 0.0) || !(d->cutoff > 0.0) || !(d->temperature > 0.0)) return fail("mmc_init: alpha, cutoff and temperature must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("mmc_init: no CUDA device available (this library has no CPU fallback)");
+    if (d->device < 0 || d->device >= ndev) return fail("mmc_init: device %d out of range (%d devices)", d->device, ndev);
+    CK(cudaSetDevice(d->device));
+    mmc_handle* h = new mmc_handle();
+    h->device = d->device; h->init_sk = d->init_sk;
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return fail("cudaStreamCreate failed"); }
+    DevConst& dc = h->dc;
+    memset(&dc, 0, sizeof dc);
+    dc.nres = d->nres; dc.ntypes = d->ntypes; dc.n_chains = d->n_chains;
+    dc.deletion_mode = d->deletion_mode; dc.use_table = d->use_table;
+    dc.alpha = d->alpha; dc.rc = d->cutoff;
+    dc.coul_const = MMC_EPS0_INV_eVA / MMC_KB_eVK;
+    dc.p_translation = d->p_translation; dc.p_rotation = d->p_rotation;
+    dc.volume = d->box_len[0] * d->box_len[1] * d->box_len[2];
+    dc.recip_const = MMC_EPS0_INV_eVA / MMC_KB_eVK * MMC_TWOPI / dc.volume;
+    int kmaxmax = 0;
+    for (int k = 0; k < 3; k++) {
+        dc.lo[k] = d->box_lo[k]; dc.L[k] = d->box_len[k]; dc.invL[k] = 1.0 / d->box_len[k]; dc.kmax[k] = d->kmax[k];
+        if (d->kmax[k] > kmaxmax) kmaxmax = d->kmax[k];
+    }
+    dc.kstride = kmaxmax + 1;
+#define BAIL(...) do { fail(__VA_ARGS__); std::string keep_ = g_err; mmc_destroy(h); g_err = keep_; return 1; } while (0)
+#define CKB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) BAIL("%s failed: %s", #call, cudaGetErrorString(e_)); } while (0)
+    // residues
+    int g_atoms = 0, g_mols = 0; size_t n_fw = 0; int n_fw_mols = 0;
+    for (int r = 0; r < d->nres; r++) {
+        dc.natoms[r] = d->natoms[r]; dc.is_active[r] = d->is_active[r] == 1;
+        if (dc.is_active[r]) {
+            if (d->natoms[r] > MMC_MAX_MOL_ATOMS) BAIL("active residue %d has %d atoms (> MMC_MAX_MOL_ATOMS=%d)", r, d->natoms[r], MMC_MAX_MOL_ATOMS);
+            int cap = d->capacity ? d->capacity[r] : d->count[r];
+            if (cap < d->count[r]) cap = d->count[r];
+            if (cap < 1) cap = 1;
+            dc.cap[r] = cap;
+            dc.active_list[dc.n_active++] = r;
+            dc.g_atom_base[r] = g_atoms; dc.g_mol_base[r] = g_mols;
+            g_atoms += cap * d->natoms[r]; g_mols += cap;
+            double se = 0.0;  // ComputeEwaldSelfInteractionSingleMol ewald_energy.f90:308-336 (constant per type)
+            for (int a = 0; a < d->natoms[r]; a++) {
+                const double q = d->charges[(size_t)r * d->max_atoms + a];
+                const int ty = d->types[(size_t)r * d->max_atoms + a];
+                if (ty < 1 || ty > d->ntypes) BAIL("residue %d atom %d: type %d outside [1,%d]", r, a, ty, d->ntypes);
+                dc.q[r][a] = q; dc.type[r][a] = ty - 1;
+                if (std::fabs(q) < MMC_ERR) continue;
+                se = se - d->alpha / std::sqrt(MMC_PI) * (q * q);
+            }
+            dc.self_e[r] = se * dc.coul_const;
+        } else {
+            dc.cap[r] = d->count[r];
+            n_fw += (size_t)d->count[r] * d->natoms[r]; n_fw_mols += d->count[r];
+        }
+    }
+    dc.g_atoms = g_atoms > 0 ? g_atoms : 1; dc.g_mols = g_mols > 0 ? g_mols : 1; dc.n_fw = (int)n_fw; h->n_fw_mols = n_fw_mols;
+    dc.n_pair_tiles = (int)((n_fw + dc.g_atoms + PAIR_THREADS - 1) / PAIR_THREADS);
+    // framework SoA (absolute positions com + offset, as ComputeDistance forms them, geometry_utils.f90:379-382)
+    {
+        std::vector<double> fx(n_fw + 1), fy(n_fw + 1), fz(n_fw + 1), fq(n_fw + 1); std::vector<int> ft(n_fw + 1), fm(n_fw + 1);
+        size_t mo = 0, ao = 0, j = 0; int molid = 0;
+        for (int r = 0; r < d->nres; r++) {
+            const int na = d->natoms[r], n = d->count[r];
+            if (!dc.is_active[r])
+                for (int m = 0; m < n; m++, molid++)
+                    for (int a = 0; a < na; a++, j++) {
+                        const double* cm = d->com + (mo + m) * 3; const double* of = d->offsets + (ao + (size_t)m * na + a) * 3;
+                        fx[j] = cm[0] + of[0]; fy[j] = cm[1] + of[1]; fz[j] = cm[2] + of[2];
+                        fq[j] = d->charges[(size_t)r * d->max_atoms + a];
+                        const int ty = d->types[(size_t)r * d->max_atoms + a];
+                        if (ty < 1 || ty > d->ntypes) BAIL("residue %d atom %d: type %d outside [1,%d]", r, a, ty, d->ntypes);
+                        ft[j] = ty - 1; fm[j] = molid;
+                    }
+            mo += n; ao += (size_t)n * na;
+        }
+        double *px, *py, *pz, *pq; int *pt, *pm;
+        CKB(dalloc(h, &px, n_fw)); CKB(dalloc(h, &py, n_fw)); CKB(dalloc(h, &pz, n_fw)); CKB(dalloc(h, &pq, n_fw));
+        CKB(dalloc(h, &pt, n_fw)); CKB(dalloc(h, &pm, n_fw));
+        if (n_fw) {
+            CKB(cudaMemcpy(px, fx.data(), n_fw * 8, cudaMemcpyHostToDevice)); CKB(cudaMemcpy(py, fy.data(), n_fw * 8, cudaMemcpyHostToDevice));
+            CKB(cudaMemcpy(pz, fz.data(), n_fw * 8, cudaMemcpyHostToDevice)); CKB(cudaMemcpy(pq, fq.data(), n_fw * 8, cudaMemcpyHostToDevice));
+            CKB(cudaMemcpy(pt, ft.data(), n_fw * 4, cudaMemcpyHostToDevice)); CKB(cudaMemcpy(pm, fm.data(), n_fw * 4, cudaMemcpyHostToDevice));
+        }
+        dc.fx = px; dc.fy = py; dc.fz = pz; dc.fq = pq; dc.ftype = pt; dc.fmol = pm;
+    }
+    // LJ table by atom type: {sigma, 4*epsilon}
+    {
+        const size_t nt2 = (size_t)d->ntypes * d->ntypes;
+        std::vector<double2> lj(nt2);
+        for (size_t i = 0; i < nt2; i++) lj[i] = make_double2(d->sigma[i], 4.0 * d->epsilon[i]);
+        double2* p; CKB(dalloc(h, &p, nt2)); CKB(cudaMemcpy(p, lj.data(), nt2 * sizeof(double2), cudaMemcpyHostToDevice));
+        dc.lj = p;
+    }
+    // k-vector list, PrecomputeValidReciprocalVectors ewald_kvectors.f90:44-99 (kx outer, kz inner)
+    {
+        std::vector<int4> kv;
+        for (int kx = 0; kx <= dc.kmax[0]; kx++)
+            for (int ky = -dc.kmax[1]; ky <= dc.kmax[1]; ky++)
+                for (int kz = -dc.kmax[2]; kz <= dc.kmax[2]; kz++) {
+                    if (kx == 0 && ky == 0 && kz == 0) continue;
+                    if (!valid_k(kx, ky, kz, dc.kmax)) continue;
+                    kv.push_back(make_int4(kx, ky, kz, 0)); h->h_kx.push_back(kx); h->h_ky.push_back(ky); h->h_kz.push_back(kz);
+                }
+        dc.nk = (int)kv.size();
+        if (dc.nk == 0) BAIL("mmc_init: empty k-vector set");
+        dc.n_k_tiles = (dc.nk + RECIP_THREADS - 1) / RECIP_THREADS;
+        int4* p; CKB(dalloc(h, &p, kv.size())); CKB(cudaMemcpy(p, kv.data(), kv.size() * sizeof(int4), cudaMemcpyHostToDevice));
+        dc.kvec = p;
+        double *fw, *w; CKB(dalloc(h, &fw, dc.nk)); CKB(dalloc(h, &w, dc.nk));
+        dc.fw = fw;
+        k_init_weights<<<(dc.nk + 255) / 256, 256, 0, h->stream>>>(dc, fw, w); h->launches++;
+        h->d_w = w;
+    }
+    // tables (PrecomputeTable tabulated_utils.f90:10): built every run like the reference does
+    {
+        double *t0, *t1, *t2; CKB(dalloc(h, &t0, 5001)); CKB(dalloc(h, &t1, 5001)); CKB(dalloc(h, &t2, 5001));
+        k_init_tables<<<(5001 + 255) / 256, 256, 0, h->stream>>>(dc.alpha, dc.rc, t0, t1, t2); h->launches++;
+        dc.tab_erfc = t0; dc.tab_r6 = t1; dc.tab_r12 = t2; dc.tab_dx = dc.rc / 5000.0;
+    }
+    // per-chain state
+    ChainState& cs = h->cs;
+    const size_t C = dc.n_chains;
+    CKB(dalloc(h, &cs.count, C * MMC_MAX_RES));
+    CKB(dalloc(h, &cs.gx, C * dc.g_atoms)); CKB(dalloc(h, &cs.gy, C * dc.g_atoms)); CKB(dalloc(h, &cs.gz, C * dc.g_atoms));
+    CKB(dalloc(h, &cs.gcom, C * dc.g_mols * 3)); CKB(dalloc(h, &cs.goff, C * dc.g_atoms * 3));
+    CKB(dalloc(h, &cs.A, C * 2 * dc.nk)); CKB(dalloc(h, &cs.cur, C));
+    CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
+    CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
+    CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
+    CKB(dalloc(h, &cs.phase, C * 2 * 3 * MMC_MAX_MOL_ATOMS * dc.kstride));
+    CKB(dalloc(h, &cs.pair_part, C * dc.n_pair_tiles * 4)); CKB(dalloc(h, &cs.recip_part, C * dc.n_k_tiles * 2));
+    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.error_flag, 1));
+    CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
+    CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
+    CKB(cudaMallocHost((void**)&h->h_tape_pos, C * sizeof(long long)));
+    memset(h->h_tape_pos, 0, C * sizeof(long long));
+    {
+        std::vector<double> fug(C * MMC_MAX_RES, 0.0), tmp(C, d->temperature), ts(C, d->translation_step), rs(C, d->rotation_step);
+        for (size_t c = 0; c < C; c++) for (int r = 0; r < d->nres; r++) fug[c * MMC_MAX_RES + r] = d->fugacity ? d->fugacity[r] : 0.0;
+        CKB(cudaMemcpy(cs.fug, fug.data(), fug.size() * 8, cudaMemcpyHostToDevice));
+        CKB(cudaMemcpy(cs.temp, tmp.data(), C * 8, cudaMemcpyHostToDevice));
+        CKB(cudaMemcpy(cs.tstep, ts.data(), C * 8, cudaMemcpyHostToDevice));
+        CKB(cudaMemcpy(cs.rstep, rs.data(), C * 8, cudaMemcpyHostToDevice));
+    }
+    for (size_t c = 0; c < C; c++)
+        if (upload_chain(h, (int)c, d->count, d->com, d->offsets)) { std::string keep = g_err; mmc_destroy(h); g_err = keep; return 1; }
+    // scratch of the single-point energy
+    SysScratch& ss = h->ss;
+    memset(&ss, 0, sizeof ss);
+    ss.n = dc.n_fw + dc.g_atoms; ss.n_tiles = (ss.n + SYS_THREADS - 1) / SYS_THREADS;
+    CKB(dalloc(h, &ss.x, ss.n)); CKB(dalloc(h, &ss.y, ss.n)); CKB(dalloc(h, &ss.z, ss.n)); CKB(dalloc(h, &ss.q, ss.n));
+    CKB(dalloc(h, &ss.type, ss.n)); CKB(dalloc(h, &ss.mol, ss.n));
+    CKB(dalloc(h, &ss.tile_min, ss.n_tiles)); CKB(dalloc(h, &ss.tile_max, ss.n_tiles));
+    const size_t npart = std::max((size_t)ss.n_tiles * ss.n_tiles, (size_t)dc.n_k_tiles) * 2;
+    CKB(dalloc(h, &ss.part, npart));
+    h->sk_chunk = SK_CHUNK;
+    while (h->sk_chunk > 1 && (size_t)h->sk_chunk * 3 * dc.kstride * sizeof(double2) > 48 * 1024) h->sk_chunk /= 2;
+    h->sk_smem = (size_t)h->sk_chunk * 3 * dc.kstride * sizeof(double2);
+    const int n_chunks = (ss.n + h->sk_chunk - 1) / h->sk_chunk;
+    ss.n_super = n_chunks < 128 ? n_chunks : 128;
+    CKB(dalloc(h, &ss.sk_part, (size_t)ss.n_super * dc.nk));
+    CKB(dalloc(h, &ss.result, 8));
+    int max_nat = 1;
+    for (int i = 0; i < dc.n_active; i++) if (dc.natoms[dc.active_list[i]] > max_nat) max_nat = dc.natoms[dc.active_list[i]];
+    h->recip_smem = (size_t)2 * 3 * max_nat * dc.kstride * sizeof(double2);
+    if (h->recip_smem > 48 * 1024) {
+        if (h->recip_smem > 200 * 1024) BAIL("kmax=%d too large for the shared-memory phase tables", kmaxmax);
+        CKB(cudaFuncSetAttribute(k_recip_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->recip_smem));
+    }
+    CKB(cudaStreamSynchronize(h->stream));
+    CKB(cudaGetLastError());
+    *out = h;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" int mmc_num_kvectors(const mmc_t* h) { return h ? h->dc.nk : -1; }
+
+extern "C" int mmc_get_kvectors(mmc_t* h, int* kx, int* ky, int* kz, double* weight, double* form) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    const int n = h->dc.nk;
+    for (int i = 0; i < n; i++) {
+        if (kx) kx[i] = h->h_kx[i];
+        if (ky) ky[i] = h->h_ky[i];
+        if (kz) kz[i] = h->h_kz[i];
+        if (form) form[i] = h->h_kx[i] == 0 ? 1.0 : 2.0;  // ComputeSymmetryFormFactor ewald_kvectors.f90:167
+    }
+    if (weight) { CK(cudaStreamSynchronize(h->stream)); CK(cudaMemcpy(weight, h->d_w, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost)); }
+    return 0;
+}
+
+extern "C" int mmc_set_chain_params(mmc_t* h, int c, const double* fugacity, double temperature) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    if (!(temperature > 0.0)) return fail("temperature must be positive");
+    double f[MMC_MAX_RES] = {0};
+    for (int r = 0; r < h->dc.nres; r++) f[r] = fugacity ? fugacity[r] : 0.0;
+    CK(cudaStreamSynchronize(h->stream));
+    if (fugacity) CK(cudaMemcpy(h->cs.fug + (size_t)c * MMC_MAX_RES, f, sizeof f, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->cs.temp + c, &temperature, sizeof(double), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int mmc_set_step_sizes(mmc_t* h, int c, double tstep, double rstep) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(h->cs.tstep + c, &tstep, sizeof(double), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->cs.rstep + c, &rstep, sizeof(double), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int mmc_set_chain_state(mmc_t* h, int c, const int* count, const double* com, const double* offsets) {
+    CHECK_CHAIN(h, c);
+    if (!count || !com || !offsets) return fail("mmc_set_chain_state: null argument");
+    CK(cudaSetDevice(h->device));
+    return upload_chain(h, c, count, com, offsets);
+}
+
+// downloads one chain; inactive residues are not written (the host already has them): their
+// entries in the packed arrays are skipped over
+static int download_chain(mmc_handle* h, int c, int* count, double* com, double* offsets) {
+    const DevConst& dc = h->dc;
+    const size_t nb = ((size_t)dc.g_mols * 3 + (size_t)dc.g_atoms * 3) * sizeof(double) + MMC_MAX_RES * sizeof(int);
+    if (ensure_stage(h, nb)) return 1;
+    double* s_com = (double*)h->h_stage; double* s_off = s_com + (size_t)dc.g_mols * 3; int* s_cnt = (int*)(s_off + (size_t)dc.g_atoms * 3);
+    cudaStream_t st = h->stream;
+    CK(cudaMemcpyAsync(s_cnt, h->cs.count + (size_t)c * MMC_MAX_RES, MMC_MAX_RES * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (com) CK(cudaMemcpyAsync(s_com, h->cs.gcom + (size_t)c * dc.g_mols * 3, (size_t)dc.g_mols * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (offsets) CK(cudaMemcpyAsync(s_off, h->cs.goff + (size_t)c * dc.g_atoms * 3, (size_t)dc.g_atoms * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    size_t mo = 0, ao = 0;
+    for (int r = 0; r < dc.nres; r++) {
+        const int na = dc.natoms[r];
+        const int n = dc.is_active[r] ? s_cnt[r] : dc.cap[r];
+        if (count) count[r] = n;
+        if (dc.is_active[r]) {
+            if (com) memcpy(com + mo * 3, s_com + (size_t)dc.g_mol_base[r] * 3, (size_t)n * 3 * sizeof(double));
+            if (offsets) memcpy(offsets + ao * 3, s_off + (size_t)dc.g_atom_base[r] * 3, (size_t)n * na * 3 * sizeof(double));
+        }
+        mo += n; ao += (size_t)n * na;
+    }
+    return 0;
+}
+
+extern "C" int mmc_get_chain_state(mmc_t* h, int c, int* count, double* com, double* offsets) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    return download_chain(h, c, count, com, offsets);
+}
+
+extern "C" int mmc_sync_to_host(mmc_t* h, int c, int* count, double* com, double* offsets, double energies[MMC_NE]) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    if (download_chain(h, c, count, com, offsets)) return 1;
+    if (energies) CK(cudaMemcpy(energies, h->cs.energy + (size_t)c * MMC_NE, MMC_NE * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int mmc_get_sk(mmc_t* h, int c, double* sk) {
+    CHECK_CHAIN(h, c);
+    if (!sk) return fail("mmc_get_sk: null output");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    int cur = 0;
+    CK(cudaMemcpy(&cur, h->cs.cur + c, sizeof(int), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(sk, h->cs.A + ((size_t)c * 2 + cur) * h->dc.nk, (size_t)h->dc.nk * sizeof(double2), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void k_store_energy(ChainState cs, int c, const double* res /* lj, coul, recip, -, self, intra */) {
+    double* E = cs.energy + c * MMC_NE;
+    E[MMC_E_NONCOUL] = res[0]; E[MMC_E_COUL] = res[1]; E[MMC_E_RECIP] = res[2]; E[MMC_E_SELF] = res[4]; E[MMC_E_INTRA] = res[5];
+    // energy_utils.f90:32-33
+    E[MMC_E_TOTAL] = E[MMC_E_RECIP] + E[MMC_E_NONCOUL] + E[MMC_E_COUL] + E[MMC_E_SELF] + E[MMC_E_INTRA];
+}
+
+extern "C" int mmc_system_energy(mmc_t* h, int c, double out[MMC_NE]) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; SysScratch& ss = h->ss; cudaStream_t st = h->stream;
+    CK(cudaMemsetAsync(ss.tile_min, 0x7f, ss.n_tiles * sizeof(int), st));
+    CK(cudaMemsetAsync(ss.tile_max, 0xff, ss.n_tiles * sizeof(int), st));
+    k_sys_gather<<<(ss.n + 255) / 256, 256, 0, st>>>(dc, h->cs, ss, c, h->n_fw_mols);
+    k_sys_pair<<<dim3(ss.n_tiles, ss.n_tiles), SYS_THREADS, 0, st>>>(dc, ss);
+    k_sum_rows<<<1, SYS_THREADS, 0, st>>>(ss.part, (long long)ss.n_tiles * ss.n_tiles, 2, ss.result, 1.0, dc.coul_const);
+    k_sys_sk<<<dim3(dc.n_k_tiles, ss.n_super), RECIP_THREADS, h->sk_smem, st>>>(dc, ss, h->sk_chunk);
+    k_sys_sk_reduce<<<dc.n_k_tiles, RECIP_THREADS, 0, st>>>(dc, h->cs, ss, c, h->init_sk == MMC_INIT_SK_FULL);
+    k_sum_rows<<<1, SYS_THREADS, 0, st>>>(ss.part, dc.n_k_tiles, 2, ss.result + 2, dc.recip_const, 0.0);
+    k_sys_self_intra<<<1, SYS_THREADS, 0, st>>>(dc, h->cs, c, ss.result + 4);
+    k_store_energy<<<1, 1, 0, st>>>(h->cs, c, ss.result);
+    h->launches += 8;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(h->h_out, h->cs.energy + (size_t)c * MMC_NE, MMC_NE * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (out) memcpy(out, h->h_out, MMC_NE * sizeof(double));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+static void launch_sweeps(mmc_handle* h, cudaStream_t st, int chain0, int n_chains) {
+    k_pair_sweep<<<dim3(h->dc.n_pair_tiles, n_chains), PAIR_THREADS, 0, st>>>(h->dc, h->cs, chain0);
+    k_recip_sweep<<<dim3(h->dc.n_k_tiles, n_chains), RECIP_THREADS, h->recip_smem, st>>>(h->dc, h->cs, chain0);
+    h->launches += 2;
+}
+
+// ---- strict mode ------------------------------------------------------------------------------
+extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
+                                double old_e[MMC_NE], double new_e[MMC_NE]) {
+    CHECK_CHAIN(h, c);
+    const DevConst& dc = h->dc;
+    if (h->pending_chain >= 0) return fail("mmc_trial_energy: a trial is already pending on chain %d (call mmc_trial_commit first)", h->pending_chain);
+    if (kind < MMC_CREATION || kind > MMC_ROTATION) return fail("Unknown move_type %d", kind);  // monte_carlo_utils.f90:218
+    if (res < 0 || res >= dc.nres || !dc.is_active[res]) return fail("mmc_trial_energy: residue %d is not an active residue type", res);
+    const int cnt = h->h_count[(size_t)c * MMC_MAX_RES + res];
+    if (kind == MMC_CREATION) {
+        if (mol != cnt) return fail("mmc_trial_energy: creation must target slot %d (got %d)", cnt, mol);
+        if (mol >= dc.cap[res]) return fail("molecule index %d exceeds the maximum allowed = %d", mol + 1, dc.cap[res]);  // CheckMoleculeIndex
+    } else if (mol < 0 || mol >= cnt) return fail("mmc_trial_energy: molecule %d out of range [0,%d)", mol, cnt);
+    if (kind != MMC_DELETION && (!com_new || !offs_new)) return fail("mmc_trial_energy: proposed geometry missing");
+    CK(cudaSetDevice(h->device));
+    HostTrial ht;
+    memset(&ht, 0, sizeof ht);
+    ht.chain = c; ht.kind = kind; ht.res = res; ht.mol = mol;
+    if (kind != MMC_DELETION) {
+        for (int d = 0; d < 3; d++) ht.com[d] = com_new[d];
+        for (int a = 0; a < dc.natoms[res]; a++) for (int d = 0; d < 3; d++) ht.off[a][d] = offs_new[a * 3 + d];
+    }
+    cudaStream_t st = h->stream;
+    k_set_trial<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht);
+    launch_sweeps(h, st, c, 1);
+    k_finalize<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, c, h->d_out);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(h->h_out, h->d_out, (2 * MMC_NE + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (old_e) memcpy(old_e, h->h_out, MMC_NE * sizeof(double));
+    if (new_e) memcpy(new_e, h->h_out + MMC_NE, MMC_NE * sizeof(double));
+    h->pending_chain = c; h->pending_kind = kind; h->pending_res = res;
+    return 0;
+}
+
+extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
+    CHECK_CHAIN(h, c);
+    if (h->pending_chain != c) return fail("mmc_trial_commit: no trial pending on chain %d", c);
+    CK(cudaSetDevice(h->device));
+    k_commit<<<1, 32, 0, h->stream>>>(h->dc, h->cs, c, accept ? 1 : 0);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (accept) {
+        if (h->pending_kind == MMC_CREATION) h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res]++;
+        if (h->pending_kind == MMC_DELETION) h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res]--;
+    }
+    h->pending_chain = -1;
+    return 0;
+}
+
+// ---- batched mode -------------------------------------------------------------------------------
+#define GRAPH_CHUNK 128
+
+static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
+    const int C = h->dc.n_chains;
+    k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, 0, 1, 0);
+    h->launches++;
+    for (int s = 0; s < n; s++) {
+        launch_sweeps(h, st, 0, C);
+        k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, s + 1, 0, s == n - 1 ? 1 : 0);
+        h->launches++;
+    }
+    k_advance<<<1, 1, 0, st>>>(h->d_ctl, n);
+    h->launches++;
+}
+
+static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const double* d_tape, int64_t tape_stride,
+                         mmc_move_record* d_recs) {
+    cudaStream_t st = h->stream;
+    BatchCtl ctl;
+    ctl.rng.tape = d_tape; ctl.rng.tape_stride = tape_stride; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
+    ctl.recs = d_recs; ctl.rec_stride = n_steps; ctl.rec_base = 0;
+    CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, st));  // pageable source: copied before return
+    CK(cudaMemsetAsync(h->cs.tape_pos, 0, h->dc.n_chains * sizeof(long long), st));
+    CK(cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), st));
+    int64_t done = 0;
+    if (n_steps >= GRAPH_CHUNK) {
+        if (!h->graph) {
+            cudaGraph_t g;
+            const int64_t l0 = h->launches;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            enqueue_steps(h, st, GRAPH_CHUNK);
+            CK(cudaStreamEndCapture(st, &g));
+            h->launches = l0;
+            CK(cudaGraphInstantiate(&h->graph, g, 0));
+            CK(cudaGraphDestroy(g));
+            h->graph_steps = GRAPH_CHUNK;
+        }
+        while (n_steps - done >= GRAPH_CHUNK) {
+            CK(cudaGraphLaunch(h->graph, st));
+            h->launches += 3 * GRAPH_CHUNK + 2;
+            done += GRAPH_CHUNK;
+        }
+    }
+    if (n_steps - done > 0) enqueue_steps(h, st, (int)(n_steps - done));
+    CK(cudaGetLastError());
+    h->steps_done += (unsigned long long)n_steps;
+    h->pending_chain = -1;
+    return 0;
+}
+
+static int refresh_counts(mmc_handle* h) {
+    CK(cudaMemcpy(h->h_count.data(), h->cs.count, h->h_count.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    int flag = 0;
+    CK(cudaMemcpy(&flag, h->cs.error_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag) return fail("a creation move exceeded the slot capacity (NB_MAX_MOLECULE analogue); that move was skipped");
+    return 0;
+}
+
+extern "C" int mmc_run_batch_async(mmc_t* h, int64_t n_steps, uint64_t seed) {
+    if (!h) return fail("null handle");
+    if (n_steps < 1) return fail("mmc_run_batch: n_steps must be >= 1");
+    CK(cudaSetDevice(h->device));
+    return enqueue_batch(h, n_steps, seed, nullptr, 0, nullptr);
+}
+
+extern "C" int mmc_synchronize(mmc_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    return refresh_counts(h);
+}
+
+extern "C" int mmc_run_batch(mmc_t* h, int64_t n_steps, uint64_t seed, const double* tape, int64_t tape_stride,
+                             mmc_move_record* records, mmc_counters* counters) {
+    if (!h) return fail("null handle");
+    if (n_steps < 1) return fail("mmc_run_batch: n_steps must be >= 1");
+    CK(cudaSetDevice(h->device));
+    const size_t C = h->dc.n_chains;
+    cudaStream_t st = h->stream;
+    const double* d_tape = nullptr;
+    if (tape) {
+        if (tape_stride < 1) return fail("mmc_run_batch: tape_stride must be >= 1");
+        const size_t n = C * (size_t)tape_stride;
+        if (n > h->tape_cap) { if (h->d_tape) cudaFree(h->d_tape); h->d_tape = nullptr; h->tape_cap = 0; CK(cudaMalloc((void**)&h->d_tape, n * sizeof(double))); h->tape_cap = n; }
+        CK(cudaMemcpyAsync(h->d_tape, tape, n * sizeof(double), cudaMemcpyHostToDevice, st));
+        d_tape = h->d_tape;
+    }
+    mmc_move_record* d_recs = nullptr;
+    if (records) {
+        const size_t n = C * (size_t)n_steps;
+        if (n > h->recs_cap) { if (h->d_recs) cudaFree(h->d_recs); h->d_recs = nullptr; h->recs_cap = 0; CK(cudaMalloc((void**)&h->d_recs, n * sizeof(mmc_move_record))); h->recs_cap = n; }
+        d_recs = h->d_recs;
+    }
+    if (enqueue_batch(h, n_steps, seed, d_tape, tape_stride, d_recs)) return 1;
+    if (records) CK(cudaMemcpyAsync(records, d_recs, C * (size_t)n_steps * sizeof(mmc_move_record), cudaMemcpyDeviceToHost, st));
+    if (counters) CK(cudaMemcpyAsync(counters, h->cs.counters, C * sizeof(mmc_counters), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h->h_tape_pos, h->cs.tape_pos, C * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return refresh_counts(h);
+}
+
+extern "C" int64_t mmc_tape_used(mmc_t* h, int c) {
+    if (!h || c < 0 || c >= h->dc.n_chains) return -1;
+    return (int64_t)h->h_tape_pos[c];
+}
+
+// ---- debug / test entry points -----------------------------------------------------------------
+extern "C" int mmc_dbg_pair_singlemol(mmc_t* h, int c, int res, int mol, double* e_nc, double* e_c) {
+    // a deletion trial requests exactly one sweep at the current geometry with the molecule excluded
+    double o[MMC_NE], n[MMC_NE];
+    if (mmc_trial_energy(h, c, MMC_DELETION, res, mol, nullptr, nullptr, o, n)) return 1;
+    if (mmc_trial_commit(h, c, 0)) return 1;
+    if (e_nc) *e_nc = o[MMC_E_NONCOUL];
+    if (e_c) *e_c = o[MMC_E_COUL];
+    return 0;
+}
+extern "C" int mmc_dbg_self_singlemol(mmc_t* h, int res, double* e_self) {
+    if (!h) return fail("null handle");
+    if (res < 0 || res >= h->dc.nres || !h->dc.is_active[res]) return fail("residue %d is not active", res);
+    if (e_self) *e_self = h->dc.self_e[res];
+    return 0;
+}
+extern "C" int mmc_dbg_intra_singlemol(mmc_t* h, int c, int res, int mol, double* e_intra) {
+    double o[MMC_NE], n[MMC_NE];
+    if (mmc_trial_energy(h, c, MMC_DELETION, res, mol, nullptr, nullptr, o, n)) return 1;
+    if (mmc_trial_commit(h, c, 0)) return 1;
+    if (e_intra) *e_intra = o[MMC_E_INTRA];
+    return 0;
+}
+static int run_elementwise(mmc_handle* h, int which, const double* in, int n, double* out) {
+    if (!h || !in || !out || n < 1) return fail("bad arguments");
+    CK(cudaSetDevice(h->device));
+    double *di = nullptr, *dout = nullptr;
+    CK(cudaMalloc((void**)&di, n * sizeof(double))); CK(cudaMalloc((void**)&dout, n * sizeof(double)));
+    CK(cudaMemcpy(di, in, n * sizeof(double), cudaMemcpyHostToDevice));
+    if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(di, n, dout);
+    else k_table_lookup<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, which, di, n, dout);
+    h->launches++;
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e == cudaSuccess) e = cudaMemcpy(out, dout, n * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaFree(di); cudaFree(dout);
+    if (e != cudaSuccess) return fail("elementwise kernel failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+extern "C" int mmc_dbg_table_lookup(mmc_t* h, int which, const double* r, int n, double* out) {
+    if (which < 0 || which > 2) return fail("which must be 0, 1 or 2");
+    return run_elementwise(h, which, r, n, out);
+}
+extern "C" int mmc_dbg_erfc(mmc_t* h, const double* x, int n, double* out) { return run_elementwise(h, -1, x, n, out); }
+extern "C" void* mmc_stream(mmc_t* h) { return h ? (void*)h->stream : nullptr; }
+extern "C" int64_t mmc_launch_count(const mmc_t* h) { return h ? h->launches : -1; }
+
+extern "C" int mmc_measure_fp64_peak(int device, double* tflops) {
+    if (!tflops) return fail("null output");
+    CK(cudaSetDevice(device));
+    cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, device));
+    const int blocks = p.multiProcessorCount * 8, threads = 256, iters = 20000;
+    double* d = nullptr; CK(cudaMalloc((void**)&d, (size_t)blocks * threads * sizeof(double)));
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    k_fp64_peak<<<blocks, threads>>>(d, 1000);
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        CK(cudaEventRecord(e0));
+        k_fp64_peak<<<blocks, threads>>>(d, iters);
+        CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+        const double tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = best;
+    return 0;
+}

@@ -156,10 +156,12 @@ def read_lammps_data(path):
         elif section == "Atoms":
             # atom_style full: id mol type q x y z [ix iy iz]
             atoms.append((int(tok[0]), int(tok[1]), int(tok[2]), float(tok[3]), float(tok[4]), float(tok[5]), float(tok[6])))
+    if not all(h > l for l, h in zip(lo, hi)):
+        raise ValueError(f"{path}: missing or empty box bounds")
     if natoms == 0 or len(atoms) != natoms:
         raise ValueError(f"{path}: expected {natoms} atoms, found {len(atoms)}")
-    if not masses:
-        raise ValueError(f"{path}: missing Masses section")
+    if not masses or len(masses) < ntypes:
+        raise ValueError(f"{path}: missing or incomplete Masses section")
     a = np.array(sorted(atoms, key=lambda t: t[0]), dtype=np.float64)
     return dict(box_lo=np.array(lo), box_hi=np.array(hi), masses=masses, atoms=a, ntypes=ntypes)
 

@@ -1,0 +1,193 @@
+"""CPU tests: the oracle against the reference's own known answers, plus the consistency
+identities that stand in for the per-move golden vectors the reference does not have."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_system, rel_err
+from maniac_mc_b200.system import (E_COUL, E_INTRA, E_NONCOUL, E_RECIP, E_SELF, E_TOTAL, MMC_CREATION, MMC_DELETION,
+                                   MMC_ROTATION, MMC_TRANSLATION, ewald_setup)
+from oracle import oracle as orc
+
+KB_KCALMOL = 0.0019872041  # constants.f90:11 (PrintStatus converts K -> kcal/mol, output_utils.f90:181-189)
+KAT = json.load(open(os.path.join(GOLDEN, "reference_kat.json")))
+
+
+def status_line(e):
+    """TotEng, E_vdwl, E_coul, E_long exactly as PrintStatus assembles them (output_utils.f90:181-193)."""
+    k = e * KB_KCALMOL
+    tot = k[E_NONCOUL] + k[E_RECIP] + k[E_COUL] + k[E_SELF] + k[E_INTRA]
+    return tot, k[E_NONCOUL], k[E_COUL] + k[E_INTRA], k[E_RECIP] + k[E_SELF]
+
+
+def test_lj_gas_kat():
+    """tests/integration/energy/LJ-gas/run-test.sh: |TotEng - LAMMPS| <= 0.01 kcal/mol."""
+    e = orc.Oracle(load_system("lj_gas")).system_energy()
+    tot, vdwl, coul, long_ = status_line(e)
+    k = KAT["lj_gas"]
+    assert abs(tot - k["TotEng"]) <= k["tolerance"]
+    assert abs(vdwl - k["E_vdwl"]) <= 1e-6          # pure LJ: no unit-constant difference
+    assert abs(coul - k["E_coul"]) <= 0.03          # 332.1155 vs LAMMPS 332.06371 and no Coulomb cut-off (Q3)
+    assert abs(long_ - k["E_long"]) <= 0.03
+    # values of the survey's independent numpy probe
+    assert abs(tot - (-38.594630)) < 2e-6 and abs(coul - 49.727958) < 2e-6 and abs(long_ - (-87.915514)) < 2e-6
+
+
+def test_h2o_gas_kat():
+    """tests/integration/energy/H2O-gas/run-test.sh: |TotEng - (-32.822927)| <= 0.01 kcal/mol."""
+    e = orc.Oracle(load_system("h2o_gas")).system_energy()
+    tot = status_line(e)[0]
+    assert abs(tot - KAT["h2o_gas"]["TotEng"]) <= KAT["h2o_gas"]["tolerance"]
+    assert abs(tot - (-32.813812)) < 2e-6
+
+
+@pytest.mark.parametrize("name,alpha,kmax,nk", [("lj_gas", 0.162157, 6, 518), ("h2o_gas", 0.162157, 16, 8936),
+                                               ("zif8_h2o", 0.162157, 5, 297)])
+def test_ewald_setup(name, alpha, kmax, nk):
+    s = load_system(name)
+    a, k, n = orc.ewald_setup(s.cutoff, s.ewald_tolerance, s.box_len)
+    assert abs(a - alpha) < 1e-6 and k == [kmax] * 3 and n == nk
+    a2, k2 = ewald_setup(s.cutoff, s.ewald_tolerance, s.box_len)
+    assert a2 == a and k2 == k and s.num_kvectors == nk
+
+
+def test_kvector_order_and_weights():
+    o = orc.Oracle(load_system("lj_gas"))
+    kx, ky, kz, W, f = o.kvectors()
+    assert (kx[0], ky[0], kz[0]) == (0, -6, 0)           # kx outer, kz inner (ewald_kvectors.f90:60-62)
+    assert np.all(kx >= 0) and np.all(f[kx == 0] == 1.0) and np.all(f[kx > 0] == 2.0)
+    k2 = (2 * np.pi / 40.0) ** 2 * (kx.astype(float) ** 2 + ky ** 2 + kz ** 2)
+    np.testing.assert_allclose(W, np.exp(-k2 / (4 * 0.16215693560202488 ** 2)) / k2, rtol=1e-13)
+
+
+def test_philox_kat():
+    """Random123 known-answer vectors for Philox4x32-10."""
+    import ctypes as C
+    for ctr, key, exp in [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+                          ((0xffffffff,) * 4, (0xffffffff, 0xffffffff), (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+                          ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+                           (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]:
+        c = (C.c_uint32 * 4)(*ctr)
+        orc.lib().orc_philox(c, key[0], key[1])
+        assert tuple(c) == exp
+    u = [orc.philox_uniform(7, 3, s, d) for s in range(50) for d in range(12)]
+    assert 0.0 <= min(u) and max(u) < 1.0 and 0.4 < np.mean(u) < 0.6
+
+
+def test_table_lookup():
+    """LookupTabulated (tabulated_utils.f90:87): f(0) below 0, 0 at/after r_c, linear in between."""
+    from scipy.special import erfc
+    s = load_system("lj_gas"); o = orc.Oracle(s)
+    assert o.table_lookup(0, -1.0)[0] == pytest.approx(2 * s.alpha / np.sqrt(np.pi))
+    assert o.table_lookup(0, s.cutoff)[0] == 0.0 and o.table_lookup(1, s.cutoff + 1)[0] == 0.0
+    r = np.linspace(0.5, s.cutoff - 1e-3, 50)
+    np.testing.assert_allclose(o.table_lookup(0, r), erfc(s.alpha * r) / r, rtol=2e-5)
+    np.testing.assert_allclose(o.table_lookup(1, r), r ** 6, rtol=5e-4)
+    np.testing.assert_allclose(o.table_lookup(2, r), r ** 12, rtol=3e-3)
+
+
+@pytest.mark.parametrize("name", ["zif8_h2o", "h2o_ads"])
+def test_tracked_energy_equals_fresh(name):
+    """Identity (i) of SURVEY 8c: with the physical switches (init_sk=full, deletion=physical) the totals tracked
+    through AcceptMove / AcceptCreationMove / AcceptDeletionMove equal a fresh ComputeSystemEnergy."""
+    s = load_system(name, init_sk=1, deletion_mode=1)
+    o = orc.Oracle(s); o.system_energy()
+    recs = o.run(600, tape=np.random.default_rng(11).random(8000))
+    assert set(np.unique(recs["kind"])) >= {MMC_CREATION, MMC_DELETION, MMC_TRANSLATION, MMC_ROTATION}
+    cnt, com, off = o.state()
+    s2 = s.copy(); s2.count, s2.com, s2.offsets = cnt, com, off
+    o2 = orc.Oracle(s2); fresh = o2.system_energy()
+    assert rel_err(o.energy(), fresh) < 1e-9
+    np.testing.assert_allclose(o.sk(), o2.sk(), atol=1e-9)
+
+
+def test_old_call_returns_previous_new():
+    """Identity (ii): the 'old' call of ComputeRecipEnergySingleMol is a no-op update that re-sums the energy of the
+    current A(k), so after an accepted move it returns the previous 'new' value."""
+    s = load_system("h2o_ads", init_sk=1, deletion_mode=1)
+    o = orc.Oracle(s); o.system_energy()
+    recs = o.run(200, tape=np.random.default_rng(5).random(3000))
+    last_new = None
+    for r in recs:
+        if r["kind"] in (MMC_TRANSLATION, MMC_ROTATION):
+            if last_new is not None:
+                assert abs(r["old_e"][E_RECIP] - last_new) <= 1e-9 * max(1.0, abs(last_new))
+        if r["kind"] != 0:
+            last_new = r["new_e"][E_RECIP] if r["accepted"] else (r["old_e"][E_RECIP] if r["kind"] in (MMC_TRANSLATION, MMC_ROTATION) else last_new)
+
+
+def test_insert_then_delete_restores_sk():
+    """Identity (iii): insertion followed by deletion of the same molecule (physical mode) restores A(k)."""
+    s = load_system("h2o_ads", init_sk=1, deletion_mode=1)
+    o = orc.Oracle(s); o.system_energy()
+    a0 = o.sk().copy(); n0 = int(o.counts()[0])
+    big = 1.0 - 1e-16
+    rec = o.single_move(MMC_CREATION, 0, n0, [0.3, 0.6, 0.2, 0.4, 0.7, 0.0])   # accept draw 0 -> accepted
+    assert rec["accepted"] == 1 and o.counts()[0] == n0 + 1
+    rec = o.single_move(MMC_DELETION, 0, n0, [0.0])
+    assert rec["accepted"] == 1 and o.counts()[0] == n0
+    np.testing.assert_allclose(o.sk(), a0, atol=1e-12)
+
+
+def test_reference_quirks_are_reproduced():
+    """Q1: tracked A(k) starts at zero; Q2: deletion ADDS the phases of the molecule swapped into the slot."""
+    s = load_system("h2o_ads")            # defaults: init_sk=zero, deletion=reference
+    o = orc.Oracle(s); o.system_energy()
+    assert np.all(o.sk() == 0)
+    n0 = int(o.counts()[0])
+    o.single_move(MMC_DELETION, 0, 2, [0.0])
+    q = s.charges[0, :4]
+    pos = s.positions().reshape(n0, 4, 3)[n0 - 1]           # the former last molecule, now in slot 2
+    kx, ky, kz, _, _ = o.kvectors()
+    kvec = 2 * np.pi * np.stack([kx, ky, kz], 1) / s.box_len
+    expect = (q[None, :] * np.exp(1j * kvec @ pos.T)).sum(1)
+    np.testing.assert_allclose(o.sk(), expect, atol=1e-10)
+
+
+def test_draw_order_and_counters():
+    """number of uniforms consumed per move type."""
+    s = load_system("h2o_ads"); o = orc.Oracle(s); o.system_energy()
+    pt, pr = s.p_translation, s.p_rotation
+    for sel, sub, expected in [(pt * 0.5, None, 3 + 3 + 1), (pt + pr * 0.5, None, 3 + 2 + 1),
+                               (0.99, 0.1, 4 + 3 + 2 + 1), (0.99, 0.9, 4 + 1)]:
+        tape = [0.0, 0.5, sel] + ([sub] if sub is not None else []) + [0.5] * 12
+        o.run(1, tape=tape)
+        assert o.tape_used == expected
+
+
+def test_adjust_step_sizes_quirk():
+    """Q6: translation shrinks unless acceptance > 0.45; rotation branch does min(angle*1.95, 1e-3)."""
+    s = load_system("h2o_ads", p_translation=0.5, p_rotation=0.5)
+    o = orc.Oracle(s); o.system_energy(); o.set_recalibrate(1)
+    o.run(1200, tape=np.random.default_rng(2).random(12000))
+    c = o.counters(); t0, r0 = o.step_sizes()
+    o.adjust_step_sizes()
+    t1, r1 = o.step_sizes()
+    acc_t = c["translations"] / c["trial_translations"]
+    assert c["trial_translations"] > 500 and c["trial_rotations"] > 500
+    assert t1 == (min(t0 * 1.05, 3.0) if acc_t - 0.40 > 0.05 else max(t0 * 0.95, 1e-3))
+    acc_r = c["rotations"] / c["trial_rotations"]
+    assert r1 == (min(r0 * 1.05, 0.78) if acc_r - 0.40 > 0.05 else min(r0 * 1.95, 1e-3))
+
+
+def test_reader_matches_fixture():
+    """The committed fixtures are what the readers produce from the reference's files (only where present)."""
+    ref = "/root/reference/mc-topology/testcase-energy/LJ-gas"
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present on this machine")
+    from maniac_mc_b200 import builders
+    s = builders.from_files(*(os.path.join(ref, f) for f in ("input.maniac", "topology.data", "parameters.inc")), capacity=256)
+    g = load_system("lj_gas")
+    np.testing.assert_array_equal(s.com, g.com); np.testing.assert_array_equal(s.epsilon, g.epsilon)
+    # robustness cases of tests/readers/data/run-test.sh: bad files must raise
+    from maniac_mc_b200 import readers
+    d = "/root/reference/tests/readers/data"
+    for f in sorted(os.listdir(d)):
+        if f.startswith("good") and f.endswith(".data"):
+            readers.read_lammps_data(os.path.join(d, f))
+        # bad-04 truncates the Angles section, which this harness never reads (topology is host-only state)
+        if f.startswith("bad") and f.endswith(".data") and "04" not in f:
+            with pytest.raises(Exception):
+                readers.read_lammps_data(os.path.join(d, f))
