@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- MC trial moves/s of the per-move energy path on B200 (BASELINE.json metric), with the
+roofline of the dominant kernel and the CPU restatement timed beside it.
+
+    python bench.py --gpus N --steps K --warmup W            # own arm (CUDA library through the C ABI)
+    python bench.py --impl reference --gpus N --steps K ...  # reference arm: the CPU oracle port on the host cores
+
+Workload (config.workload = "c4_large_k"): BASELINE.json configs[3] -- synthetic 50 000-atom framework (one
+inactive residue) + 200 rigid TIP4P guests per chain, L = 96 A, r_c = 12 A, Ewald tol 1e-6 -> K = 37 782
+k-vectors; `--chains` independent chains per GPU (isotherm: 64 log-spaced fugacities x replicas, configs[4]),
+`--moves` MC steps per chain per bench step, translation/rotation/insertion/deletion 0.4/0.4/0.1/0.1.
+One bench "step" = one batch: chains x moves trial moves (CUDA-graph replay of 128-step chunks).
+
+Multi-GPU: one process per GPU (torchrun); chains (pressure points x replicas) are dealt to ranks, no data-path
+collective; weak scaling (chains per GPU fixed).  The only collectives are the barrier and the MAX of
+the device-timed durations.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+W_PAIR_FLOP = 90.0   # FP64 flop per pair-eval, SURVEY.md 8(d) / DESIGN.md
+B_K_BYTES = 40.0     # HBM bytes per k-eval: A(k) read 16 + A'(k) write 16 + f*W 8
+FUG_LO_ATM, FUG_HI_ATM, N_POINTS = 1.0e-2, 1.0e4, 64
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="own", choices=["own", "reference"])
+    p.add_argument("--chains", type=int, default=64, help="independent chains per GPU")
+    p.add_argument("--moves", type=int, default=256, help="MC steps per chain per bench step")
+    p.add_argument("--framework", type=int, default=50000)
+    p.add_argument("--guests", type=int, default=200)
+    p.add_argument("--cpu-moves", type=int, default=8, help="moves per host thread per CPU sample/step")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def make_system(args):
+    from maniac_mc_b200 import builders
+    s = builders.synthetic_framework(n_framework=args.framework, n_guests=args.guests, box=96.0, cutoff=12.0,
+                                     tol=1e-6, seed=4, capacity=512, p_translation=0.4, p_rotation=0.4)
+    s.init_sk, s.deletion_mode = 1, 1   # physically consistent A(k) (quirk switches Q1/Q2 off); work per move is unchanged
+    return s
+
+
+def chain_fugacity(s, global_chain):
+    from maniac_mc_b200 import builders
+    point = global_chain % N_POINTS
+    f_atm = FUG_LO_ATM * (FUG_HI_ATM / FUG_LO_ATM) ** (point / (N_POINTS - 1))
+    f = s.fugacity.copy()
+    f[0] = builders.fugacity_from_atm(f_atm, s.temperature)
+    return f
+
+
+def workload_config(args, s, world):
+    return {"workload": "c4_large_k", "framework_atoms": int(args.framework), "guests_per_chain_initial": int(args.guests),
+            "guest_atoms_per_molecule": 4, "box_A": 96.0, "cutoff_A": 12.0, "ewald_tol": 1e-6,
+            "k_vectors": int(s.num_kvectors), "chains_per_gpu": int(args.chains), "moves_per_chain_per_step": int(args.moves),
+            "move_mix": "translation 0.4 / rotation 0.4 / insertion 0.1 / deletion 0.1",
+            "isotherm": f"{N_POINTS} fugacities {FUG_LO_ATM:g}..{FUG_HI_ATM:g} atm x replicas, chains dealt to ranks",
+            "parallelism": f"chains x{world} (no data-path collective)", "quirks": "init_sk=full, deletion=physical",
+            "rng": "device Philox4x32-10", "l2": "256 MiB write between steps (inside the timed region)"}
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc = None; self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True); self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def pair_evals_of(s, args, counts, d_counters):
+    """pair-evals done by the moves counted in d_counters (per chain dicts of counter deltas)."""
+    nat, n_fw = 4, args.framework
+    total = 0.0
+    for c, d in enumerate(d_counters):
+        n_atoms = n_fw + nat * float(counts[c])
+        total += (d["trial_translations"] + d["trial_rotations"]) * 2.0 * nat * (n_atoms - nat)
+        total += d["trial_creations"] * nat * n_atoms + d["trial_deletions"] * nat * (n_atoms - nat)
+    return total
+
+
+def counters_delta(a, b):
+    return [{k: b[i][k] - a[i][k] for k in b[i]} for i in range(len(b))]
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU leg: the oracle port (oracle/maniac_oracle.c, plain C, glibc) -- the only place bench.py executes oracle/.
+# The reference itself is pure Fortran and neither this image nor the GPU box has a Fortran compiler, so the
+# baseline kind is "port".  One independent chain per host thread (the reference is single threaded; replicas
+# are the only way it can use more cores).
+class CpuSample:
+    def __init__(self, s, n_threads):
+        from oracle.oracle import Oracle
+        cpu = s.copy()
+        cpu.init_sk = 0   # reference default (Q1): skips the ~30 s single-point start-up per chain; per-move work identical
+        self.oracles = [Oracle(cpu) for _ in range(n_threads)]
+        self.step0 = 0
+
+    def run(self, moves):
+        """every thread advances its chain by `moves` MC steps; returns wall seconds"""
+        def work(i, o):
+            o.run(moves, seed=99, chain=i, step0=self.step0, records=False)
+        ths = [threading.Thread(target=work, args=(i, o)) for i, o in enumerate(self.oracles)]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t0
+        self.step0 += moves
+        return dt
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    s = make_system(args)
+    nt = host_threads()
+    cs = CpuSample(s, nt)
+    for _ in range(args.warmup):
+        cs.run(max(1, args.cpu_moves // 4))
+    t = 0.0
+    for _ in range(args.steps):
+        t += cs.run(args.cpu_moves)
+    moves = nt * args.cpu_moves * args.steps
+    v = moves / t
+    sample = (f"{nt} host threads x {args.cpu_moves} MC moves per step of the same c4_large_k system, one independent chain "
+              f"per thread (oracle port, gcc -O2, reference-default init_sk=zero)")
+    cfg = workload_config(args, s, world)
+    print(json.dumps({"impl": "reference", "metric": "mc_trial_moves_per_s", "value": v, "unit": "moves/s", "n_gpus": args.gpus,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+                      "cpu_baseline": {"value": v, "unit": "moves/s", "cores": nt, "kind": "port", "sample": sample},
+                      "e2e": {"value": v, "unit": "moves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------------
+def run_own(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from maniac_mc_b200 import lib
+    from maniac_mc_b200.lib import ManiacGPU
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    s = make_system(args)
+    C = args.chains
+    gpu = ManiacGPU(s, n_chains=C, device=local_rank)
+    for c in range(C):
+        gpu.set_chain_params(c, chain_fugacity(s, rank * C + c), s.temperature)
+        gpu.system_energy(c)
+    stream = torch.cuda.ExternalStream(gpu.stream(), device=local_rank)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
+    g_mols, g_atoms = gpu.chain_capacity()
+    pin = lambda *shape, dt=torch.float64: torch.zeros(*shape, dtype=dt).pin_memory()
+    h_cnt, h_com, h_off = pin(C, s.nres, dt=torch.int32), pin(C, g_mols, 3), pin(C, g_atoms, 3)
+    h_e, h_ctr = pin(C, 6), pin(C, 8, dt=torch.int64)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def download():
+        gpu.download_chains(h_cnt.data_ptr(), h_com.data_ptr(), h_off.data_ptr(), h_e.data_ptr(), h_ctr.data_ptr())
+
+    def counters():
+        download()
+        names = ["translations", "rotations", "creations", "deletions", "trial_translations", "trial_rotations",
+                 "trial_creations", "trial_deletions"]
+        a = h_ctr.numpy().copy()
+        return [dict(zip(names, (int(v) for v in row))) for row in a]
+
+    def device_step(seed):
+        with torch.cuda.stream(stream):
+            flush.fill_(1)
+        gpu.run_batch_async(args.moves, seed=seed)
+
+    def e2e_step(seed):
+        gpu.upload_chains(h_cnt.data_ptr(), h_com.data_ptr(), h_off.data_ptr())   # H2D of the step's inputs (pinned)
+        gpu.run_batch_async(args.moves, seed=seed)
+        download()                                                                # D2H of the step's results (pinned)
+
+    # ---- device-resident throughput --------------------------------------------------------------
+    for w in range(args.warmup):
+        device_step(7)
+    gpu.synchronize()
+    c0 = counters(); l0 = gpu.launch_count()
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for k in range(args.steps):
+        device_step(7)
+    ev1.record(stream)
+    gpu.synchronize()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = gpu.launch_count() - l0
+    c1 = counters()
+    clk = clocks.stop() if clocks else None
+    # ---- end to end through the C ABI with host buffers ------------------------------------------
+    download()
+    for w in range(2):
+        e2e_step(11)
+    barrier()
+    ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev2.record(stream)
+    for k in range(args.steps):
+        e2e_step(11)
+    ev3.record(stream)
+    gpu.synchronize()
+    barrier()
+    ms_e2e = ev2.elapsed_time(ev3)
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+    moves_total = world * C * args.moves * args.steps
+    value = moves_total / (ms * 1e-3)
+    e2e_value = moves_total / (ms_e2e * 1e-3)
+    h2d = h_cnt.numel() * 4 + (h_com.numel() + h_off.numel()) * 8
+    d2h = h2d + h_e.numel() * 8 + h_ctr.numel() * 8
+    if rank != 0:
+        gpu.close()
+        return
+    # ---- roofline of the dominant kernel (rank 0): instrumented replay right after the timed region
+    cp0 = counters()
+    prof = gpu.profile_kernels(32, seed=13)
+    cp1 = counters()
+    counts = h_cnt.numpy()[:, 0].copy()
+    dprof = counters_delta(cp0, cp1)
+    evals = pair_evals_of(s, args, counts, dprof)
+    k_evals = sum(sum(d[k] for k in d if k.startswith("trial_")) for d in dprof) * float(gpu.nk)
+    fp64_peak = lib.measure_fp64_peak(local_rank)
+    pair_tflops = evals * W_PAIR_FLOP / (prof["pair_ms"] * 1e-3 * prof["launches_each"]) / 1e12
+    recip_gbs = k_evals * B_K_BYTES / (prof["recip_ms"] * 1e-3 * prof["launches_each"]) / 1e9
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    step_ms = prof["pair_ms"] + prof["recip_ms"] + prof["tail_ms"]
+    roofline = {"kernel": "k_pair_sweep", "bound": "fp64", "achieved": pair_tflops, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": pair_tflops / fp64_peak, "traffic": None,
+                "peak_source": "DFMA micro-benchmark run in this process (mmc_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
+                "algorithmic": f"{W_PAIR_FLOP:g} FP64 flop per pair-eval x pair-evals per launch",
+                "avg_launch_ms": prof["pair_ms"], "share_of_step": prof["pair_ms"] / step_ms,
+                "pair_evals_per_s": evals / (prof["pair_ms"] * 1e-3 * prof["launches_each"])}
+    roofline_recip = {"kernel": "k_recip_sweep", "bound": "hbm", "achieved": recip_gbs, "peak": hbm_peak, "unit": "GB/s",
+                      "frac": recip_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                      "algorithmic": f"{B_K_BYTES:g} B per k-eval x k-evals per launch",
+                      "avg_launch_ms": prof["recip_ms"], "share_of_step": prof["recip_ms"] / step_ms,
+                      "k_evals_per_s": k_evals / (prof["recip_ms"] * 1e-3 * prof["launches_each"])}
+    dall = counters_delta(c0, c1)
+    evals_timed = pair_evals_of(s, args, counts, dall)
+    out = {"metric": "mc_trial_moves_per_s", "value": value, "unit": "moves/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, s, world),
+           "pair_evals_per_s": world * evals_timed / (ms * 1e-3),
+           "e2e": {"value": e2e_value, "unit": "moves/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "call": "mmc_upload_chains + mmc_run_batch_async + mmc_download_chains per step, pinned host buffers"},
+           "gpu_launches": int(launches), "roofline": roofline, "roofline_recip": roofline_recip,
+           "tail_avg_launch_ms": prof["tail_ms"], "clocks": clk, "mean_guests_per_chain": float(counts.mean())}
+    gpu.close()
+    if world == 1 and not args.no_cpu_baseline:
+        nt = host_threads()
+        cs = CpuSample(s, nt)
+        cs.run(1)
+        dt = cs.run(args.cpu_moves)
+        out["cpu_baseline"] = {"value": nt * args.cpu_moves / dt, "unit": "moves/s", "cores": nt, "kind": "port",
+                               "sample": f"{nt} host threads x {args.cpu_moves} MC moves of the same c4_large_k system, one "
+                                         f"independent chain per thread (oracle port, gcc -O2, init_sk=zero), {dt:.1f} s wall"}
+    print(json.dumps(out))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    run_own(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -163,6 +163,21 @@ int mmc_trial_commit(mmc_t* handle, int chain, int accept);
  * counts and packed coordinates of one chain */
 int mmc_sync_to_host(mmc_t* handle, int chain, int* count, double* com, double* offsets,
                      double energies[MMC_NE]);
+/* Bulk form of the per-block exchange for many chains (isotherm sweeps): the host keeps, per chain,
+ * fixed-capacity arrays like the reference's primary%mol_com(3,nres,NB_MAX) / site_offset
+ * (input_parser.f90:250-251), restricted to the ACTIVE residues:
+ *   count  [n_chains][nres]
+ *   com    [n_chains][g_mols ][3]   slot of (active residue r, molecule m) = mol_base[r] + m
+ *   offsets[n_chains][g_atoms][3]   slot of (r, m, a) = atom_base[r] + m*natoms[r] + a
+ * with g_mols = sum_r capacity[r], g_atoms = sum_r capacity[r]*natoms[r] over active residues in
+ * residue order (mmc_chain_capacity returns them).  Host buffers may be pinned; copies are
+ * asynchronous on the handle's stream, the calls return after the stream has drained.
+ * mmc_download_chains also returns tracked energies [n_chains][MMC_NE] and counters [n_chains]
+ * (any pointer may be NULL). */
+int mmc_chain_capacity(const mmc_t* handle, int* g_mols, int* g_atoms);
+int mmc_upload_chains(mmc_t* handle, const int* count, const double* com, const double* offsets);
+int mmc_download_chains(mmc_t* handle, int* count, double* com, double* offsets, double* energies,
+                        mmc_counters* counters);
 /* tracked A(k) as (re,im) pairs, 2*K doubles (ewald%recip_amplitude) */
 int mmc_get_sk(mmc_t* handle, int chain, double* sk);
 
@@ -202,6 +217,11 @@ int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
 void* mmc_stream(mmc_t* handle);
 /* kernel launches issued by this handle since init (bench.py's gpu_launches) */
 int64_t mmc_launch_count(const mmc_t* handle);
+/* Instrumented replay for the roofline report: runs n_steps batched steps WITHOUT graph capture,
+ * CUDA events around every launch on the handle's stream, and returns the average duration in ms
+ * of one launch of {pair sweep, reciprocal sweep, step tail} in ms[0..2] and the number of
+ * launches of each in n[0..2].  Advances the chains like mmc_run_batch_async. */
+int mmc_profile_kernels(mmc_t* handle, int n_steps, uint64_t seed, double ms[3], int64_t n[3]);
 /* FP64 FMA peak micro-benchmark (register-resident DFMA chains): returns TFLOP/s */
 int mmc_measure_fp64_peak(int device, double* tflops);
 

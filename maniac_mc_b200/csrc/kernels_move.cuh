@@ -502,4 +502,16 @@ __global__ void __launch_bounds__(TAIL_THREADS) k_step_tail(DevConst dc, ChainSt
     __syncthreads();
     build_phase_tables(dc, cs, c);
 }
+// positions = COM + offset for every guest slot of every chain (after a bulk upload); grid = (tiles, n_chains)
+__global__ void k_rebuild_positions(DevConst dc, ChainState cs) {
+    const int c = blockIdx.y, g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= dc.g_atoms) return;
+    int r = 0;
+    for (int i = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (g >= dc.g_atom_base[rr]) r = rr; }
+    const int m = (g - dc.g_atom_base[r]) / dc.natoms[r];
+    const size_t ia = (size_t)c * dc.g_atoms + g;
+    const double* com = cs.gcom + ((size_t)c * dc.g_mols + dc.g_mol_base[r] + m) * 3;
+    const double* off = cs.goff + ia * 3;
+    cs.gx[ia] = com[0] + off[0]; cs.gy[ia] = com[1] + off[1]; cs.gz[ia] = com[2] + off[2];
+}
 __global__ void k_advance(BatchCtl* ctl, int g) { ctl->rng.step += (unsigned long long)g; ctl->rec_base += g; }

@@ -420,6 +420,53 @@ extern "C" int mmc_sync_to_host(mmc_t* h, int c, int* count, double* com, double
     return 0;
 }
 
+extern "C" int mmc_chain_capacity(const mmc_t* h, int* g_mols, int* g_atoms) {
+    if (!h) return fail("null handle");
+    if (g_mols) *g_mols = h->dc.g_mols;
+    if (g_atoms) *g_atoms = h->dc.g_atoms;
+    return 0;
+}
+
+// the host arrays hold nres counts per chain, the device MMC_MAX_RES: one strided 2-D copy
+extern "C" int mmc_upload_chains(mmc_t* h, const int* count, const double* com, const double* offsets) {
+    if (!h) return fail("null handle");
+    if (!count || !com || !offsets) return fail("mmc_upload_chains: null argument");
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; const size_t C = dc.n_chains; cudaStream_t st = h->stream;
+    for (size_t c = 0; c < C; c++)
+        for (int r = 0; r < dc.nres; r++)
+            if (dc.is_active[r] && (count[c * dc.nres + r] < 0 || count[c * dc.nres + r] > dc.cap[r]))
+                return fail("chain %d residue %d: count %d outside [0,%d]", (int)c, r, count[c * dc.nres + r], dc.cap[r]);
+    CK(cudaMemcpy2DAsync(h->cs.count, MMC_MAX_RES * sizeof(int), count, dc.nres * sizeof(int), dc.nres * sizeof(int), C, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.gcom, com, C * dc.g_mols * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(h->cs.goff, offsets, C * dc.g_atoms * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    k_rebuild_positions<<<dim3((dc.g_atoms + 255) / 256, (unsigned)C), 256, 0, st>>>(dc, h->cs);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    for (size_t c = 0; c < C; c++)
+        for (int r = 0; r < MMC_MAX_RES; r++)
+            h->h_count[c * MMC_MAX_RES + r] = (r < dc.nres && dc.is_active[r]) ? count[c * dc.nres + r] : 0;
+    h->pending_chain = -1;
+    return 0;
+}
+
+extern "C" int mmc_download_chains(mmc_t* h, int* count, double* com, double* offsets, double* energies, mmc_counters* counters) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; const size_t C = dc.n_chains; cudaStream_t st = h->stream;
+    if (count) CK(cudaMemcpy2DAsync(count, dc.nres * sizeof(int), h->cs.count, MMC_MAX_RES * sizeof(int), dc.nres * sizeof(int), C, cudaMemcpyDeviceToHost, st));
+    if (com) CK(cudaMemcpyAsync(com, h->cs.gcom, C * dc.g_mols * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (offsets) CK(cudaMemcpyAsync(offsets, h->cs.goff, C * dc.g_atoms * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (energies) CK(cudaMemcpyAsync(energies, h->cs.energy, C * MMC_NE * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (counters) CK(cudaMemcpyAsync(counters, h->cs.counters, C * sizeof(mmc_counters), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (count)  // inactive residues: the host already knows them
+        for (size_t c = 0; c < C; c++)
+            for (int r = 0; r < dc.nres; r++) if (!dc.is_active[r]) count[c * dc.nres + r] = dc.cap[r];
+    return 0;
+}
+
 extern "C" int mmc_get_sk(mmc_t* h, int c, double* sk) {
     CHECK_CHAIN(h, c);
     if (!sk) return fail("mmc_get_sk: null output");
@@ -583,6 +630,42 @@ extern "C" int mmc_run_batch_async(mmc_t* h, int64_t n_steps, uint64_t seed) {
     if (n_steps < 1) return fail("mmc_run_batch: n_steps must be >= 1");
     CK(cudaSetDevice(h->device));
     return enqueue_batch(h, n_steps, seed, nullptr, 0, nullptr);
+}
+
+extern "C" int mmc_profile_kernels(mmc_t* h, int n_steps, uint64_t seed, double ms[3], int64_t n[3]) {
+    if (!h || !ms || !n) return fail("mmc_profile_kernels: null argument");
+    if (n_steps < 1 || n_steps > 4096) return fail("mmc_profile_kernels: n_steps must be in [1,4096]");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream; const int C = h->dc.n_chains;
+    BatchCtl ctl;
+    ctl.rng.tape = nullptr; ctl.rng.tape_stride = 0; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
+    ctl.recs = nullptr; ctl.rec_stride = n_steps; ctl.rec_base = 0;
+    CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), st));
+    std::vector<cudaEvent_t> ev((size_t)n_steps * 4);
+    for (auto& e : ev) CK(cudaEventCreate(&e));
+    k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, 0, 1, 0);
+    for (int s = 0; s < n_steps; s++) {
+        cudaEvent_t* e = &ev[(size_t)s * 4];
+        CK(cudaEventRecord(e[0], st));
+        k_pair_sweep<<<dim3(h->dc.n_pair_tiles, C), PAIR_THREADS, 0, st>>>(h->dc, h->cs, 0);
+        CK(cudaEventRecord(e[1], st));
+        k_recip_sweep<<<dim3(h->dc.n_k_tiles, C), RECIP_THREADS, h->recip_smem, st>>>(h->dc, h->cs, 0);
+        CK(cudaEventRecord(e[2], st));
+        k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, s + 1, 0, s == n_steps - 1 ? 1 : 0);
+        CK(cudaEventRecord(e[3], st));
+    }
+    h->launches += 1 + 3 * (int64_t)n_steps;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    double acc[3] = {0, 0, 0};
+    for (int s = 0; s < n_steps; s++)
+        for (int k = 0; k < 3; k++) { float t = 0; CK(cudaEventElapsedTime(&t, ev[(size_t)s * 4 + k], ev[(size_t)s * 4 + k + 1])); acc[k] += t; }
+    for (auto& e : ev) cudaEventDestroy(e);
+    for (int k = 0; k < 3; k++) { ms[k] = acc[k] / n_steps; n[k] = n_steps; }
+    h->steps_done += (unsigned long long)n_steps;
+    h->pending_chain = -1;
+    return refresh_counts(h);
 }
 
 extern "C" int mmc_synchronize(mmc_t* h) {

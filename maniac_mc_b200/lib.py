@@ -46,6 +46,7 @@ ABI_SYMBOLS = [
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
+    "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels",
 ]
 
 _lib = None
@@ -87,6 +88,10 @@ def load():
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
     L.mmc_measure_fp64_peak.argtypes = [C.c_int, dp]
+    L.mmc_chain_capacity.argtypes = [vp, ip, ip]
+    L.mmc_upload_chains.argtypes = [vp, vp, vp, vp]
+    L.mmc_download_chains.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.mmc_profile_kernels.argtypes = [vp, C.c_int, C.c_uint64, dp, C.POINTER(C.c_int64)]
     _lib = L
     return L
 
@@ -97,6 +102,14 @@ def _dp(a):
 
 def _ip(a):
     return None if a is None else a.ctypes.data_as(C.POINTER(C.c_int))
+
+
+def _addr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    return a.ctypes.data
 
 
 def _ck(rc):
@@ -234,6 +247,25 @@ class ManiacGPU:
 
     def tape_used(self, chain=0):
         return load().mmc_tape_used(self.h, chain)
+
+    # ---- bulk per-block exchange (fixed-capacity host arrays, see include/maniac_gpu.h)
+    def chain_capacity(self):
+        a, b = C.c_int(), C.c_int()
+        _ck(load().mmc_chain_capacity(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def upload_chains(self, count, com, offsets):
+        """count int32 [C, nres], com f8 [C, g_mols, 3], offsets f8 [C, g_atoms, 3]; numpy arrays or raw
+        addresses (ints) of host buffers, e.g. pinned torch tensors' data_ptr()."""
+        _ck(load().mmc_upload_chains(self.h, _addr(count), _addr(com), _addr(offsets)))
+
+    def download_chains(self, count=None, com=None, offsets=None, energies=None, counters=None):
+        _ck(load().mmc_download_chains(self.h, _addr(count), _addr(com), _addr(offsets), _addr(energies), _addr(counters)))
+
+    def profile_kernels(self, n_steps, seed=0):
+        ms = (C.c_double * 3)(); n = (C.c_int64 * 3)()
+        _ck(load().mmc_profile_kernels(self.h, n_steps, seed, ms, n))
+        return {"pair_ms": ms[0], "recip_ms": ms[1], "tail_ms": ms[2], "launches_each": n[0]}
 
     # ---- debug
     def dbg_pair_singlemol(self, res, mol, chain=0):
