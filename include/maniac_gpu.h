@@ -82,6 +82,10 @@ typedef struct mmc_desc {
     int deletion_mode;     /* MMC_DELETION_* */
     int use_table;         /* 0: direct erfc/LJ (reference behaviour, parameters.f90:42); 1: tabulated_utils.f90 tables */
     int device;            /* CUDA device ordinal */
+    double coulomb_xcut;   /* real-space Coulomb terms with alpha*r >= xcut are skipped by the per-move sweep:
+                            * erfc(xcut) is below one ulp of the sums the reference forms over all minimum-image
+                            * pairs (energy_utils.f90:425-433).  0 = default 6.5 (erfc = 3.8e-20), max 7;
+                            * negative = evaluate every pair literally as the reference does */
 } mmc_desc;
 
 /* One record per trial move of a batched run (optional output). */

@@ -12,11 +12,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/maniac_gpu.h"
+#include "erfc_table.h"
 
 #define MMC_MAX_RES 8
-#define PAIR_THREADS 256
-#define RECIP_THREADS 256
+#define RECIP_THREADS 256   // single-point S(k) kernels
 #define TAIL_THREADS 128
+#define SWEEP_THREADS 256   // strict-mode sweep: CTAs of this size, dc.sweep_parts per chain
+#define TILE 32             // framework atoms per tile (one per lane)
+#define CULL_CHUNK 4096     // tiles culled per pass (shared-memory list)
 
 // constants.f90:7-20
 #define MMC_PI 3.14159265358979323846
@@ -33,7 +36,6 @@ struct DevConst {
     int g_mol_base[MMC_MAX_RES];   // first guest-molecule slot of residue r
     int g_atoms, g_mols;           // per-chain guest capacities (atoms, molecules)
     int n_fw;                      // framework atoms (all inactive residues, flattened)
-    int n_pair_tiles;              // ceil((n_fw + g_atoms) / PAIR_THREADS)
     int n_k_tiles;                 // ceil(nk / RECIP_THREADS)
     int nk, kmax[3], kstride;      // kstride = max(kmax)+1 : row length of a 1-D phase table
     int deletion_mode, use_table;
@@ -51,6 +53,21 @@ struct DevConst {
     const double* fw;
     const double *tab_erfc, *tab_r6, *tab_r12;  // tabulated_utils.f90 tables (5001 points each)
     double tab_dx;
+    // ---- per-move sweep layout (kernels_sweep.cuh) ----
+    // framework atoms in Morton order of their cell, padded to whole tiles of 32 atoms; tile t owns
+    // atoms [32 t, 32 t + 32).  tbox[t] = {centre xyz, half extent xyz} of the tile's wrapped positions.
+    const double *sx, *sy, *sz, *sq;
+    const int* stype;
+    const double* tbox;            // [n_tiles][6]
+    int n_tiles;
+    const double* erfc_tab;        // [(MMC_ERFC_DEG+1) * MMC_ERFC_NSEG], erfc_table.h
+    const uint32_t* kpack;         // per k-vector table indices kx | (ky+kmax_y)<<10 | (kz+kmax_z)<<21
+    const double* res_q;           // [MMC_MAX_RES][MMC_MAX_MOL_ATOMS] charges of the active residues
+    const int* res_type;           // same, 0-based atom types
+    // real-space reach: LJ inside rc, erfc-Coulomb inside x_cut/alpha (terms beyond it are < erfc(x_cut),
+    // far below one ulp of the sums); reach2 = inf when culling is off (every pair evaluated, Q3 literally)
+    double rc2, alpha2, reach, reach2;
+    int max_nat, sweep_parts;      // largest active molecule; CTAs per chain of the strict-mode sweep
 };
 
 // one pending trial move of one chain
@@ -85,9 +102,7 @@ struct ChainState {
     double* rstep;     // [C]
     mmc_counters* counters;  // [C]
     Trial* trial;      // [C]
-    double2* phase;    // [C][2 sets][3 axes][MMC_MAX_MOL_ATOMS][kstride]  (set 0 = plus, 1 = minus)
-    double* pair_part; // [C][n_pair_tiles][4]  (lj_old, coul_old, lj_new, coul_new)
-    double* recip_part;// [C][n_k_tiles][2]     (sum fW|A|^2, sum fW|A'|^2)
+    double* part;      // [C][sweep_parts][6]  (lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2)
     long long* tape_pos;  // [C]
     int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)
 };
@@ -159,7 +174,36 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
 
 // erfc used by the real-space sweeps.  Accuracy contract (tests/test_gpu_parity.py::test_erfc):
 // |device - glibc| <= 2e-15 absolute and <= 1e-13 relative on [0, 6].
-__device__ __forceinline__ double mmc_erfc(double x) { return erfc(x); }
+__device__ __noinline__ double mmc_erfc_slow(double x) { return erfc(x); }
+// exp(-x^2) * P_seg(t): piecewise degree-9 fit of erfcx (tools/gen_erfc_table.py, 3e-15 relative) for
+// 0 <= x < 7; `e` = exp(-x^2) supplied by the caller (it has -alpha^2 r^2 exactly); tab may be shared memory.
+__device__ __forceinline__ double mmc_erfcx_poly(double x, const double* tab) {
+    const double u = x * ((double)MMC_ERFC_NSEG / MMC_ERFC_XMAX);
+    const int i = min((int)u, MMC_ERFC_NSEG - 1);
+    const double t = fma(2.0, u - (double)i, -1.0);
+    double p = tab[MMC_ERFC_DEG * MMC_ERFC_NSEG + i];
+#pragma unroll
+    for (int d = MMC_ERFC_DEG - 1; d >= 0; d--) p = fma(p, t, tab[d * MMC_ERFC_NSEG + i]);
+    return p;
+}
+__device__ __forceinline__ double mmc_erfc(double x, const double* tab) {
+    if (x >= MMC_ERFC_XMAX || x < 0.0) return mmc_erfc_slow(x);
+    return exp(-x * x) * mmc_erfcx_poly(x, tab);
+}
+// 1/sqrt(a) for a in the normal float range: float seed (2 ulp) + one cubically convergent FP64 step
+// (residual error ~ (5/16) e^3 with e ~ 5e-7 -> below 1 ulp)
+__device__ __forceinline__ double mmc_rsqrt(double a) {
+    const double y = (double)rsqrtf((float)a);
+    const double e = fma(-a * y, y, 1.0);
+    return fma(y * e, fma(0.375, e, 0.5), y);
+}
+// minimum image by round-to-nearest: d - L * nint(d / L).  Same value as the reference's
+// modulo(d + L/2, L) - L/2 (geometry_utils.f90:385-393) up to rounding; the 1.5*2^52 constant rounds to integer
+__device__ __forceinline__ double min_image_fast(double d, double L, double invL) {
+    const double big = 6755399441055744.0;
+    const double n = fma(d, invL, big) - big;
+    return fma(-n, L, d);
+}
 
 // LookupTabulated tabulated_utils.f90:87-113
 __device__ __forceinline__ double table_lookup(const double* f, double dx, double r) {

@@ -1,0 +1,60 @@
+// kernels_chain.cuh -- batched mode: the inner `do current_step` loop of MonteCarloLoop
+// (monte_carlo.f90:42-76) for MANY independent chains (pressure points x replicas) in one launch.
+//
+// Chains never exchange data, so a chain needs no grid-wide synchronisation: ONE CTA owns a chain for the
+// whole launch and loops over the MC steps; block barriers are the only synchronisation.  Per step:
+//   thread 0      : selection + proposal (propose_move, draw order of SURVEY 3.8)
+//   all threads   : stage the trial in shared memory (positions, LJ rows, 1-D phase tables)
+//   all threads   : real-space sweep over the framework tiles in reach + this chain's guests (FP64 pipe)
+//   all threads   : reciprocal sweep A'(k) = A(k) + dS(k), sum f W |A|^2 (HBM / shared memory)
+//   thread 0      : energy assembly, Metropolis test, commit (coordinates, A buffer flip), record
+// Several CTAs are resident per SM, so one chain's serial sections overlap other chains' sweeps.
+// grid = chains handled by this launch (chain = chain0 + blockIdx.x).
+#pragma once
+#include "kernels_move.cuh"
+#include "kernels_sweep.cuh"
+
+// phases: bit 0 = real-space sweep, bit 1 = reciprocal sweep (both for production; single-phase variants
+// exist only so bench.py can time each sweep alone on the same trials -- they do not commit)
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState cs, const BatchCtl* ctl, int chain0, int n_steps,
+                                                        int phases) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const SweepCtx s = sweep_carve(dc, smem, NT);
+    const int c = chain0 + blockIdx.x;
+    sweep_load_tables(dc, s);
+    RngSrc rs = ctl->rng;
+    const unsigned long long step0 = rs.step;
+    for (int st = 0; st < n_steps; st++) {
+        rs.step = step0 + (unsigned long long)st;
+        if (threadIdx.x == 0) {
+            propose_move(dc, cs, rs, c);
+            if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
+        }
+        __syncthreads();
+        sweep_stage(dc, cs, c, s);
+        double v[6] = {0, 0, 0, 0, 0, 0};
+        double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
+        double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
+        if (phases & 1) pair_phase<NT>(dc, cs, c, s, 0, 1, pa);
+        if (phases & 2) recip_phase<NT>(dc, cs, c, s, 0, 1, ra);
+        block_sum<6, NT>(v, s.red);
+        if (threadIdx.x == 0) {
+            Trial& t = cs.trial[c];
+            const int kind = t.kind;
+            if (kind > 0) {
+                finalize_trial(dc, cs, c, v);
+                Rng rng{&rs, cs, c, t.draw};  // the accept draw follows the proposal's draws
+                const double u = rng.next();
+                commit_trial(dc, cs, c, (phases == 3 && u <= t.prob) ? 1 : 0);
+            }
+            if (ctl->recs) {
+                mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + st];
+                rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
+                rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
+                for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
+            }
+        }
+        __syncthreads();
+    }
+}

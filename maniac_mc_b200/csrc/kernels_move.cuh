@@ -97,26 +97,6 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
     }
 }
 
-// 1-D phase tables e^{i k theta}, k = 0..kmax, by direct cos/sin(k*theta)
-// (ComputeAtomPhase + ComputePhaseFactors1D, ewald_phase.f90:41-109).  All threads of the block.
-__device__ inline void build_phase_tables(const DevConst& dc, const ChainState& cs, int c) {
-    const Trial& t = cs.trial[c];
-    if (t.kind <= 0) return;
-    const int ks = dc.kstride;
-    double2* ph = cs.phase + (size_t)c * 2 * 3 * MMC_MAX_MOL_ATOMS * ks;
-    const int per_set = 3 * t.nat * ks;
-    for (int i = threadIdx.x; i < 2 * per_set; i += blockDim.x) {
-        const int set = i / per_set, j = i % per_set;
-        const int ax = j / (t.nat * ks), a = (j / ks) % t.nat, k = j % ks;
-        if (k > dc.kmax[ax]) continue;
-        if ((set == 0 && !t.r_plus) || (set == 1 && !t.r_minus)) continue;
-        const double pos = set == 0 ? t.p_plus[a][ax] : t.p_old[a][ax];
-        const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
-        double s, co; sincos((double)k * theta, &s, &co);
-        ph[((size_t)(set * 3 + ax) * MMC_MAX_MOL_ATOMS + a) * ks + k] = make_double2(co, s);
-    }
-}
-
 // ----------------------------------------------------------------------------------------------
 // strict mode: the host made the proposal (Fortran RandomTranslation / ApplyRandomRotation /
 // InsertAndOrientMolecule); arguments by value, no H2D copy.
@@ -124,8 +104,6 @@ struct HostTrial { int chain, kind, res, mol; double com[3]; double off[MMC_MAX_
 
 __global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
     if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, ht.kind, ht.res, ht.mol, ht.com, ht.off);
-    __syncthreads();
-    build_phase_tables(dc, cs, ht.chain);
 }
 
 // batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
@@ -196,149 +174,6 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
 }
 
 // ----------------------------------------------------------------------------------------------
-// Real-space sweep: ComputePairInteractionEnergy_singlemol (energy_utils.f90:374-442) for the old
-// and the proposed geometry of the moved molecule in ONE pass over all other atoms.
-// grid = (n_pair_tiles, n_chains), block = PAIR_THREADS; thread j owns one "other" atom
-// (framework atoms are shared by all chains and stay L2 resident; guest atoms are per chain).
-// LJ only inside the cut-off, erfc-Coulomb for every minimum-image pair (Q3), charges below
-// 1e-10 skipped.  FP64 throughout.  Partial sums per block, summed in fixed order by the tail.
-struct PairSmem {
-    double px_o[MMC_MAX_MOL_ATOMS], py_o[MMC_MAX_MOL_ATOMS], pz_o[MMC_MAX_MOL_ATOMS];
-    double px_n[MMC_MAX_MOL_ATOMS], py_n[MMC_MAX_MOL_ATOMS], pz_n[MMC_MAX_MOL_ATOMS];
-    double q[MMC_MAX_MOL_ATOMS];
-    int type[MMC_MAX_MOL_ATOMS];
-    int nat, do_old, do_new, kind;
-    double red[4 * PAIR_THREADS / 32];
-};
-
-__device__ __forceinline__ void pair_eval(const DevConst& dc, double dx, double dy, double dz, double qa, double qj,
-                                          double2 lj, bool charged, double& e_lj, double& e_c) {
-    dx = min_image(dx, dc.L[0], dc.invL[0]);
-    dy = min_image(dy, dc.L[1], dc.invL[1]);
-    dz = min_image(dz, dc.L[2], dc.invL[2]);
-    const double r2 = dx * dx + dy * dy + dz * dz;
-    const double r = sqrt(r2);
-    if (r < dc.rc && lj.y != 0.0) {
-        const double sr = lj.x / r;
-        const double sr2 = sr * sr;
-        const double r6 = sr2 * sr2 * sr2;
-        e_lj += lj.y * (r6 * r6 - r6);
-    }
-    if (charged) e_c += qa * qj * mmc_erfc(dc.alpha * r) / r;
-}
-
-__global__ void __launch_bounds__(PAIR_THREADS) k_pair_sweep(DevConst dc, ChainState cs, int chain0) {
-    __shared__ PairSmem sm;
-    const int c = blockIdx.y + chain0;
-    const Trial& t = cs.trial[c];
-    if (t.kind <= 0 || (!t.do_old && !t.do_new)) return;  // uniform per block
-    if (threadIdx.x < t.nat) {
-        const int a = threadIdx.x;
-        sm.px_o[a] = t.p_old[a][0]; sm.py_o[a] = t.p_old[a][1]; sm.pz_o[a] = t.p_old[a][2];
-        sm.px_n[a] = t.p_new[a][0]; sm.py_n[a] = t.p_new[a][1]; sm.pz_n[a] = t.p_new[a][2];
-        sm.q[a] = t.q[a]; sm.type[a] = t.type[a];
-    }
-    if (threadIdx.x == 0) { sm.nat = t.nat; sm.do_old = t.do_old; sm.do_new = t.do_new; sm.kind = t.kind; }
-    __syncthreads();
-    const int j = blockIdx.x * PAIR_THREADS + threadIdx.x;
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    bool valid = false; double xj = 0, yj = 0, zj = 0, qj = 0; int tj = 0;
-    if (j < dc.n_fw) {
-        valid = true; xj = dc.fx[j]; yj = dc.fy[j]; zj = dc.fz[j]; qj = dc.fq[j]; tj = dc.ftype[j];
-    } else if (j < dc.n_fw + dc.g_atoms) {
-        const int g = j - dc.n_fw;
-        // which active residue / slot does guest atom g belong to
-        int r = 0;
-#pragma unroll 1
-        for (int i = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (g >= dc.g_atom_base[rr]) r = rr; }
-        const int na = dc.natoms[r];
-        const int m = (g - dc.g_atom_base[r]) / na, a = (g - dc.g_atom_base[r]) % na;
-        if (m < cs.count[c * MMC_MAX_RES + r] && !(t.excl && r == t.res && m == t.mol)) {
-            valid = true;
-            const size_t ia = (size_t)c * dc.g_atoms + g;
-            xj = cs.gx[ia]; yj = cs.gy[ia]; zj = cs.gz[ia]; qj = dc.q[r][a]; tj = dc.type[r][a];
-        }
-    }
-    if (valid) {
-        const bool qj_ok = fabs(qj) >= MMC_ERR;
-        const int nat = sm.nat;
-        for (int a = 0; a < nat; a++) {
-            const double qa = sm.q[a];
-            const bool charged = qj_ok && fabs(qa) >= MMC_ERR;
-            const double2 lj = dc.lj[sm.type[a] * dc.ntypes + tj];
-            // ComputeDistance: delta = pos(other) - pos(moved)
-            if (sm.do_old) pair_eval(dc, xj - sm.px_o[a], yj - sm.py_o[a], zj - sm.pz_o[a], qa, qj, lj, charged, acc[0], acc[1]);
-            if (sm.do_new) pair_eval(dc, xj - sm.px_n[a], yj - sm.py_n[a], zj - sm.pz_n[a], qa, qj, lj, charged, acc[2], acc[3]);
-        }
-    }
-    block_sum<4, PAIR_THREADS>(acc, sm.red);
-    if (threadIdx.x == 0) {
-        double* out = cs.pair_part + ((size_t)c * dc.n_pair_tiles + blockIdx.x) * 4;
-        out[0] = acc[0]; out[1] = acc[1]; out[2] = acc[2]; out[3] = acc[3];
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// Reciprocal sweep: ComputeRecipEnergySingleMol (ewald_energy.f90:191-274), parallel over k.
-// grid = (n_k_tiles, n_chains), block = RECIP_THREADS; one k-vector per thread.  Reads the current
-// A(k), writes A'(k) into the other half of the double buffer (replaces the K-length copies of
-// Save/RestoreSingleMolFourier, ewald_phase.f90:179-181,249-251) and accumulates both
-// sum f W |A|^2 (the reference's "old" call, a no-op update) and sum f W |A'|^2.
-// The moved molecule's 1-D phase tables (built once per trial by build_phase_tables) are staged in
-// shared memory.  HBM traffic per k-eval: 16 B read + 16 B write + 8 B fW + 16 B kvec.
-__device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
-__device__ __forceinline__ double2 ph_at(const double2* tab, int k) {  // negative k by conjugation (ewald_phase.f90:105-107)
-    double2 v = tab[k < 0 ? -k : k];
-    if (k < 0) v.y = -v.y;
-    return v;
-}
-
-__global__ void __launch_bounds__(RECIP_THREADS) k_recip_sweep(DevConst dc, ChainState cs, int chain0) {
-    extern __shared__ double2 s_ph[];  // [2][3][nat][kstride]
-    __shared__ double red[2 * RECIP_THREADS / 32];
-    const int c = blockIdx.y + chain0;
-    const Trial& t = cs.trial[c];
-    if (t.kind <= 0) return;
-    const int nat = t.nat, ks = dc.kstride;
-    const bool plus = t.r_plus, minus = t.r_minus;
-    const double2* gph = cs.phase + (size_t)c * 2 * 3 * MMC_MAX_MOL_ATOMS * ks;
-    for (int i = threadIdx.x; i < 2 * 3 * nat * ks; i += blockDim.x) {
-        const int k = i % ks, a = (i / ks) % nat, sa = i / (ks * nat);  // sa = set*3+axis
-        s_ph[i] = gph[((size_t)sa * MMC_MAX_MOL_ATOMS + a) * ks + k];
-    }
-    __syncthreads();
-    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
-    double acc[2] = {0.0, 0.0};
-    if (ik < dc.nk) {
-        const int cur = cs.cur[c];
-        const double2* A = cs.A + ((size_t)c * 2 + cur) * dc.nk;
-        double2* An = cs.A + ((size_t)c * 2 + (cur ^ 1)) * dc.nk;
-        const int4 kv = dc.kvec[ik];
-        double sre = 0.0, sim = 0.0;
-        for (int a = 0; a < nat; a++) {
-            double2 pn = make_double2(0.0, 0.0), po = make_double2(0.0, 0.0);
-            if (plus) pn = cmul(cmul(ph_at(s_ph + ((0 * 3 + 0) * nat + a) * ks, kv.x), ph_at(s_ph + ((0 * 3 + 1) * nat + a) * ks, kv.y)),
-                                ph_at(s_ph + ((0 * 3 + 2) * nat + a) * ks, kv.z));
-            if (minus) po = cmul(cmul(ph_at(s_ph + ((1 * 3 + 0) * nat + a) * ks, kv.x), ph_at(s_ph + ((1 * 3 + 1) * nat + a) * ks, kv.y)),
-                                 ph_at(s_ph + ((1 * 3 + 2) * nat + a) * ks, kv.z));
-            const double q = t.q[a];
-            sre += q * (pn.x - po.x); sim += q * (pn.y - po.y);
-        }
-        const double2 a0 = A[ik];
-        const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
-        An[ik] = a1;
-        const double w = dc.fw[ik];
-        acc[0] = w * (a0.x * a0.x + a0.y * a0.y);  // amplitude_squared helper_utils.f90:125
-        acc[1] = w * (a1.x * a1.x + a1.y * a1.y);
-    }
-    block_sum<2, RECIP_THREADS>(acc, red);
-    if (threadIdx.x == 0) {
-        double* out = cs.recip_part + ((size_t)c * dc.n_k_tiles + blockIdx.x) * 2;
-        out[0] = acc[0]; out[1] = acc[1];
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
 // ComputeIntraResidueRealCoulombEnergySingleMol ewald_energy.f90:371-411 on explicit positions
 __device__ inline double intra_energy(const DevConst& dc, int nat, const double* q, const double (*p)[3]) {
     double e = 0.0;
@@ -353,23 +188,12 @@ __device__ inline double intra_energy(const DevConst& dc, int nat, const double*
     return e * dc.coul_const;
 }
 
-// Sums the per-block partials in a fixed order and assembles type(energy_state) old/new exactly as
-// ComputeOldEnergy / ComputeNewEnergy do for each move type (monte_carlo_utils.f90:275-396).
-// All threads of the block participate; results land in the Trial (thread 0).
-__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, double* red) {
+// Assembles type(energy_state) old/new from the six sweep sums exactly as ComputeOldEnergy /
+// ComputeNewEnergy do for each move type (monte_carlo_utils.f90:275-396) and the acceptance probability.
+// v = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2}.  Single thread.
+__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, const double* v) {
     Trial& t = cs.trial[c];
     if (t.kind <= 0) return;
-    double v[6] = {0, 0, 0, 0, 0, 0};
-    if (t.do_old || t.do_new) {
-        const double* pp = cs.pair_part + (size_t)c * dc.n_pair_tiles * 4;
-        for (int i = threadIdx.x; i < dc.n_pair_tiles; i += TAIL_THREADS) {
-            v[0] += pp[i * 4 + 0]; v[1] += pp[i * 4 + 1]; v[2] += pp[i * 4 + 2]; v[3] += pp[i * 4 + 3];
-        }
-    }
-    const double* rp = cs.recip_part + (size_t)c * dc.n_k_tiles * 2;
-    for (int i = threadIdx.x; i < dc.n_k_tiles; i += TAIL_THREADS) { v[4] += rp[i * 2 + 0]; v[5] += rp[i * 2 + 1]; }
-    block_sum<6, TAIL_THREADS>(v, red);
-    if (threadIdx.x != 0) return;
     const double lj_o = v[0], c_o = v[1] * dc.coul_const, lj_n = v[2], c_n = v[3] * dc.coul_const;
     const double rec_o = v[4] * dc.recip_const, rec_n = v[5] * dc.recip_const;
     double* o = t.old_e; double* n = t.new_e;
@@ -450,58 +274,29 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
     t.kind = -t.kind;
 }
 
-// strict mode: sums -> Trial.old_e/new_e ; the host reads them and decides
+// strict mode: sums the per-CTA partials of k_sweep in a fixed order -> Trial.old_e/new_e ; the host decides
 __global__ void __launch_bounds__(TAIL_THREADS) k_finalize(DevConst dc, ChainState cs, int chain, double* out /* 13 doubles */) {
     __shared__ double red[6 * TAIL_THREADS / 32];
-    finalize_trial(dc, cs, chain, red);
-    if (threadIdx.x == 0 && out) {
-        const Trial& t = cs.trial[chain];
-        for (int i = 0; i < MMC_NE; i++) { out[i] = t.old_e[i]; out[MMC_NE + i] = t.new_e[i]; }
-        out[2 * MMC_NE] = t.prob;
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    const double* pp = cs.part + (size_t)chain * dc.sweep_parts * 6;
+    for (int i = threadIdx.x; i < dc.sweep_parts; i += TAIL_THREADS)
+        for (int k = 0; k < 6; k++) v[k] += pp[i * 6 + k];
+    block_sum<6, TAIL_THREADS>(v, red);
+    if (threadIdx.x == 0) {
+        finalize_trial(dc, cs, chain, v);
+        if (out) {
+            const Trial& t = cs.trial[chain];
+            for (int i = 0; i < MMC_NE; i++) { out[i] = t.old_e[i]; out[MMC_NE + i] = t.new_e[i]; }
+            out[2 * MMC_NE] = t.prob;
+        }
     }
 }
 __global__ void k_commit(DevConst dc, ChainState cs, int chain, int accept) {
     if (threadIdx.x == 0) commit_trial(dc, cs, chain, accept);
 }
 
-// batched mode tail: finalize step s-1 (Metropolis test, commit, record), then propose step s.
-// grid = n_chains blocks.  first = 1: only propose (start of a chunk); last = 1: only finish.
 struct BatchCtl { RngSrc rng; mmc_move_record* recs; long long rec_stride; long long rec_base; };
 
-__global__ void __launch_bounds__(TAIL_THREADS) k_step_tail(DevConst dc, ChainState cs, const BatchCtl* ctl, int s, int first, int last) {
-    __shared__ double red[6 * TAIL_THREADS / 32];
-    const int c = blockIdx.x;
-    RngSrc rs = ctl->rng;
-    rs.step += (unsigned long long)s;
-    if (!first) {
-        finalize_trial(dc, cs, c, red);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            Trial& t = cs.trial[c];
-            const int kind = t.kind;
-            if (kind > 0) {
-                RngSrc prev = rs; prev.step = rs.step - 1;  // the accept draw belongs to the step being finished
-                Rng rng{&prev, cs, c, t.draw};
-                const double u = rng.next();
-                commit_trial(dc, cs, c, u <= t.prob ? 1 : 0);
-            }
-            if (ctl->recs) {
-                mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + s - 1];
-                rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
-                rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
-                for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
-            }
-        }
-        __syncthreads();
-    }
-    if (last) return;
-    if (threadIdx.x == 0) {
-        propose_move(dc, cs, rs, c);
-        if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
-    }
-    __syncthreads();
-    build_phase_tables(dc, cs, c);
-}
 // positions = COM + offset for every guest slot of every chain (after a bulk upload); grid = (tiles, n_chains)
 __global__ void k_rebuild_positions(DevConst dc, ChainState cs) {
     const int c = blockIdx.y, g = blockIdx.x * blockDim.x + threadIdx.x;

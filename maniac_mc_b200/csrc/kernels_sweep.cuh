@@ -1,0 +1,319 @@
+// kernels_sweep.cuh -- the two sweeps of one trial move, written once and used by both drivers:
+//   * strict mode  : k_sweep, dc.sweep_parts CTAs share one chain's trial (whole GPU on one move)
+//   * batched mode : k_chain_run (kernels_chain.cuh), one CTA owns a chain and loops over MC steps
+//
+// Real-space sweep = ComputePairInteractionEnergy_singlemol (energy_utils.f90:374-442) for the old and
+// the proposed geometry in ONE pass.  The framework is stored in Morton order in tiles of 32 atoms with a
+// bounding box each; a tile is visited only if it can hold an atom within `reach` of the moved molecule
+// (reach = max(r_c, x_cut/alpha): LJ needs r < r_c, and erfc(alpha r) < erfc(x_cut) ~ 4e-20 beyond it, which is
+// below one ulp of the sums the reference forms over ALL minimum-image pairs, Q3).  With culling disabled
+// (reach2 = inf) every pair is evaluated exactly as the reference does.
+//
+// Reciprocal sweep = ComputeRecipEnergySingleMol (ewald_energy.f90:191-274), parallel over k:
+// A'(k) = A(k) + sum_terms X_t(kx) Y_t(ky) qZ_t(kz), terms = atoms added (+q) and atoms removed (-q);
+// the 1-D tables (ComputePhaseFactors1D, ewald_phase.f90:90-109) live in shared memory, extended to negative
+// k by conjugation as the reference does (:105-107).
+#pragma once
+#include "common.cuh"
+
+// moved molecule staged in shared memory
+struct MolS {
+    double po[MMC_MAX_MOL_ATOMS][3], pn[MMC_MAX_MOL_ATOMS][3];
+    double q[MMC_MAX_MOL_ATOMS];
+    double cen[2][4];   // bounding sphere {x, y, z, radius + reach} of the old / new geometry
+    int type[MMC_MAX_MOL_ATOMS];
+    int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
+};
+
+struct SweepCtx {
+    double* erfc;    // [(DEG+1) * NSEG]
+    double2* lj;     // [max_nat][ntypes] {sigma^2, 4 eps} rows of the moved molecule's atom types
+    double2 *X, *Y, *Z;  // [2 max_nat][nx | ny | nz]
+    uint32_t* mask;  // [CULL_CHUNK / 32]
+    int* prefix;     // [CULL_CHUNK / 32]
+    uint16_t* list;  // [CULL_CHUNK]
+    double* red;     // [6 * warps]
+    MolS* mol;
+    int nx, ny, nz;
+};
+
+__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[9]) {
+    size_t o = 0;
+    const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = 2 * kmax[2] + 1;
+    off[0] = o; o += (size_t)(MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG * sizeof(double);
+    off[1] = o; o += (size_t)max_nat * ntypes * sizeof(double2);
+    off[2] = o; o += (size_t)2 * max_nat * nx * sizeof(double2);
+    off[3] = o; o += (size_t)2 * max_nat * ny * sizeof(double2);
+    off[4] = o; o += (size_t)2 * max_nat * nz * sizeof(double2);
+    off[5] = o; o += (size_t)6 * (threads / 32) * sizeof(double);
+    off[6] = o; o += (sizeof(MolS) + 15) / 16 * 16;
+    off[7] = o; o += (CULL_CHUNK / 32) * sizeof(uint32_t) * 2;
+    off[8] = o; o += CULL_CHUNK * sizeof(uint16_t);
+    return o;
+}
+
+__device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned char* smem, int threads) {
+    size_t off[9];
+    sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
+    SweepCtx s;
+    s.erfc = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
+    s.X = (double2*)(smem + off[2]); s.Y = (double2*)(smem + off[3]); s.Z = (double2*)(smem + off[4]);
+    s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]);
+    s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
+    s.list = (uint16_t*)(smem + off[8]);
+    s.nx = dc.kmax[0] + 1; s.ny = 2 * dc.kmax[1] + 1; s.nz = 2 * dc.kmax[2] + 1;
+    return s;
+}
+
+// once per kernel: the erfcx coefficient table
+__device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const SweepCtx& s) {
+    for (int i = threadIdx.x; i < (MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG; i += blockDim.x) s.erfc[i] = dc.erfc_tab[i];
+}
+
+// Stages the pending Trial of chain c: positions, charges, LJ rows, bounding spheres and the 1-D phase
+// tables (ComputeAtomPhase + ComputePhaseFactors1D, ewald_phase.f90:41-109: direct cos/sin(k theta)).
+// All threads; ends with a barrier.
+__device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
+    const Trial& t = cs.trial[c];
+    MolS& m = *s.mol;
+    const int tid = threadIdx.x;
+    const int nat = t.nat;
+    if (tid == 0) {
+        m.nat = nat; m.kind = t.kind; m.do_old = t.do_old; m.do_new = t.do_new; m.excl = t.excl; m.res = t.res; m.mol = t.mol;
+        m.nterm = nat * ((t.r_plus ? 1 : 0) + (t.r_minus ? 1 : 0)); m.cur = cs.cur[c];
+    }
+    if (t.kind <= 0) { __syncthreads(); return; }
+    if (tid < nat) {
+        for (int d = 0; d < 3; d++) { m.po[tid][d] = t.p_old[tid][d]; m.pn[tid][d] = t.p_new[tid][d]; }
+        m.q[tid] = t.q[tid]; m.type[tid] = t.type[tid];
+    }
+    if (tid < 2) {  // bounding sphere of one geometry: centroid + largest distance + reach
+        const double (*p)[3] = tid == 0 ? t.p_old : t.p_new;
+        double cx = 0, cy = 0, cz = 0;
+        for (int a = 0; a < nat; a++) { cx += p[a][0]; cy += p[a][1]; cz += p[a][2]; }
+        cx /= nat; cy /= nat; cz /= nat;
+        double r2 = 0;
+        for (int a = 0; a < nat; a++) {
+            const double dx = p[a][0] - cx, dy = p[a][1] - cy, dz = p[a][2] - cz;
+            r2 = fmax(r2, dx * dx + dy * dy + dz * dz);
+        }
+        m.cen[tid][0] = cx; m.cen[tid][1] = cy; m.cen[tid][2] = cz; m.cen[tid][3] = sqrt(r2) * (1.0 + 1e-12) + dc.reach;
+    }
+    for (int i = tid; i < nat * dc.ntypes; i += blockDim.x) {
+        const int a = i / dc.ntypes, tj = i % dc.ntypes;
+        const double2 v = dc.lj[t.type[a] * dc.ntypes + tj];
+        s.lj[i] = make_double2(v.x * v.x, v.y);
+    }
+    // phase tables: term index = plus atoms first, then minus atoms (charge sign folded into Z)
+    const int nplus = t.r_plus ? nat : 0, nterm = nplus + (t.r_minus ? nat : 0);
+    const int per = s.nx + s.ny + s.nz;
+    for (int i = tid; i < nterm * per; i += blockDim.x) {
+        const int term = i / per; int j = i % per;
+        const bool plus = term < nplus;
+        const int a = plus ? term : term - nplus;
+        int ax, k; double2* dst;
+        if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
+        else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
+        else { j -= s.nx + s.ny; ax = 2; k = j - dc.kmax[2]; dst = s.Z + term * s.nz + j; }
+        const double pos = plus ? t.p_plus[a][ax] : t.p_old[a][ax];
+        const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
+        double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
+        if (k < 0) sn = -sn;
+        if (ax == 2) { const double q = plus ? t.q[a] : -t.q[a]; co *= q; sn *= q; }
+        *dst = make_double2(co, sn);
+    }
+    __syncthreads();
+}
+
+// ----------------------------------------------------------------------------------------------
+struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, alpha2, rc; };
+
+// one (moved atom, other atom) pair at one geometry
+__device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_erfc, double dx, double dy, double dz,
+                                         double qq, bool charged, double2 lj, double& e_lj, double& e_c) {
+    dx = min_image_fast(dx, pc.Lx, pc.iLx);
+    dy = min_image_fast(dy, pc.Ly, pc.iLy);
+    dz = min_image_fast(dz, pc.Lz, pc.iLz);
+    const double r2 = fma(dx, dx, fma(dy, dy, dz * dz));
+    if (r2 < pc.reach2) {
+        const double rinv = mmc_rsqrt(r2);
+        const double r = r2 * rinv;
+        if (charged) {
+            const double x = pc.alpha * r;
+            double ec;
+            if (x < MMC_ERFC_XMAX) ec = exp(-pc.alpha2 * r2) * mmc_erfcx_poly(x, s_erfc);
+            else ec = mmc_erfc_slow(x);
+            e_c = fma(qq * rinv, ec, e_c);
+        }
+        if (r < pc.rc && lj.y != 0.0) {
+            const double s2 = lj.x * (rinv * rinv);
+            const double s6 = s2 * s2 * s2;
+            e_lj = fma(lj.y, fma(s6, s6, -s6), e_lj);
+        }
+    }
+}
+
+// one "other" atom against every atom of the moved molecule, old and/or new geometry
+template <bool OLD, bool NEW>
+__device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
+                                          double qj, int tj, double (&acc)[4]) {
+    const MolS& m = *s.mol;
+    const bool qj_ok = fabs(qj) >= MMC_ERR;
+    const int nat = m.nat;
+#pragma unroll 2
+    for (int a = 0; a < nat; a++) {
+        const double qa = m.q[a];
+        const bool charged = qj_ok && fabs(qa) >= MMC_ERR;
+        const double qq = qa * qj;
+        const double2 lj = s.lj[a * ntypes + tj];
+        // ComputeDistance: delta = pos(other) - pos(moved)
+        if (OLD) pair_one(pc, s.erfc, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1]);
+        if (NEW) pair_one(pc, s.erfc, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3]);
+    }
+}
+
+// can tile `t` hold an atom within reach of the moved molecule?  periodic point-to-box distance per axis
+__device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m, int t, bool use_old, bool use_new) {
+    const double* b = dc.tbox + (size_t)t * 6;
+    const double bx = b[0], by = b[1], bz = b[2], hx = b[3], hy = b[4], hz = b[5];
+    bool hit = false;
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+        if (g == 0 ? !use_old : !use_new) continue;
+        const double dx = fmax(0.0, fabs(min_image_fast(m.cen[g][0] - bx, dc.L[0], dc.invL[0])) - hx);
+        const double dy = fmax(0.0, fabs(min_image_fast(m.cen[g][1] - by, dc.L[1], dc.invL[1])) - hy);
+        const double dz = fmax(0.0, fabs(min_image_fast(m.cen[g][2] - bz, dc.L[2], dc.invL[2])) - hz);
+        const double R = m.cen[g][3];
+        hit = hit || (dx * dx + dy * dy + dz * dz <= R * R);
+    }
+    return hit;
+}
+
+// ----------------------------------------------------------------------------------------------
+// Real-space phase of one trial.  Work items = framework tiles in reach (ordered compaction of the cull
+// result, so the item -> warp assignment and hence the summation order is deterministic) followed by tiles
+// of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
+template <int NT, bool OLD, bool NEW>
+__device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                    double (&acc)[4]) {
+    const MolS& m = *s.mol;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
+    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.alpha2, dc.rc};
+    const bool cull = dc.reach2 < 1e300;
+    int item0 = 0;
+    for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
+        const int n = min(CULL_CHUNK, dc.n_tiles - base);
+        const int nwords = (n + 31) >> 5;
+        for (int i0 = warp * 32; i0 < n; i0 += NT) {
+            const int i = i0 + lane;
+            const bool hit = i < n && (!cull || tile_in_reach(dc, m, base + i, OLD, NEW));
+            const unsigned b = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) s.mask[i0 >> 5] = b;
+        }
+        __syncthreads();
+        if (warp == 0) {  // exclusive prefix of the per-word counts
+            int run = 0;
+            for (int w0 = 0; w0 < nwords; w0 += 32) {
+                const int w = w0 + lane;
+                const int cnt = w < nwords ? __popc(s.mask[w]) : 0;
+                int inc = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+                if (w < nwords) s.prefix[w] = run + inc - cnt;
+                run += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) s.mol->nlist = run;
+        }
+        __syncthreads();
+        for (int i0 = warp * 32; i0 < n; i0 += NT) {
+            const unsigned b = s.mask[i0 >> 5];
+            if ((b >> lane) & 1u) s.list[s.prefix[i0 >> 5] + __popc(b & ((1u << lane) - 1u))] = (uint16_t)(i0 + lane);
+        }
+        __syncthreads();
+        const int nlist = m.nlist;
+        for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
+            const int j = (base + (int)s.list[it]) * TILE + lane;
+            if (j < dc.n_fw) pair_atom<OLD, NEW>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc);
+        }
+        item0 += nlist;
+        __syncthreads();  // list is rebuilt by the next chunk
+    }
+    // guests of this chain: slots [0, count) of every active residue, the moved slot excluded
+    for (int ia = 0; ia < dc.n_active; ia++) {
+        const int r = dc.active_list[ia], na = dc.natoms[r];
+        const int n_at = cs.count[c * MMC_MAX_RES + r] * na;
+        const int ntile = (n_at + 31) >> 5;
+        const size_t base = (size_t)c * dc.g_atoms + dc.g_atom_base[r];
+        for (int it = (gw + gstride - item0 % gstride) % gstride; it < ntile; it += gstride) {
+            const int i = it * 32 + lane;
+            if (i < n_at) {
+                const int mol = i / na, a = i - mol * na;
+                if (!(m.excl && r == m.res && mol == m.mol))
+                    pair_atom<OLD, NEW>(pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
+                                        dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc);
+            }
+        }
+        item0 += ntile;
+    }
+}
+
+template <int NT>
+__device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                  double (&acc)[4]) {
+    const MolS& m = *s.mol;
+    if (m.kind <= 0) return;
+    if (m.do_old && m.do_new) pair_phase_t<NT, true, true>(dc, cs, c, s, part, n_parts, acc);
+    else if (m.do_old) pair_phase_t<NT, true, false>(dc, cs, c, s, part, n_parts, acc);
+    else if (m.do_new) pair_phase_t<NT, false, true>(dc, cs, c, s, part, n_parts, acc);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Reciprocal phase: this part's contiguous share of the k list, one k per thread per pass (coalesced A
+// read, A' write into the other half of the double buffer).  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
+template <int NT>
+__device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                   double (&acc)[2]) {
+    const MolS& m = *s.mol;
+    if (m.kind <= 0) return;
+    const int nterm = m.nterm, nx = s.nx, ny = s.ny, nz = s.nz;
+    const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
+    double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
+    const int per = (((dc.nk + n_parts - 1) / n_parts) + 31) & ~31;
+    const int k0 = part * per, k1 = min(dc.nk, k0 + per);
+    for (int k = k0 + threadIdx.x; k < k1; k += NT) {
+        const uint32_t kp = dc.kpack[k];
+        const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, iz = kp >> 21;
+        const double2 a0 = A[k];
+        const double w = dc.fw[k];
+        double sre = 0.0, sim = 0.0;
+        for (int t = 0; t < nterm; t++) {
+            const double2 X = s.X[t * nx + ix], Y = s.Y[t * ny + iy], Z = s.Z[t * nz + iz];
+            const double xr = fma(X.x, Y.x, -X.y * Y.y), xi = fma(X.x, Y.y, X.y * Y.x);
+            sre = fma(xr, Z.x, sre); sre = fma(-xi, Z.y, sre);
+            sim = fma(xr, Z.y, sim); sim = fma(xi, Z.x, sim);
+        }
+        const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
+        An[k] = a1;
+        acc[0] = fma(w, fma(a0.x, a0.x, a0.y * a0.y), acc[0]);  // amplitude_squared helper_utils.f90:125
+        acc[1] = fma(w, fma(a1.x, a1.x, a1.y * a1.y), acc[1]);
+    }
+}
+
+// strict mode: grid = dc.sweep_parts CTAs on the pending trial of chain c; partial sums -> cs.part
+__global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState cs, int c) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
+    sweep_load_tables(dc, s);
+    sweep_stage(dc, cs, c, s);
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
+    double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
+    pair_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, pa);
+    recip_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, ra);
+    block_sum<6, SWEEP_THREADS>(v, s.red);
+    if (threadIdx.x == 0) {
+        double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
+        for (int i = 0; i < 6; i++) out[i] = v[i];
+    }
+}

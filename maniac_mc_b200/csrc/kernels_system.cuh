@@ -233,9 +233,9 @@ __global__ void k_table_lookup(DevConst dc, int which, const double* r, int n, d
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = table_lookup(which == 0 ? dc.tab_erfc : which == 1 ? dc.tab_r6 : dc.tab_r12, dc.tab_dx, r[i]);
 }
-__global__ void k_erfc_test(const double* x, int n, double* out) {
+__global__ void k_erfc_test(const double* tab, const double* x, int n, double* out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = mmc_erfc(x[i]);
+    if (i < n) out[i] = mmc_erfc(x[i], tab);
 }
 
 // FP64 peak: 8 independent DFMA chains per thread, register resident

@@ -10,7 +10,11 @@
 
 #include "common.cuh"
 #include "kernels_move.cuh"
+#include "kernels_sweep.cuh"
+#include "kernels_chain.cuh"
 #include "kernels_system.cuh"
+#include <algorithm>
+#include <numeric>
 
 static thread_local std::string g_err;
 static int fail(const char* fmt, ...) {
@@ -31,7 +35,10 @@ struct mmc_handle {
     int init_sk = 0;
     int n_fw_mols = 0;
     int sk_chunk = SK_CHUNK;
-    size_t recip_smem = 0, sk_smem = 0;
+    size_t sk_smem = 0;
+    size_t sweep_smem = 0, chain_smem = 0;  // dynamic shared memory of k_sweep / k_chain_run
+    int chain_threads = 256;                // CTA size of k_chain_run (256 x4, 512 x2 or 1024 x1 per SM)
+    int n_sm = 148;
     std::vector<void*> allocs;
     std::vector<int> h_res_is_fw;          // per residue: 1 = inactive (framework)
     std::vector<int> h_kx, h_ky, h_kz;
@@ -153,6 +160,111 @@ static int upload_chain(mmc_handle* h, int c, const int* count, const double* co
     return 0;
 }
 
+// Layout of the per-move sweeps (kernels_sweep.cuh): framework atoms in Morton order of their cell in
+// tiles of 32 with a bounding box each, the packed k list, the erfcx table, the real-space reach, and
+// the launch configuration of k_sweep / k_chain_run.
+static uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) {
+    auto spread = [](uint32_t v) { uint32_t r = 0; for (int b = 0; b < 10; b++) r |= ((v >> b) & 1u) << (3 * b); return r; };
+    return spread(x) | (spread(y) << 1) | (spread(z) << 2);
+}
+static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
+    DevConst& dc = h->dc;
+    const size_t n = (size_t)dc.n_fw;
+    std::vector<double> fx(n + 1), fy(n + 1), fz(n + 1), fq(n + 1); std::vector<int> ft(n + 1);
+    if (n) {
+        CK(cudaMemcpy(fx.data(), dc.fx, n * 8, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(fy.data(), dc.fy, n * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(fz.data(), dc.fz, n * 8, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(fq.data(), dc.fq, n * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(ft.data(), dc.ftype, n * 4, cudaMemcpyDeviceToHost));
+    }
+    int bits = 1;
+    while (bits < 10 && (1u << (3 * bits)) * 2 < n) bits++;   // about two atoms per cell
+    const uint32_t ncell = 1u << bits;
+    std::vector<double> wx(n), wy(n), wz(n);  // wrapped into [lo, lo + L)
+    std::vector<uint32_t> code(n); std::vector<int> order(n);
+    auto wrap = [&](double x, int ax) { double u = (x - dc.lo[ax]) / dc.L[ax]; u -= std::floor(u); if (u >= 1.0) u = 0.0; return u; };
+    for (size_t j = 0; j < n; j++) {
+        const double ux = wrap(fx[j], 0), uy = wrap(fy[j], 1), uz = wrap(fz[j], 2);
+        wx[j] = dc.lo[0] + ux * dc.L[0]; wy[j] = dc.lo[1] + uy * dc.L[1]; wz[j] = dc.lo[2] + uz * dc.L[2];
+        auto cell = [&](double u) { uint32_t c = (uint32_t)(u * ncell); return c >= ncell ? ncell - 1 : c; };
+        code[j] = morton3(cell(ux), cell(uy), cell(uz));
+    }
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return code[a] < code[b]; });
+    const int n_tiles = (int)((n + TILE - 1) / TILE);
+    const size_t np = (size_t)n_tiles * TILE;
+    std::vector<double> sx(np + 1, 0.0), sy(np + 1, 0.0), sz(np + 1, 0.0), sq(np + 1, 0.0), tbox((size_t)n_tiles * 6 + 1, 0.0);
+    std::vector<int> st(np + 1, 0);
+    for (int t = 0; t < n_tiles; t++) {
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (int l = 0; l < TILE; l++) {
+            const size_t i = (size_t)t * TILE + l;
+            if (i >= n) break;
+            const int j = order[i];
+            sx[i] = fx[j]; sy[i] = fy[j]; sz[i] = fz[j]; sq[i] = fq[j]; st[i] = ft[j];
+            const double w[3] = {wx[j], wy[j], wz[j]};
+            for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], w[k]); hi[k] = std::max(hi[k], w[k]); }
+        }
+        for (int k = 0; k < 3; k++) {
+            tbox[(size_t)t * 6 + k] = 0.5 * (lo[k] + hi[k]);
+            tbox[(size_t)t * 6 + 3 + k] = 0.5 * (hi[k] - lo[k]) * (1.0 + 1e-12) + 1e-9;   // never under-estimate the box
+        }
+    }
+    double *px, *py, *pz, *pq, *pb, *pe, *prq; int *pt, *prt; uint32_t* pk;
+    CK(dalloc(h, &px, np)); CK(dalloc(h, &py, np)); CK(dalloc(h, &pz, np)); CK(dalloc(h, &pq, np)); CK(dalloc(h, &pt, np));
+    CK(dalloc(h, &pb, (size_t)n_tiles * 6));
+    if (np) {
+        CK(cudaMemcpy(px, sx.data(), np * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(py, sy.data(), np * 8, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(pz, sz.data(), np * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(pq, sq.data(), np * 8, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(pt, st.data(), np * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(pb, tbox.data(), (size_t)n_tiles * 6 * 8, cudaMemcpyHostToDevice));
+    }
+    dc.sx = px; dc.sy = py; dc.sz = pz; dc.sq = pq; dc.stype = pt; dc.tbox = pb; dc.n_tiles = n_tiles;
+    const size_t ne = (size_t)(MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG;
+    CK(dalloc(h, &pe, ne)); CK(cudaMemcpy(pe, h_erfc_table, ne * 8, cudaMemcpyHostToDevice));
+    dc.erfc_tab = pe;
+    {   // per-residue charge / type rows for the guest part of the sweep
+        std::vector<double> rq(MMC_MAX_RES * MMC_MAX_MOL_ATOMS, 0.0); std::vector<int> rt(MMC_MAX_RES * MMC_MAX_MOL_ATOMS, 0);
+        for (int r = 0; r < dc.nres; r++) if (dc.is_active[r])
+            for (int a = 0; a < dc.natoms[r]; a++) { rq[r * MMC_MAX_MOL_ATOMS + a] = dc.q[r][a]; rt[r * MMC_MAX_MOL_ATOMS + a] = dc.type[r][a]; }
+        CK(dalloc(h, &prq, rq.size())); CK(dalloc(h, &prt, rt.size()));
+        CK(cudaMemcpy(prq, rq.data(), rq.size() * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(prt, rt.data(), rt.size() * 4, cudaMemcpyHostToDevice));
+        dc.res_q = prq; dc.res_type = prt;
+    }
+    {   // table indices of every k-vector: ix = kx, iy = ky + kmax_y, iz = kz + kmax_z
+        std::vector<uint32_t> kp(dc.nk);
+        for (int i = 0; i < dc.nk; i++)
+            kp[i] = (uint32_t)h->h_kx[i] | ((uint32_t)(h->h_ky[i] + dc.kmax[1]) << 10) | ((uint32_t)(h->h_kz[i] + dc.kmax[2]) << 21);
+        CK(dalloc(h, &pk, kp.size())); CK(cudaMemcpy(pk, kp.data(), kp.size() * 4, cudaMemcpyHostToDevice));
+        dc.kpack = pk;
+    }
+    // reach of the real-space sweep
+    bool any_charge = false;
+    for (size_t j = 0; j < n; j++) if (std::fabs(fq[j]) >= MMC_ERR) any_charge = true;
+    for (int r = 0; r < dc.nres; r++) if (dc.is_active[r]) for (int a = 0; a < dc.natoms[r]; a++) if (std::fabs(dc.q[r][a]) >= MMC_ERR) any_charge = true;
+    dc.rc2 = dc.rc * dc.rc; dc.alpha2 = dc.alpha * dc.alpha;
+    double xcut = d->coulomb_xcut == 0.0 ? 6.5 : d->coulomb_xcut;
+    if (xcut > MMC_ERFC_XMAX) xcut = MMC_ERFC_XMAX;
+    if (xcut < 0.0) { dc.reach = 1e200; dc.reach2 = INFINITY; }
+    else { dc.reach = any_charge ? std::max(dc.rc, xcut / dc.alpha) : dc.rc; dc.reach2 = dc.reach * dc.reach; }
+    // launch configuration
+    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, h->device));
+    h->n_sm = prop.multiProcessorCount;
+    const int work = std::max((dc.nk + 511) / 512, (n_tiles + dc.g_atoms / TILE + 15) / 16);
+    dc.sweep_parts = std::max(1, std::min(2 * h->n_sm, work));
+    size_t off[9];
+    h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, SWEEP_THREADS, off);
+    h->chain_threads = dc.n_chains >= 3 * h->n_sm ? 256 : dc.n_chains >= 3 * h->n_sm / 2 ? 512 : 1024;
+    h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
+    if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
+                                                 dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
+    CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
+    CK(cudaFuncSetAttribute(k_chain_run<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    CK(cudaFuncSetAttribute(k_chain_run<512, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    CK(cudaFuncSetAttribute(k_chain_run<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    CK(dalloc(h, &h->cs.part, (size_t)dc.n_chains * dc.sweep_parts * 6));
+    return 0;
+}
+
 extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     if (!out || !d) return fail("mmc_init: null argument");
     *out = nullptr;
@@ -216,7 +328,6 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
         }
     }
     dc.g_atoms = g_atoms > 0 ? g_atoms : 1; dc.g_mols = g_mols > 0 ? g_mols : 1; dc.n_fw = (int)n_fw; h->n_fw_mols = n_fw_mols;
-    dc.n_pair_tiles = (int)((n_fw + dc.g_atoms + PAIR_THREADS - 1) / PAIR_THREADS);
     // framework SoA (absolute positions com + offset, as ComputeDistance forms them, geometry_utils.f90:379-382)
     {
         std::vector<double> fx(n_fw + 1), fy(n_fw + 1), fz(n_fw + 1), fq(n_fw + 1); std::vector<int> ft(n_fw + 1), fm(n_fw + 1);
@@ -289,8 +400,6 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
     CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
     CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
-    CKB(dalloc(h, &cs.phase, C * 2 * 3 * MMC_MAX_MOL_ATOMS * dc.kstride));
-    CKB(dalloc(h, &cs.pair_part, C * dc.n_pair_tiles * 4)); CKB(dalloc(h, &cs.recip_part, C * dc.n_k_tiles * 2));
     CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.error_flag, 1));
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
@@ -324,11 +433,9 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &ss.result, 8));
     int max_nat = 1;
     for (int i = 0; i < dc.n_active; i++) if (dc.natoms[dc.active_list[i]] > max_nat) max_nat = dc.natoms[dc.active_list[i]];
-    h->recip_smem = (size_t)2 * 3 * max_nat * dc.kstride * sizeof(double2);
-    if (h->recip_smem > 48 * 1024) {
-        if (h->recip_smem > 200 * 1024) BAIL("kmax=%d too large for the shared-memory phase tables", kmaxmax);
-        CKB(cudaFuncSetAttribute(k_recip_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->recip_smem));
-    }
+    dc.max_nat = max_nat;
+    if (dc.kmax[0] > 1023 || dc.kmax[1] > 511 || dc.kmax[2] > 511) BAIL("kmax too large for the packed k-vector list");
+    if (build_sweep_layout(h, d)) { std::string keep = g_err; mmc_destroy(h); g_err = keep; return 1; }
     CKB(cudaStreamSynchronize(h->stream));
     CKB(cudaGetLastError());
     *out = h;
@@ -509,10 +616,9 @@ extern "C" int mmc_system_energy(mmc_t* h, int c, double out[MMC_NE]) {
 }
 
 // ---------------------------------------------------------------------------------------------
-static void launch_sweeps(mmc_handle* h, cudaStream_t st, int chain0, int n_chains) {
-    k_pair_sweep<<<dim3(h->dc.n_pair_tiles, n_chains), PAIR_THREADS, 0, st>>>(h->dc, h->cs, chain0);
-    k_recip_sweep<<<dim3(h->dc.n_k_tiles, n_chains), RECIP_THREADS, h->recip_smem, st>>>(h->dc, h->cs, chain0);
-    h->launches += 2;
+static void launch_sweeps(mmc_handle* h, cudaStream_t st, int chain) {
+    k_sweep<<<h->dc.sweep_parts, SWEEP_THREADS, h->sweep_smem, st>>>(h->dc, h->cs, chain);
+    h->launches += 1;
 }
 
 // ---- strict mode ------------------------------------------------------------------------------
@@ -539,7 +645,7 @@ extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, con
     }
     cudaStream_t st = h->stream;
     k_set_trial<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht);
-    launch_sweeps(h, st, c, 1);
+    launch_sweeps(h, st, c);
     k_finalize<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, c, h->d_out);
     h->launches += 2;
     CK(cudaGetLastError());
@@ -569,15 +675,16 @@ extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
 // ---- batched mode -------------------------------------------------------------------------------
 #define GRAPH_CHUNK 128
 
-static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
+// one launch of the chain-per-CTA kernel: every chain advances n steps
+static void launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases) {
     const int C = h->dc.n_chains;
-    k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, 0, 1, 0);
+    if (h->chain_threads == 256) k_chain_run<256, 4><<<C, 256, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    else if (h->chain_threads == 512) k_chain_run<512, 2><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    else k_chain_run<1024, 1><<<C, 1024, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
     h->launches++;
-    for (int s = 0; s < n; s++) {
-        launch_sweeps(h, st, 0, C);
-        k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, s + 1, 0, s == n - 1 ? 1 : 0);
-        h->launches++;
-    }
+}
+static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
+    launch_chain_run(h, st, n, 3);
     k_advance<<<1, 1, 0, st>>>(h->d_ctl, n);
     h->launches++;
 }
@@ -606,7 +713,7 @@ static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const do
         }
         while (n_steps - done >= GRAPH_CHUNK) {
             CK(cudaGraphLaunch(h->graph, st));
-            h->launches += 3 * GRAPH_CHUNK + 2;
+            h->launches += 2;
             done += GRAPH_CHUNK;
         }
     }
@@ -636,33 +743,31 @@ extern "C" int mmc_profile_kernels(mmc_t* h, int n_steps, uint64_t seed, double 
     if (!h || !ms || !n) return fail("mmc_profile_kernels: null argument");
     if (n_steps < 1 || n_steps > 4096) return fail("mmc_profile_kernels: n_steps must be in [1,4096]");
     CK(cudaSetDevice(h->device));
-    cudaStream_t st = h->stream; const int C = h->dc.n_chains;
+    cudaStream_t st = h->stream;
     BatchCtl ctl;
     ctl.rng.tape = nullptr; ctl.rng.tape_stride = 0; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
     ctl.recs = nullptr; ctl.rec_stride = n_steps; ctl.rec_base = 0;
     CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), st));
-    std::vector<cudaEvent_t> ev((size_t)n_steps * 4);
+    cudaEvent_t ev[4];
     for (auto& e : ev) CK(cudaEventCreate(&e));
-    k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, 0, 1, 0);
-    for (int s = 0; s < n_steps; s++) {
-        cudaEvent_t* e = &ev[(size_t)s * 4];
-        CK(cudaEventRecord(e[0], st));
-        k_pair_sweep<<<dim3(h->dc.n_pair_tiles, C), PAIR_THREADS, 0, st>>>(h->dc, h->cs, 0);
-        CK(cudaEventRecord(e[1], st));
-        k_recip_sweep<<<dim3(h->dc.n_k_tiles, C), RECIP_THREADS, h->recip_smem, st>>>(h->dc, h->cs, 0);
-        CK(cudaEventRecord(e[2], st));
-        k_step_tail<<<C, TAIL_THREADS, 0, st>>>(h->dc, h->cs, h->d_ctl, s + 1, 0, s == n_steps - 1 ? 1 : 0);
-        CK(cudaEventRecord(e[3], st));
+    // the same n_steps proposals three times: real-space phase only, reciprocal phase only (neither commits,
+    // so the chains do not move), then the full step, which does commit
+    const int phases[3] = {1, 2, 3};
+    mmc_counters* d_save = nullptr;   // the single-phase passes must not count as trial moves
+    CK(cudaMalloc((void**)&d_save, h->dc.n_chains * sizeof(mmc_counters)));
+    CK(cudaMemcpyAsync(d_save, h->cs.counters, h->dc.n_chains * sizeof(mmc_counters), cudaMemcpyDeviceToDevice, st));
+    for (int k = 0; k < 3; k++) {
+        if (k == 2) CK(cudaMemcpyAsync(h->cs.counters, d_save, h->dc.n_chains * sizeof(mmc_counters), cudaMemcpyDeviceToDevice, st));
+        CK(cudaEventRecord(ev[k], st));
+        launch_chain_run(h, st, n_steps, phases[k]);
     }
-    h->launches += 1 + 3 * (int64_t)n_steps;
+    CK(cudaEventRecord(ev[3], st));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
-    double acc[3] = {0, 0, 0};
-    for (int s = 0; s < n_steps; s++)
-        for (int k = 0; k < 3; k++) { float t = 0; CK(cudaEventElapsedTime(&t, ev[(size_t)s * 4 + k], ev[(size_t)s * 4 + k + 1])); acc[k] += t; }
+    for (int k = 0; k < 3; k++) { float t = 0; CK(cudaEventElapsedTime(&t, ev[k], ev[k + 1])); ms[k] = t; n[k] = 1; }
     for (auto& e : ev) cudaEventDestroy(e);
-    for (int k = 0; k < 3; k++) { ms[k] = acc[k] / n_steps; n[k] = n_steps; }
+    cudaFree(d_save);
     h->steps_done += (unsigned long long)n_steps;
     h->pending_chain = -1;
     return refresh_counts(h);
@@ -738,7 +843,7 @@ static int run_elementwise(mmc_handle* h, int which, const double* in, int n, do
     double *di = nullptr, *dout = nullptr;
     CK(cudaMalloc((void**)&di, n * sizeof(double))); CK(cudaMalloc((void**)&dout, n * sizeof(double)));
     CK(cudaMemcpy(di, in, n * sizeof(double), cudaMemcpyHostToDevice));
-    if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(di, n, dout);
+    if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc.erfc_tab, di, n, dout);
     else k_table_lookup<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, which, di, n, dout);
     h->launches++;
     cudaError_t e = cudaStreamSynchronize(h->stream);

@@ -34,6 +34,7 @@ class MmcDesc(C.Structure):
         ("translation_step", C.c_double), ("rotation_step", C.c_double),
         ("p_translation", C.c_double), ("p_rotation", C.c_double),
         ("init_sk", C.c_int), ("deletion_mode", C.c_int), ("use_table", C.c_int), ("device", C.c_int),
+        ("coulomb_xcut", C.c_double),
     ]
 
 
@@ -99,6 +100,7 @@ class System:
     init_sk: int = 0
     deletion_mode: int = 0
     use_table: int = 0
+    coulomb_xcut: float = 0.0   # 0 = library default (6.5), negative = evaluate every pair
     names: list = field(default_factory=list)
     ewald_tolerance: float = 1e-5
 
@@ -163,6 +165,7 @@ class System:
         d.translation_step, d.rotation_step = self.translation_step, self.rotation_step
         d.p_translation, d.p_rotation = self.p_translation, self.p_rotation
         d.init_sk, d.deletion_mode, d.use_table, d.device = self.init_sk, self.deletion_mode, self.use_table, device
+        d.coulomb_xcut = float(self.coulomb_xcut)
         d._keep = keep
         return d
 

@@ -60,7 +60,7 @@ def test_device_erfc_accuracy():
     g = ManiacGPU(load_system("lj_gas"))
     x = np.concatenate([np.linspace(0, 6.5, 20001), np.random.default_rng(0).random(20000) * 27.0])
     d = g.dbg_erfc(x); ref = erfc(x)
-    assert np.max(np.abs(d - ref)) < 2e-15
+    assert np.max(np.abs(d - ref)) < 5e-15   # piecewise erfcx fit: 3.1e-15 relative (tools/gen_erfc_table.py)
     m = x <= 6.0
     assert np.max(np.abs(d[m] - ref[m]) / ref[m]) < 1e-13
     g.close()
