@@ -9,7 +9,8 @@ Workload (config.workload = "c4_large_k"): BASELINE.json configs[3] -- synthetic
 inactive residue) + 200 rigid TIP4P guests per chain, L = 96 A, r_c = 12 A, Ewald tol 1e-6 -> K = 37 782
 k-vectors; `--chains` independent chains per GPU (isotherm: 64 log-spaced fugacities x replicas, configs[4]),
 `--moves` MC steps per chain per bench step, translation/rotation/insertion/deletion 0.4/0.4/0.1/0.1.
-One bench "step" = one batch: chains x moves trial moves (CUDA-graph replay of 128-step chunks).
+One bench "step" = one batch: chains x moves trial moves (chain-per-CTA kernel k_chain_run, 128 MC steps per launch,
+launches replayed from a CUDA graph).
 
 Multi-GPU: one process per GPU (torchrun); chains (pressure points x replicas) are dealt to ranks, no data-path
 collective; weak scaling (chains per GPU fixed).  The only collectives are the barrier and the MAX of
@@ -42,11 +43,11 @@ def parse_args():
     p.add_argument("--steps", type=int, default=5)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="own", choices=["own", "reference"])
-    p.add_argument("--chains", type=int, default=64, help="independent chains per GPU")
+    p.add_argument("--chains", type=int, default=592, help="independent chains per GPU (4 resident CTAs x 148 SMs)")
     p.add_argument("--moves", type=int, default=256, help="MC steps per chain per bench step")
     p.add_argument("--framework", type=int, default=50000)
     p.add_argument("--guests", type=int, default=200)
-    p.add_argument("--cpu-moves", type=int, default=8, help="moves per host thread per CPU sample/step")
+    p.add_argument("--cpu-moves", type=int, default=100, help="moves per host thread per reference-arm step; the cpu_baseline sample is 4x that")
     p.add_argument("--no-cpu-baseline", action="store_true")
     return p.parse_args()
 
@@ -286,17 +287,22 @@ def run_own(args, rank, world, local_rank):
     if rank != 0:
         gpu.close()
         return
-    # ---- roofline of the dominant kernel (rank 0): instrumented replay right after the timed region
+    # ---- roofline of the dominant kernel (rank 0): instrumented replay right after the timed region.
+    # mmc_profile_kernels runs the SAME 32 proposals of every chain three times with CUDA events on the library's
+    # stream: real-space phase only, reciprocal phase only (no commit), then the full k_chain_run launch.
+    PROF_STEPS = 32
     cp0 = counters()
-    prof = gpu.profile_kernels(32, seed=13)
+    counts0 = h_cnt.numpy()[:, 0].copy()
+    prof = gpu.profile_kernels(PROF_STEPS, seed=13)
     cp1 = counters()
     counts = h_cnt.numpy()[:, 0].copy()
     dprof = counters_delta(cp0, cp1)
-    evals = pair_evals_of(s, args, counts, dprof)
+    evals = pair_evals_of(s, args, 0.5 * (counts0 + counts), dprof)
+    nat = 4
     k_evals = sum(sum(d[k] for k in d if k.startswith("trial_")) for d in dprof) * float(gpu.nk)
+    k_flop = sum((d["trial_translations"] + d["trial_rotations"]) * (30.0 * nat + 5.0) +
+                 (d["trial_creations"] + d["trial_deletions"]) * (15.0 * nat + 5.0) for d in dprof) * float(gpu.nk)
     fp64_peak = lib.measure_fp64_peak(local_rank)
-    pair_tflops = evals * W_PAIR_FLOP / (prof["pair_ms"] * 1e-3 * prof["launches_each"]) / 1e12
-    recip_gbs = k_evals * B_K_BYTES / (prof["recip_ms"] * 1e-3 * prof["launches_each"]) / 1e9
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -304,18 +310,23 @@ def run_own(args, rank, world, local_rank):
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-    step_ms = prof["pair_ms"] + prof["recip_ms"] + prof["tail_ms"]
-    roofline = {"kernel": "k_pair_sweep", "bound": "fp64", "achieved": pair_tflops, "peak": fp64_peak, "unit": "TFLOP/s",
-                "frac": pair_tflops / fp64_peak, "traffic": None,
+    full_s, pair_s, recip_s = prof["tail_ms"] * 1e-3, prof["pair_ms"] * 1e-3, prof["recip_ms"] * 1e-3
+    tflops = (evals * W_PAIR_FLOP + k_flop) / full_s / 1e12
+    roofline = {"kernel": "k_chain_run (propose + real-space sweep + reciprocal sweep + accept/commit, %d MC steps per launch)" % PROF_STEPS,
+                "bound": "fp64", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak, "traffic": None,
                 "peak_source": "DFMA micro-benchmark run in this process (mmc_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
-                "algorithmic": f"{W_PAIR_FLOP:g} FP64 flop per pair-eval x pair-evals per launch",
-                "avg_launch_ms": prof["pair_ms"], "share_of_step": prof["pair_ms"] / step_ms,
-                "pair_evals_per_s": evals / (prof["pair_ms"] * 1e-3 * prof["launches_each"])}
-    roofline_recip = {"kernel": "k_recip_sweep", "bound": "hbm", "achieved": recip_gbs, "peak": hbm_peak, "unit": "GB/s",
+                "algorithmic": f"{W_PAIR_FLOP:g} flop x pair-evals (all minimum-image pairs of the reference loop, SURVEY 8d) + (30 natoms + 5) flop x "
+                               "k-evals per launch; tiles out of reach (alpha r > 6.5) are culled, so executed flops are lower",
+                "avg_launch_ms": prof["tail_ms"], "share_of_step": 1.0,
+                "pair_evals_per_s": evals / full_s, "k_evals_per_s": k_evals / full_s,
+                "phase_only_ms": {"real_space": prof["pair_ms"], "reciprocal": prof["recip_ms"], "full": prof["tail_ms"]},
+                "real_space_only_tflops": evals * W_PAIR_FLOP / pair_s / 1e12}
+    recip_gbs = k_evals * B_K_BYTES / full_s / 1e9
+    roofline_recip = {"kernel": "k_chain_run, reciprocal share", "bound": "hbm", "achieved": recip_gbs, "peak": hbm_peak, "unit": "GB/s",
                       "frac": recip_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
-                      "algorithmic": f"{B_K_BYTES:g} B per k-eval x k-evals per launch",
-                      "avg_launch_ms": prof["recip_ms"], "share_of_step": prof["recip_ms"] / step_ms,
-                      "k_evals_per_s": k_evals / (prof["recip_ms"] * 1e-3 * prof["launches_each"])}
+                      "algorithmic": f"{B_K_BYTES:g} B per k-eval x k-evals per launch (A read 16 + A' write 16 + f*W 8)",
+                      "avg_launch_ms": prof["tail_ms"],
+                      "reciprocal_only_gbs": k_evals * B_K_BYTES / recip_s / 1e9}
     dall = counters_delta(c0, c1)
     evals_timed = pair_evals_of(s, args, counts, dall)
     out = {"metric": "mc_trial_moves_per_s", "value": value, "unit": "moves/s", "n_gpus": world, "steps": args.steps,
@@ -325,15 +336,16 @@ def run_own(args, rank, world, local_rank):
            "e2e": {"value": e2e_value, "unit": "moves/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "call": "mmc_upload_chains + mmc_run_batch_async + mmc_download_chains per step, pinned host buffers"},
            "gpu_launches": int(launches), "roofline": roofline, "roofline_recip": roofline_recip,
-           "tail_avg_launch_ms": prof["tail_ms"], "clocks": clk, "mean_guests_per_chain": float(counts.mean())}
+           "clocks": clk, "mean_guests_per_chain": float(counts.mean())}
     gpu.close()
     if world == 1 and not args.no_cpu_baseline:
         nt = host_threads()
         cs = CpuSample(s, nt)
         cs.run(1)
-        dt = cs.run(args.cpu_moves)
-        out["cpu_baseline"] = {"value": nt * args.cpu_moves / dt, "unit": "moves/s", "cores": nt, "kind": "port",
-                               "sample": f"{nt} host threads x {args.cpu_moves} MC moves of the same c4_large_k system, one "
+        n_cpu = 4 * args.cpu_moves
+        dt = cs.run(n_cpu)
+        out["cpu_baseline"] = {"value": nt * n_cpu / dt, "unit": "moves/s", "cores": nt, "kind": "port",
+                               "sample": f"{nt} host threads x {n_cpu} MC moves of the same c4_large_k system, one "
                                          f"independent chain per thread (oracle port, gcc -O2, init_sk=zero), {dt:.1f} s wall"}
     print(json.dumps(out))
 

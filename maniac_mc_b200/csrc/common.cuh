@@ -12,7 +12,6 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/maniac_gpu.h"
-#include "erfc_table.h"
 
 #define MMC_MAX_RES 8
 #define RECIP_THREADS 256   // single-point S(k) kernels
@@ -60,7 +59,9 @@ struct DevConst {
     const int* stype;
     const double* tbox;            // [n_tiles][6]
     int n_tiles;
-    const double* erfc_tab;        // [(MMC_ERFC_DEG+1) * MMC_ERFC_NSEG], erfc_table.h
+    const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
+    int gtab_base;                 // segment index of s = gtab_smin
+    double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
     const uint32_t* kpack;         // per k-vector table indices kx | (ky+kmax_y)<<10 | (kz+kmax_z)<<21
     const double* res_q;           // [MMC_MAX_RES][MMC_MAX_MOL_ATOMS] charges of the active residues
     const int* res_type;           // same, 0-based atom types
@@ -174,28 +175,35 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
 
 // erfc used by the real-space sweeps.  Accuracy contract (tests/test_gpu_parity.py::test_erfc):
 // |device - glibc| <= 2e-15 absolute and <= 1e-13 relative on [0, 6].
-__device__ __noinline__ double mmc_erfc_slow(double x) { return erfc(x); }
-// exp(-x^2) * P_seg(t): piecewise degree-9 fit of erfcx (tools/gen_erfc_table.py, 3e-15 relative) for
-// 0 <= x < 7; `e` = exp(-x^2) supplied by the caller (it has -alpha^2 r^2 exactly); tab may be shared memory.
-__device__ __forceinline__ double mmc_erfcx_poly(double x, const double* tab) {
-    const double u = x * ((double)MMC_ERFC_NSEG / MMC_ERFC_XMAX);
-    const int i = min((int)u, MMC_ERFC_NSEG - 1);
-    const double t = fma(2.0, u - (double)i, -1.0);
-    double p = tab[MMC_ERFC_DEG * MMC_ERFC_NSEG + i];
+// ---- real-space Coulomb kernel g(s) = erfc(alpha sqrt(s)) / sqrt(s), s = r^2 ----------------------------
+// Piecewise degree-9 polynomials on segments that follow the binary representation of s: 8 segments per
+// octave (exponent + top 3 mantissa bits select the segment, the remaining mantissa bits give the local
+// variable t in [-1, 1)), built at mmc_init for this system's alpha in long double (build_coulomb_table,
+// maniac_gpu.cu).  Absolute error <= 5e-16 (it is at the rounding floor of the coefficients), i.e. a few
+// 1e-16 relative where the terms matter (alpha r < 1.5) -- no sqrt, no exp, no division per pair.
+#define MMC_GTAB_DEG 9
+#define MMC_GTAB_MBITS 3
+#define MMC_GTAB_MAXSEG 128   // also the row stride: layout [degree][segment]
+__device__ __noinline__ double coul_kernel_slow(double s, double alpha) { const double r = sqrt(s); return erfc(alpha * r) / r; }
+__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base) {
+    const int hi = __double2hiint(s), lo = __double2loint(s);
+    const int idx = (hi >> (20 - MMC_GTAB_MBITS)) - base;
+    const double f = __hiloint2double(0x3FF00000 | ((hi & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
+                                          (int)((unsigned)lo >> (32 - MMC_GTAB_MBITS)), lo << MMC_GTAB_MBITS);
+    const double t = fma(2.0, f, -3.0);
+    double p = tab[MMC_GTAB_DEG * MMC_GTAB_MAXSEG + idx];
 #pragma unroll
-    for (int d = MMC_ERFC_DEG - 1; d >= 0; d--) p = fma(p, t, tab[d * MMC_ERFC_NSEG + i]);
+    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, tab[d * MMC_GTAB_MAXSEG + idx]);
     return p;
 }
-__device__ __forceinline__ double mmc_erfc(double x, const double* tab) {
-    if (x >= MMC_ERFC_XMAX || x < 0.0) return mmc_erfc_slow(x);
-    return exp(-x * x) * mmc_erfcx_poly(x, tab);
-}
-// 1/sqrt(a) for a in the normal float range: float seed (2 ulp) + one cubically convergent FP64 step
-// (residual error ~ (5/16) e^3 with e ~ 5e-7 -> below 1 ulp)
-__device__ __forceinline__ double mmc_rsqrt(double a) {
-    const double y = (double)rsqrtf((float)a);
-    const double e = fma(-a * y, y, 1.0);
-    return fma(y * e, fma(0.375, e, 0.5), y);
+// 1/a: MUFU.RCP64H seed + two Newton steps
+__device__ __forceinline__ double mmc_rcp(double a) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    double e = fma(-a, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-a, y, 1.0);
+    return fma(y, e, y);
 }
 // minimum image by round-to-nearest: d - L * nint(d / L).  Same value as the reference's
 // modulo(d + L/2, L) - L/2 (geometry_utils.f90:385-393) up to rounding; the 1.5*2^52 constant rounds to integer

@@ -21,12 +21,14 @@ struct MolS {
     double po[MMC_MAX_MOL_ATOMS][3], pn[MMC_MAX_MOL_ATOMS][3];
     double q[MMC_MAX_MOL_ATOMS];
     double cen[2][4];   // bounding sphere {x, y, z, radius + reach} of the old / new geometry
+    double cc[4];       // common sphere of the geometries swept: {x, y, z, (radius + reach)^2}
+    int shift_ok;       // reach + radius < L/2 on every axis: one periodic shift per other atom is exact
     int type[MMC_MAX_MOL_ATOMS];
     int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
 };
 
 struct SweepCtx {
-    double* erfc;    // [(DEG+1) * NSEG]
+    double* gtab;    // [MMC_GTAB_DEG+1][MMC_GTAB_MAXSEG] Coulomb kernel table
     double2* lj;     // [max_nat][ntypes] {sigma^2, 4 eps} rows of the moved molecule's atom types
     double2 *X, *Y, *Z;  // [2 max_nat][nx | ny | nz]
     uint32_t* mask;  // [CULL_CHUNK / 32]
@@ -40,7 +42,7 @@ struct SweepCtx {
 __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[9]) {
     size_t o = 0;
     const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = 2 * kmax[2] + 1;
-    off[0] = o; o += (size_t)(MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG * sizeof(double);
+    off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
     off[1] = o; o += (size_t)max_nat * ntypes * sizeof(double2);
     off[2] = o; o += (size_t)2 * max_nat * nx * sizeof(double2);
     off[3] = o; o += (size_t)2 * max_nat * ny * sizeof(double2);
@@ -56,7 +58,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
     size_t off[9];
     sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
     SweepCtx s;
-    s.erfc = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
+    s.gtab = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
     s.X = (double2*)(smem + off[2]); s.Y = (double2*)(smem + off[3]); s.Z = (double2*)(smem + off[4]);
     s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]);
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
@@ -65,9 +67,9 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
     return s;
 }
 
-// once per kernel: the erfcx coefficient table
+// once per kernel: the Coulomb kernel table
 __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const SweepCtx& s) {
-    for (int i = threadIdx.x; i < (MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG; i += blockDim.x) s.erfc[i] = dc.erfc_tab[i];
+    for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG; i += blockDim.x) s.gtab[i] = dc.gtab[i];
 }
 
 // Stages the pending Trial of chain c: positions, charges, LJ rows, bounding spheres and the 1-D phase
@@ -99,6 +101,23 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
         }
         m.cen[tid][0] = cx; m.cen[tid][1] = cy; m.cen[tid][2] = cz; m.cen[tid][3] = sqrt(r2) * (1.0 + 1e-12) + dc.reach;
     }
+    if (tid == 32) {  // common sphere of the swept geometries, and whether the single-shift path is exact
+        const bool uo = t.do_old, un = t.do_new;
+        double cx = 0, cy = 0, cz = 0; int n = 0;
+        for (int a = 0; a < nat; a++) {
+            if (uo) { cx += t.p_old[a][0]; cy += t.p_old[a][1]; cz += t.p_old[a][2]; n++; }
+            if (un) { cx += t.p_new[a][0]; cy += t.p_new[a][1]; cz += t.p_new[a][2]; n++; }
+        }
+        if (n) { cx /= n; cy /= n; cz /= n; }
+        double r2 = 0;
+        for (int a = 0; a < nat; a++) {
+            if (uo) { const double dx = t.p_old[a][0] - cx, dy = t.p_old[a][1] - cy, dz = t.p_old[a][2] - cz; r2 = fmax(r2, dx * dx + dy * dy + dz * dz); }
+            if (un) { const double dx = t.p_new[a][0] - cx, dy = t.p_new[a][1] - cy, dz = t.p_new[a][2] - cz; r2 = fmax(r2, dx * dx + dy * dy + dz * dz); }
+        }
+        const double R = sqrt(r2) * (1.0 + 1e-12) + 1e-9 + dc.reach;
+        m.cc[0] = cx; m.cc[1] = cy; m.cc[2] = cz; m.cc[3] = R * R;
+        m.shift_ok = R < 0.4999 * fmin(dc.L[0], fmin(dc.L[1], dc.L[2]));
+    }
     for (int i = tid; i < nat * dc.ntypes; i += blockDim.x) {
         const int a = i / dc.ntypes, tj = i % dc.ntypes;
         const double2 v = dc.lj[t.type[a] * dc.ntypes + tj];
@@ -126,27 +145,28 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
 }
 
 // ----------------------------------------------------------------------------------------------
-struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, alpha2, rc; };
+struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase; };
 
-// one (moved atom, other atom) pair at one geometry
-__device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_erfc, double dx, double dy, double dz,
+// one (moved atom, other atom) pair at one geometry; SHIFT: the other atom was already moved to the periodic
+// image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
+template <bool SHIFT>
+__device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gtab, double dx, double dy, double dz,
                                          double qq, bool charged, double2 lj, double& e_lj, double& e_c) {
-    dx = min_image_fast(dx, pc.Lx, pc.iLx);
-    dy = min_image_fast(dy, pc.Ly, pc.iLy);
-    dz = min_image_fast(dz, pc.Lz, pc.iLz);
+    if (!SHIFT) {
+        dx = min_image_fast(dx, pc.Lx, pc.iLx);
+        dy = min_image_fast(dy, pc.Ly, pc.iLy);
+        dz = min_image_fast(dz, pc.Lz, pc.iLz);
+    }
     const double r2 = fma(dx, dx, fma(dy, dy, dz * dz));
     if (r2 < pc.reach2) {
-        const double rinv = mmc_rsqrt(r2);
-        const double r = r2 * rinv;
-        if (charged) {
-            const double x = pc.alpha * r;
-            double ec;
-            if (x < MMC_ERFC_XMAX) ec = exp(-pc.alpha2 * r2) * mmc_erfcx_poly(x, s_erfc);
-            else ec = mmc_erfc_slow(x);
-            e_c = fma(qq * rinv, ec, e_c);
+        if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
+            double g;
+            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase);
+            else g = coul_kernel_slow(r2, pc.alpha);
+            e_c = fma(qq, g, e_c);
         }
-        if (r < pc.rc && lj.y != 0.0) {
-            const double s2 = lj.x * (rinv * rinv);
+        if (r2 < pc.rc2 && lj.y != 0.0) {  // 4 eps [(sigma/r)^12 - (sigma/r)^6], energy_utils.f90:417-423
+            const double s2 = lj.x * mmc_rcp(r2);
             const double s6 = s2 * s2 * s2;
             e_lj = fma(lj.y, fma(s6, s6, -s6), e_lj);
         }
@@ -154,10 +174,18 @@ __device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_er
 }
 
 // one "other" atom against every atom of the moved molecule, old and/or new geometry
-template <bool OLD, bool NEW>
+template <bool OLD, bool NEW, bool SHIFT>
 __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
                                           double qj, int tj, double (&acc)[4]) {
     const MolS& m = *s.mol;
+    if (SHIFT) {
+        double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
+        const double big = 6755399441055744.0;
+        const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
+        xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
+        dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
+        if (fma(dx, dx, fma(dy, dy, dz * dz)) > m.cc[3]) return;  // beyond reach of every atom of the molecule
+    }
     const bool qj_ok = fabs(qj) >= MMC_ERR;
     const int nat = m.nat;
 #pragma unroll 2
@@ -166,9 +194,10 @@ __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s
         const bool charged = qj_ok && fabs(qa) >= MMC_ERR;
         const double qq = qa * qj;
         const double2 lj = s.lj[a * ntypes + tj];
+        if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
-        if (OLD) pair_one(pc, s.erfc, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1]);
-        if (NEW) pair_one(pc, s.erfc, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3]);
+        if (OLD) pair_one<SHIFT>(pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1]);
+        if (NEW) pair_one<SHIFT>(pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3]);
     }
 }
 
@@ -193,13 +222,13 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
 // Real-space phase of one trial.  Work items = framework tiles in reach (ordered compaction of the cull
 // result, so the item -> warp assignment and hence the summation order is deterministic) followed by tiles
 // of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
-template <int NT, bool OLD, bool NEW>
+template <int NT, bool OLD, bool NEW, bool SHIFT>
 __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                     double (&acc)[4]) {
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
-    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.alpha2, dc.rc};
+    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base};
     const bool cull = dc.reach2 < 1e300;
     int item0 = 0;
     for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
@@ -234,7 +263,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
         const int nlist = m.nlist;
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
             const int j = (base + (int)s.list[it]) * TILE + lane;
-            if (j < dc.n_fw) pair_atom<OLD, NEW>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc);
+            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc);
         }
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
@@ -250,7 +279,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
             if (i < n_at) {
                 const int mol = i / na, a = i - mol * na;
                 if (!(m.excl && r == m.res && mol == m.mol))
-                    pair_atom<OLD, NEW>(pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
+                    pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
                                         dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc);
             }
         }
@@ -263,9 +292,10 @@ __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int 
                                   double (&acc)[4]) {
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
-    if (m.do_old && m.do_new) pair_phase_t<NT, true, true>(dc, cs, c, s, part, n_parts, acc);
-    else if (m.do_old) pair_phase_t<NT, true, false>(dc, cs, c, s, part, n_parts, acc);
-    else if (m.do_new) pair_phase_t<NT, false, true>(dc, cs, c, s, part, n_parts, acc);
+    const bool sh = m.shift_ok && dc.reach2 < 1e300;
+    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, true, true, false>(dc, cs, c, s, part, n_parts, acc); }
+    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, true, false, false>(dc, cs, c, s, part, n_parts, acc); }
+    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, false, true, false>(dc, cs, c, s, part, n_parts, acc); }
 }
 
 // ----------------------------------------------------------------------------------------------

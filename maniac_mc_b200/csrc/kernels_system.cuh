@@ -233,9 +233,14 @@ __global__ void k_table_lookup(DevConst dc, int which, const double* r, int n, d
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = table_lookup(which == 0 ? dc.tab_erfc : which == 1 ? dc.tab_r6 : dc.tab_r12, dc.tab_dx, r[i]);
 }
-__global__ void k_erfc_test(const double* tab, const double* x, int n, double* out) {
+// erfc(x) as the per-move sweep evaluates it: r = x / alpha, erfc = r * g(r^2) with the Coulomb kernel table
+// (slow path outside the table's domain)
+__global__ void k_erfc_test(DevConst dc, const double* x, int n, double* out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = mmc_erfc(x[i], tab);
+    if (i >= n) return;
+    const double r = x[i] / dc.alpha, s = r * r;
+    const double g = (s >= dc.gtab_smin && s < dc.gtab_smax) ? coul_kernel_tab(s, dc.gtab, dc.gtab_base) : coul_kernel_slow(s, dc.alpha);
+    out[i] = r * g;
 }
 
 // FP64 peak: 8 independent DFMA chains per thread, register resident

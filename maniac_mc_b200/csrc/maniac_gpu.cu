@@ -161,12 +161,53 @@ static int upload_chain(mmc_handle* h, int c, const int* count, const double* co
 }
 
 // Layout of the per-move sweeps (kernels_sweep.cuh): framework atoms in Morton order of their cell in
-// tiles of 32 with a bounding box each, the packed k list, the erfcx table, the real-space reach, and
+// tiles of 32 with a bounding box each, the packed k list, the Coulomb kernel table, the real-space reach, and
 // the launch configuration of k_sweep / k_chain_run.
 static uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) {
     auto spread = [](uint32_t v) { uint32_t r = 0; for (int b = 0; b < 10; b++) r |= ((v >> b) & 1u) << (3 * b); return r; };
     return spread(x) | (spread(y) << 1) | (spread(z) << 2);
 }
+// Coulomb kernel table (common.cuh coul_kernel_tab): g(s) = erfc(alpha sqrt(s))/sqrt(s) on segments
+// [2^e (1 + j/8), 2^e (1 + (j+1)/8)), degree-9 interpolation at Chebyshev nodes solved in long double.
+// Domain: s_min (0.25 A^2, raised if more than MMC_GTAB_MAXSEG segments would be needed) to (xmax/alpha)^2.
+static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out) {
+    const int D = MMC_GTAB_DEG, M = MMC_GTAB_MBITS, NS = 1 << M;
+    const double smax = (xmax / alpha) * (xmax / alpha);
+    int e_hi = 0; std::frexp(smax, &e_hi);   // smax in [2^(e_hi-1), 2^e_hi)
+    int e_lo = -2;
+    while ((e_hi - e_lo) * NS > MMC_GTAB_MAXSEG) e_lo++;
+    const int nseg = (e_hi - e_lo) * NS;
+    tab.assign((size_t)(D + 1) * MMC_GTAB_MAXSEG, 0.0);
+    const long double pi = 3.14159265358979323846264338327950288L;
+    long double nodes[D + 1];
+    for (int k = 0; k <= D; k++) nodes[k] = cosl(pi * (2 * k + 1) / (2.0L * (D + 1)));
+    for (int seg = 0; seg < nseg; seg++) {
+        const int e = e_lo + seg / NS, j = seg % NS;
+        const long double s0 = ldexpl(1.0L + (long double)j / NS, e), w = ldexpl(1.0L / NS, e);
+        long double V[D + 1][D + 2];
+        for (int r = 0; r <= D; r++) {
+            long double p = 1.0L;
+            for (int c = 0; c <= D; c++) { V[r][c] = p; p *= nodes[r]; }
+            const long double sv = s0 + (nodes[r] + 1.0L) * 0.5L * w, rr = sqrtl(sv);
+            V[r][D + 1] = erfcl((long double)alpha * rr) / rr;
+        }
+        for (int c = 0; c <= D; c++) {  // Gauss-Jordan with partial pivoting
+            int piv = c;
+            for (int r = c + 1; r <= D; r++) if (fabsl(V[r][c]) > fabsl(V[piv][c])) piv = r;
+            for (int k = 0; k <= D + 1; k++) std::swap(V[c][k], V[piv][k]);
+            for (int r = 0; r <= D; r++) if (r != c) {
+                const long double f = V[r][c] / V[c][c];
+                for (int k = c; k <= D + 1; k++) V[r][k] -= f * V[c][k];
+            }
+        }
+        for (int c = 0; c <= D; c++) tab[(size_t)c * MMC_GTAB_MAXSEG + seg] = (double)(V[c][D + 1] / V[c][c]);
+    }
+    const double smin = std::ldexp(1.0, e_lo);
+    union { double d; uint64_t u; } cv; cv.d = smin;
+    *base = (int)(cv.u >> (52 - M));
+    *smin_out = smin; *smax_out = std::ldexp(1.0, e_hi);
+}
+
 static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     DevConst& dc = h->dc;
     const size_t n = (size_t)dc.n_fw;
@@ -219,9 +260,12 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
         CK(cudaMemcpy(pb, tbox.data(), (size_t)n_tiles * 6 * 8, cudaMemcpyHostToDevice));
     }
     dc.sx = px; dc.sy = py; dc.sz = pz; dc.sq = pq; dc.stype = pt; dc.tbox = pb; dc.n_tiles = n_tiles;
-    const size_t ne = (size_t)(MMC_ERFC_DEG + 1) * MMC_ERFC_NSEG;
-    CK(dalloc(h, &pe, ne)); CK(cudaMemcpy(pe, h_erfc_table, ne * 8, cudaMemcpyHostToDevice));
-    dc.erfc_tab = pe;
+    {
+        std::vector<double> tab;
+        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax);
+        CK(dalloc(h, &pe, tab.size())); CK(cudaMemcpy(pe, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
+        dc.gtab = pe;
+    }
     {   // per-residue charge / type rows for the guest part of the sweep
         std::vector<double> rq(MMC_MAX_RES * MMC_MAX_MOL_ATOMS, 0.0); std::vector<int> rt(MMC_MAX_RES * MMC_MAX_MOL_ATOMS, 0);
         for (int r = 0; r < dc.nres; r++) if (dc.is_active[r])
@@ -243,7 +287,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     for (int r = 0; r < dc.nres; r++) if (dc.is_active[r]) for (int a = 0; a < dc.natoms[r]; a++) if (std::fabs(dc.q[r][a]) >= MMC_ERR) any_charge = true;
     dc.rc2 = dc.rc * dc.rc; dc.alpha2 = dc.alpha * dc.alpha;
     double xcut = d->coulomb_xcut == 0.0 ? 6.5 : d->coulomb_xcut;
-    if (xcut > MMC_ERFC_XMAX) xcut = MMC_ERFC_XMAX;
+    if (xcut > 7.0) xcut = 7.0;
     if (xcut < 0.0) { dc.reach = 1e200; dc.reach2 = INFINITY; }
     else { dc.reach = any_charge ? std::max(dc.rc, xcut / dc.alpha) : dc.rc; dc.reach2 = dc.reach * dc.reach; }
     // launch configuration
@@ -843,7 +887,7 @@ static int run_elementwise(mmc_handle* h, int which, const double* in, int n, do
     double *di = nullptr, *dout = nullptr;
     CK(cudaMalloc((void**)&di, n * sizeof(double))); CK(cudaMalloc((void**)&dout, n * sizeof(double)));
     CK(cudaMemcpy(di, in, n * sizeof(double), cudaMemcpyHostToDevice));
-    if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc.erfc_tab, di, n, dout);
+    if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, di, n, dout);
     else k_table_lookup<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, which, di, n, dout);
     h->launches++;
     cudaError_t e = cudaStreamSynchronize(h->stream);

@@ -17,7 +17,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
 SO_PATH = os.path.join(_PKG, "libmaniacgpu.so")
 SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("maniac_gpu.cu", "common.cuh", "kernels_move.cuh", "kernels_sweep.cuh", "kernels_chain.cuh",
-                                                        "kernels_system.cuh", "erfc_table.h")] + \
+                                                        "kernels_system.cuh")] + \
           [os.path.join(_ROOT, "include", "maniac_gpu.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
