@@ -63,6 +63,7 @@ struct DevConst {
     int gtab_base;                 // segment index of s = gtab_smin
     double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
     const uint32_t* kpack;         // per k-vector table indices kx | (ky+kmax_y)<<10 | (kz+kmax_z)<<21
+    const int* row_start;          // [nx*ny + 1] first k of every flattened (kx, ky) row (k list is kz-fastest)
     const double* res_q;           // [MMC_MAX_RES][MMC_MAX_MOL_ATOMS] charges of the active residues
     const int* res_type;           // same, 0-based atom types
     // real-space reach: LJ inside rc, erfc-Coulomb inside x_cut/alpha (terms beyond it are < erfc(x_cut),

@@ -25,12 +25,14 @@ struct MolS {
     int shift_ok;       // reach + radius < L/2 on every axis: one periodic shift per other atom is exact
     int type[MMC_MAX_MOL_ATOMS];
     int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
+    signed char term[2 * MMC_MAX_MOL_ATOMS];  // reciprocal terms: +(a+1) = atom a added, -(a+1) = atom a removed
 };
 
 struct SweepCtx {
     double* gtab;    // [MMC_GTAB_DEG+1][MMC_GTAB_MAXSEG] Coulomb kernel table
     double2* lj;     // [max_nat][ntypes] {sigma^2, 4 eps} rows of the moved molecule's atom types
     double2 *X, *Y, *Z;  // [2 max_nat][nx | ny | nz]
+    double2* XY;     // [2 buffers][2 max_nat][threads / 4 rows] products X_t(kx) Y_t(ky) of a chunk of (kx, ky) rows
     uint32_t* mask;  // [CULL_CHUNK / 32]
     int* prefix;     // [CULL_CHUNK / 32]
     uint16_t* list;  // [CULL_CHUNK]
@@ -39,7 +41,7 @@ struct SweepCtx {
     int nx, ny, nz;
 };
 
-__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[9]) {
+__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[10]) {
     size_t o = 0;
     const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = 2 * kmax[2] + 1;
     off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
@@ -51,11 +53,13 @@ __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, con
     off[6] = o; o += (sizeof(MolS) + 15) / 16 * 16;
     off[7] = o; o += (CULL_CHUNK / 32) * sizeof(uint32_t) * 2;
     off[8] = o; o += CULL_CHUNK * sizeof(uint16_t);
+    o = (o + 15) / 16 * 16;
+    off[9] = o; o += (size_t)2 * 2 * max_nat * (threads / 4) * sizeof(double2);
     return o;
 }
 
 __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned char* smem, int threads) {
-    size_t off[9];
+    size_t off[10];
     sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
     SweepCtx s;
     s.gtab = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
@@ -63,6 +67,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
     s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]);
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
     s.list = (uint16_t*)(smem + off[8]);
+    s.XY = (double2*)(smem + off[9]);
     s.nx = dc.kmax[0] + 1; s.ny = 2 * dc.kmax[1] + 1; s.nz = 2 * dc.kmax[2] + 1;
     return s;
 }
@@ -82,7 +87,14 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
     const int nat = t.nat;
     if (tid == 0) {
         m.nat = nat; m.kind = t.kind; m.do_old = t.do_old; m.do_new = t.do_new; m.excl = t.excl; m.res = t.res; m.mol = t.mol;
-        m.nterm = nat * ((t.r_plus ? 1 : 0) + (t.r_minus ? 1 : 0)); m.cur = cs.cur[c];
+        m.cur = cs.cur[c];
+        // atoms with q == 0 add exactly zero to A(k) (ewald_energy.f90:241-256 multiplies by the charge): no term
+        int n = 0;
+        if (t.kind > 0) {
+            if (t.r_plus) for (int a = 0; a < nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(a + 1);
+            if (t.r_minus) for (int a = 0; a < nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(-(a + 1));
+        }
+        m.nterm = n;
     }
     if (t.kind <= 0) { __syncthreads(); return; }
     if (tid < nat) {
@@ -123,13 +135,15 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
         const double2 v = dc.lj[t.type[a] * dc.ntypes + tj];
         s.lj[i] = make_double2(v.x * v.x, v.y);
     }
-    // phase tables: term index = plus atoms first, then minus atoms (charge sign folded into Z)
-    const int nplus = t.r_plus ? nat : 0, nterm = nplus + (t.r_minus ? nat : 0);
+    __syncthreads();  // term map
+    // phase tables, one row per reciprocal term (charge and sign folded into Z)
+    const int nterm = m.nterm;
     const int per = s.nx + s.ny + s.nz;
     for (int i = tid; i < nterm * per; i += blockDim.x) {
         const int term = i / per; int j = i % per;
-        const bool plus = term < nplus;
-        const int a = plus ? term : term - nplus;
+        const int ta = m.term[term];
+        const bool plus = ta > 0;
+        const int a = (plus ? ta : -ta) - 1;
         int ax, k; double2* dst;
         if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
         else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
@@ -299,34 +313,64 @@ __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int 
 }
 
 // ----------------------------------------------------------------------------------------------
-// Reciprocal phase: this part's contiguous share of the k list, one k per thread per pass (coalesced A
-// read, A' write into the other half of the double buffer).  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
+// Reciprocal phase.  The k list is ordered (kx, ky, kz) with kz fastest, so all k of one (kx, ky) "row" are
+// contiguous and share the product X_t(kx) Y_t(ky).  The rows (flattened index kx*ny + ky+kmax_y) are walked in
+// chunks of NT/4: the chunk's products are staged in shared memory (double buffered: the next chunk is staged
+// while this one is consumed, one barrier per chunk), then one k per thread per pass: coalesced A read, A' write
+// into the other half of the double buffer, 4 FMAs per term.  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
+template <int NT>
+__device__ __forceinline__ void recip_stage_rows(const SweepCtx& s, int nterm, int r_a, int r_b, double2* buf) {
+    constexpr int RMAX = NT / 4;
+    const int nrow = r_b - r_a;
+    for (int i = threadIdx.x; i < nrow * nterm; i += NT) {
+        const int t = i / nrow, rl = i - t * nrow;
+        const int r = r_a + rl, ix = r / s.ny, iy = r - ix * s.ny;
+        const double2 X = s.X[t * s.nx + ix], Y = s.Y[t * s.ny + iy];
+        buf[t * RMAX + rl] = make_double2(fma(X.x, Y.x, -X.y * Y.y), fma(X.x, Y.y, X.y * Y.x));
+    }
+}
+
 template <int NT>
 __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                    double (&acc)[2]) {
+    constexpr int RMAX = NT / 4;
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
-    const int nterm = m.nterm, nx = s.nx, ny = s.ny, nz = s.nz;
+    const int nterm = m.nterm, ny = s.ny, nz = s.nz;
     const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
     double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
-    const int per = (((dc.nk + n_parts - 1) / n_parts) + 31) & ~31;
-    const int k0 = part * per, k1 = min(dc.nk, k0 + per);
-    for (int k = k0 + threadIdx.x; k < k1; k += NT) {
-        const uint32_t kp = dc.kpack[k];
-        const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, iz = kp >> 21;
-        const double2 a0 = A[k];
-        const double w = dc.fw[k];
-        double sre = 0.0, sim = 0.0;
-        for (int t = 0; t < nterm; t++) {
-            const double2 X = s.X[t * nx + ix], Y = s.Y[t * ny + iy], Z = s.Z[t * nz + iz];
-            const double xr = fma(X.x, Y.x, -X.y * Y.y), xi = fma(X.x, Y.y, X.y * Y.x);
-            sre = fma(xr, Z.x, sre); sre = fma(-xi, Z.y, sre);
-            sim = fma(xr, Z.y, sim); sim = fma(xi, Z.x, sim);
+    const int nrows = s.nx * ny;
+    const int rpp = (nrows + n_parts - 1) / n_parts;
+    const int r0 = min(nrows, part * rpp), r1 = min(nrows, r0 + rpp);
+    if (r0 >= r1) return;
+    int buf = 0;
+    recip_stage_rows<NT>(s, nterm, r0, min(r1, r0 + RMAX), s.XY);
+    __syncthreads();
+    for (int ra = r0; ra < r1; ra += RMAX) {
+        const int rb = min(r1, ra + RMAX);
+        if (rb < r1) recip_stage_rows<NT>(s, nterm, rb, min(r1, rb + RMAX), s.XY + (size_t)(buf ^ 1) * nterm * RMAX);
+        const double2* xy = s.XY + (size_t)buf * nterm * RMAX;
+        const int k0 = dc.row_start[ra], k1 = dc.row_start[rb];
+        for (int k = k0 + threadIdx.x; k < k1; k += NT) {
+            const uint32_t kp = dc.kpack[k];
+            const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, iz = kp >> 21;
+            const int rl = ix * ny + iy - ra;
+            const double2 a0 = A[k];
+            const double w = dc.fw[k];
+            double sre = 0.0, sim = 0.0;
+#pragma unroll 3
+            for (int t = 0; t < nterm; t++) {
+                const double2 P = xy[t * RMAX + rl], Z = s.Z[t * nz + iz];
+                sre = fma(P.x, Z.x, sre); sre = fma(-P.y, Z.y, sre);
+                sim = fma(P.x, Z.y, sim); sim = fma(P.y, Z.x, sim);
+            }
+            const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
+            An[k] = a1;
+            acc[0] = fma(w, fma(a0.x, a0.x, a0.y * a0.y), acc[0]);  // amplitude_squared helper_utils.f90:125
+            acc[1] = fma(w, fma(a1.x, a1.x, a1.y * a1.y), acc[1]);
         }
-        const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
-        An[k] = a1;
-        acc[0] = fma(w, fma(a0.x, a0.x, a0.y * a0.y), acc[0]);  // amplitude_squared helper_utils.f90:125
-        acc[1] = fma(w, fma(a1.x, a1.x, a1.y * a1.y), acc[1]);
+        __syncthreads();
+        buf ^= 1;
     }
 }
 

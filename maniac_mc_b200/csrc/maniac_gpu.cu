@@ -280,6 +280,12 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
             kp[i] = (uint32_t)h->h_kx[i] | ((uint32_t)(h->h_ky[i] + dc.kmax[1]) << 10) | ((uint32_t)(h->h_kz[i] + dc.kmax[2]) << 21);
         CK(dalloc(h, &pk, kp.size())); CK(cudaMemcpy(pk, kp.data(), kp.size() * 4, cudaMemcpyHostToDevice));
         dc.kpack = pk;
+        const int ny = 2 * dc.kmax[1] + 1, nrows = (dc.kmax[0] + 1) * ny;
+        std::vector<int> rs(nrows + 1, dc.nk);
+        for (int i = dc.nk - 1; i >= 0; i--) rs[h->h_kx[i] * ny + h->h_ky[i] + dc.kmax[1]] = i;
+        for (int r = nrows - 1; r >= 0; r--) if (rs[r] > rs[r + 1]) rs[r] = rs[r + 1];   // empty rows point at the next one
+        int* prs; CK(dalloc(h, &prs, rs.size())); CK(cudaMemcpy(prs, rs.data(), rs.size() * 4, cudaMemcpyHostToDevice));
+        dc.row_start = prs;
     }
     // reach of the real-space sweep
     bool any_charge = false;
@@ -295,7 +301,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     h->n_sm = prop.multiProcessorCount;
     const int work = std::max((dc.nk + 511) / 512, (n_tiles + dc.g_atoms / TILE + 15) / 16);
     dc.sweep_parts = std::max(1, std::min(2 * h->n_sm, work));
-    size_t off[9];
+    size_t off[10];
     h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, SWEEP_THREADS, off);
     h->chain_threads = dc.n_chains >= 3 * h->n_sm ? 256 : dc.n_chains >= 3 * h->n_sm / 2 ? 512 : 1024;
     h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
