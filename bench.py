@@ -35,6 +35,10 @@ if ROOT not in sys.path:
 W_PAIR_FLOP = 90.0   # FP64 flop per pair-eval, SURVEY.md 8(d) / DESIGN.md
 B_K_BYTES = 40.0     # HBM bytes per k-eval: A(k) read 16 + A'(k) write 16 + f*W 8
 FUG_LO_ATM, FUG_HI_ATM, N_POINTS = 1.0e-2, 1.0e4, 64
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_chain_run launch from the committed `ncu --set full` capture,
+# divided by that launch's k-evals (592 chains x 32 steps x 37 782 k); bench.py scales it to its own launch.
+NCU_DRAM_BYTES_PER_K_EVAL = 23460991000.0 / (592 * 32 * 37782)
+NCU_TRAFFIC_SOURCE = "profiles/r1d_ncu_summary.txt (23.46 GB per launch of 592 chains x 32 steps), scaled by k-evals"
 
 
 def parse_args():
@@ -293,7 +297,9 @@ def run_own(args, rank, world, local_rank):
     PROF_STEPS = 32
     cp0 = counters()
     counts0 = h_cnt.numpy()[:, 0].copy()
+    pw0 = gpu.pair_work()
     prof = gpu.profile_kernels(PROF_STEPS, seed=13)
+    pw1 = gpu.pair_work()
     cp1 = counters()
     counts = h_cnt.numpy()[:, 0].copy()
     dprof = counters_delta(cp0, cp1)
@@ -311,22 +317,37 @@ def run_own(args, rank, world, local_rank):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     full_s, pair_s, recip_s = prof["tail_ms"] * 1e-3, prof["pair_ms"] * 1e-3, prof["recip_ms"] * 1e-3
-    tflops = (evals * W_PAIR_FLOP + k_flop) / full_s / 1e12
-    roofline = {"kernel": "k_chain_run (propose + real-space sweep + reciprocal sweep + accept/commit, %d MC steps per launch)" % PROF_STEPS,
-                "bound": "fp64", "achieved": tflops, "peak": fp64_peak, "unit": "TFLOP/s", "frac": tflops / fp64_peak, "traffic": None,
-                "peak_source": "DFMA micro-benchmark run in this process (mmc_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
-                "algorithmic": f"{W_PAIR_FLOP:g} flop x pair-evals (all minimum-image pairs of the reference loop, SURVEY 8d) + (30 natoms + 5) flop x "
-                               "k-evals per launch; tiles out of reach (alpha r > 6.5) are culled, so executed flops are lower",
-                "avg_launch_ms": prof["tail_ms"], "share_of_step": 1.0,
-                "pair_evals_per_s": evals / full_s, "k_evals_per_s": k_evals / full_s,
-                "phase_only_ms": {"real_space": prof["pair_ms"], "reciprocal": prof["recip_ms"], "full": prof["tail_ms"]},
-                "real_space_only_tflops": evals * W_PAIR_FLOP / pair_s / 1e12}
+    # profile_kernels launches the real-space phase twice on the same trials (alone, then inside the full launch)
+    dist_exec, in_reach = ((b - a) / 2.0 for a, b in zip(pw0, pw1))
+    # Dominant phase of the fused kernel = the reciprocal sweep (HBM): every trial streams its chain's A(k) in and
+    # A'(k) out.  achieved = algorithmic bytes of the launch / duration of the WHOLE fused launch.
     recip_gbs = k_evals * B_K_BYTES / full_s / 1e9
-    roofline_recip = {"kernel": "k_chain_run, reciprocal share", "bound": "hbm", "achieved": recip_gbs, "peak": hbm_peak, "unit": "GB/s",
-                      "frac": recip_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
-                      "algorithmic": f"{B_K_BYTES:g} B per k-eval x k-evals per launch (A read 16 + A' write 16 + f*W 8)",
-                      "avg_launch_ms": prof["tail_ms"],
-                      "reciprocal_only_gbs": k_evals * B_K_BYTES / recip_s / 1e9}
+    roofline = {"kernel": "k_chain_run (propose + real-space sweep + reciprocal sweep + accept/commit fused, %d MC steps per launch, "
+                          "one CTA per chain)" % PROF_STEPS,
+                "bound": "hbm", "achieved": recip_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": recip_gbs / hbm_peak,
+                "traffic": NCU_DRAM_BYTES_PER_K_EVAL * k_evals if NCU_DRAM_BYTES_PER_K_EVAL else None,
+                "traffic_source": NCU_TRAFFIC_SOURCE, "peak_source": hbm_src,
+                "algorithmic": f"{B_K_BYTES:g} B per k-eval x k-evals per launch (A read 16 + A' write 16 + f*W 8; f*W is shared by all "
+                               "chains and stays in L2, so DRAM traffic is ~32 B per k-eval)",
+                "algorithmic_bytes_per_launch": k_evals * B_K_BYTES,
+                "avg_launch_ms": prof["tail_ms"], "share_of_step": 1.0, "k_evals_per_s": k_evals / full_s,
+                "phase_only_ms": {"real_space": prof["pair_ms"], "reciprocal": prof["recip_ms"], "full": prof["tail_ms"]},
+                "reciprocal_phase_alone_gbs": k_evals * B_K_BYTES / recip_s / 1e9,
+                "reciprocal_phase_alone_frac": k_evals * B_K_BYTES / recip_s / 1e9 / hbm_peak}
+    # Real-space phase (FP64 pipe).  Two figures: the reference loop's pair-evals (every minimum-image pair, 90 flop
+    # each) and the work the tile-culled sweep actually executes (distance formed: 12 flop; pair inside
+    # reach: + 10-term Coulomb table 24 flop + LJ 10 flop).  The first can exceed the FP64 peak -- that is the culling.
+    exec_flop = dist_exec * 12.0 + in_reach * 34.0
+    roofline_pair = {"kernel": "k_chain_run, real-space share", "bound": "fp64", "unit": "TFLOP/s", "peak": fp64_peak,
+                     "peak_source": "DFMA micro-benchmark run in this process (mmc_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 entry",
+                     "achieved": exec_flop / pair_s / 1e12, "frac": exec_flop / pair_s / 1e12 / fp64_peak,
+                     "algorithmic": "executed work: 12 flop per distance formed + 34 flop per pair inside reach (counted on the device, "
+                                    "mmc_pair_work); phase timed alone on the same trials",
+                     "reference_loop_pair_evals_per_s": evals / pair_s,
+                     "reference_loop_tflops_equivalent": evals * W_PAIR_FLOP / pair_s / 1e12,
+                     "distances_formed_per_reference_pair": dist_exec / max(evals, 1.0),
+                     "pairs_in_reach_per_reference_pair": in_reach / max(evals, 1.0),
+                     "phase_alone_ms": prof["pair_ms"]}
     dall = counters_delta(c0, c1)
     evals_timed = pair_evals_of(s, args, counts, dall)
     out = {"metric": "mc_trial_moves_per_s", "value": value, "unit": "moves/s", "n_gpus": world, "steps": args.steps,
@@ -335,7 +356,7 @@ def run_own(args, rank, world, local_rank):
            "pair_evals_per_s": world * evals_timed / (ms * 1e-3),
            "e2e": {"value": e2e_value, "unit": "moves/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "call": "mmc_upload_chains + mmc_run_batch_async + mmc_download_chains per step, pinned host buffers"},
-           "gpu_launches": int(launches), "roofline": roofline, "roofline_recip": roofline_recip,
+           "gpu_launches": int(launches), "roofline": roofline, "roofline_pair": roofline_pair,
            "clocks": clk, "mean_guests_per_chain": float(counts.mean())}
     gpu.close()
     if world == 1 and not args.no_cpu_baseline:

@@ -221,6 +221,11 @@ int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
 void* mmc_stream(mmc_t* handle);
 /* kernel launches issued by this handle since init (bench.py's gpu_launches) */
 int64_t mmc_launch_count(const mmc_t* handle);
+/* Executed real-space work of the per-move sweeps since mmc_init (all chains): out[0] = minimum-image distances
+ * formed, out[1] = pairs found inside the reach (Coulomb kernel and/or LJ evaluated).  The reference loop
+ * (energy_utils.f90:399-437) forms every distance; the tile-culled sweep forms only these.  Used by bench.py for
+ * the executed-flop figure next to the algorithmic one. */
+int mmc_pair_work(mmc_t* handle, int64_t out[2]);
 /* Instrumented replay for the roofline report: runs n_steps batched steps WITHOUT graph capture,
  * CUDA events around every launch on the handle's stream, and returns the average duration in ms
  * of one launch of {pair sweep, reciprocal sweep, step tail} in ms[0..2] and the number of

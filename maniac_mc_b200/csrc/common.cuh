@@ -62,8 +62,11 @@ struct DevConst {
     const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
     int gtab_base;                 // segment index of s = gtab_smin
     double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
-    const uint32_t* kpack;         // per k-vector table indices kx | (ky+kmax_y)<<10 | (kz+kmax_z)<<21
-    const int* row_start;          // [nx*ny + 1] first k of every flattened (kx, ky) row (k list is kz-fastest)
+    // reciprocal work items (build_sweep_layout): one per (kx, ky) row and kz >= 0, serving k(+kz) and k(-kz).
+    // .x = kx | (ky+kmax_y)<<10 | kz<<21 | flag<<31, .y = index of k(+kz); index of k(-kz) = .y - 2 kz + flag
+    const int2* kitem;
+    const int* item_row_start;     // [nx*ny + 1] first item of every flattened (kx, ky) row
+    int n_items;
     const double* res_q;           // [MMC_MAX_RES][MMC_MAX_MOL_ATOMS] charges of the active residues
     const int* res_type;           // same, 0-based atom types
     // real-space reach: LJ inside rc, erfc-Coulomb inside x_cut/alpha (terms beyond it are < erfc(x_cut),
@@ -106,6 +109,7 @@ struct ChainState {
     Trial* trial;      // [C]
     double* part;      // [C][sweep_parts][6]  (lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2)
     long long* tape_pos;  // [C]
+    unsigned long long* pair_count;  // [2] executed real-space work since mmc_init: distances formed, pairs inside reach
     int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)
 };
 

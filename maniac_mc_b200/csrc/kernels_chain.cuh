@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
     sweep_load_tables(dc, s);
     RngSrc rs = ctl->rng;
     const unsigned long long step0 = rs.step;
+    unsigned cnt[2] = {0u, 0u};
     for (int st = 0; st < n_steps; st++) {
         rs.step = step0 + (unsigned long long)st;
         if (threadIdx.x == 0) {
@@ -36,7 +37,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         double v[6] = {0, 0, 0, 0, 0, 0};
         double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
         double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
-        if (phases & 1) pair_phase<NT>(dc, cs, c, s, 0, 1, pa);
+        if (phases & 1) pair_phase<NT>(dc, cs, c, s, 0, 1, pa, cnt);
         if (phases & 2) recip_phase<NT>(dc, cs, c, s, 0, 1, ra);
         block_sum<6, NT>(v, s.red);
         if (threadIdx.x == 0) {
@@ -57,4 +58,5 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         }
         __syncthreads();
     }
+    pair_count_flush(cs, cnt);
 }

@@ -165,7 +165,7 @@ struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, s
 // image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
 template <bool SHIFT>
 __device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gtab, double dx, double dy, double dz,
-                                         double qq, bool charged, double2 lj, double& e_lj, double& e_c) {
+                                         double qq, bool charged, double2 lj, double& e_lj, double& e_c, unsigned& n_in) {
     if (!SHIFT) {
         dx = min_image_fast(dx, pc.Lx, pc.iLx);
         dy = min_image_fast(dy, pc.Ly, pc.iLy);
@@ -173,6 +173,7 @@ __device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gt
     }
     const double r2 = fma(dx, dx, fma(dy, dy, dz * dz));
     if (r2 < pc.reach2) {
+        n_in++;
         if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
             double g;
             if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase);
@@ -190,7 +191,7 @@ __device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gt
 // one "other" atom against every atom of the moved molecule, old and/or new geometry
 template <bool OLD, bool NEW, bool SHIFT>
 __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
-                                          double qj, int tj, double (&acc)[4]) {
+                                          double qj, int tj, double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
     if (SHIFT) {
         double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
@@ -210,8 +211,9 @@ __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s
         const double2 lj = s.lj[a * ntypes + tj];
         if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
-        if (OLD) pair_one<SHIFT>(pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1]);
-        if (NEW) pair_one<SHIFT>(pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3]);
+        cnt[0] += (OLD ? 1u : 0u) + (NEW ? 1u : 0u);
+        if (OLD) pair_one<SHIFT>(pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt[1]);
+        if (NEW) pair_one<SHIFT>(pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt[1]);
     }
 }
 
@@ -238,7 +240,7 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
 // of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
 template <int NT, bool OLD, bool NEW, bool SHIFT>
 __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                    double (&acc)[4]) {
+                                    double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
@@ -277,7 +279,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
         const int nlist = m.nlist;
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
             const int j = (base + (int)s.list[it]) * TILE + lane;
-            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc);
+            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc, cnt);
         }
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
@@ -294,7 +296,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
                 const int mol = i / na, a = i - mol * na;
                 if (!(m.excl && r == m.res && mol == m.mol))
                     pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
-                                        dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc);
+                                        dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc, cnt);
             }
         }
         item0 += ntile;
@@ -303,21 +305,23 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
 
 template <int NT>
 __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                  double (&acc)[4]) {
+                                  double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
     const bool sh = m.shift_ok && dc.reach2 < 1e300;
-    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, true, true, false>(dc, cs, c, s, part, n_parts, acc); }
-    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, true, false, false>(dc, cs, c, s, part, n_parts, acc); }
-    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true>(dc, cs, c, s, part, n_parts, acc); else pair_phase_t<NT, false, true, false>(dc, cs, c, s, part, n_parts, acc); }
+    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, false, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
 }
 
 // ----------------------------------------------------------------------------------------------
 // Reciprocal phase.  The k list is ordered (kx, ky, kz) with kz fastest, so all k of one (kx, ky) "row" are
 // contiguous and share the product X_t(kx) Y_t(ky).  The rows (flattened index kx*ny + ky+kmax_y) are walked in
 // chunks of NT/4: the chunk's products are staged in shared memory (double buffered: the next chunk is staged
-// while this one is consumed, one barrier per chunk), then one k per thread per pass: coalesced A read, A' write
-// into the other half of the double buffer, 4 FMAs per term.  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
+// while this one is consumed, one barrier per chunk).  One work item per thread per pass = the two k-vectors
+// (kx, ky, +kz) and (kx, ky, -kz): Z(-kz) = conj Z(kz), so both updates come from the same four real product sums
+// (4 FMAs and two 16-byte shared loads per term for TWO k-vectors).  A is read ascending for +kz and descending for
+// -kz (both coalesced), A' goes to the other half of the double buffer.  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
 template <int NT>
 __device__ __forceinline__ void recip_stage_rows(const SweepCtx& s, int nterm, int r_a, int r_b, double2* buf) {
     constexpr int RMAX = NT / 4;
@@ -336,7 +340,7 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
     constexpr int RMAX = NT / 4;
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
-    const int nterm = m.nterm, ny = s.ny, nz = s.nz;
+    const int nterm = m.nterm, ny = s.ny, nz = s.nz, kmz = dc.kmax[2];
     const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
     double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
     const int nrows = s.nx * ny;
@@ -350,27 +354,49 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
         const int rb = min(r1, ra + RMAX);
         if (rb < r1) recip_stage_rows<NT>(s, nterm, rb, min(r1, rb + RMAX), s.XY + (size_t)(buf ^ 1) * nterm * RMAX);
         const double2* xy = s.XY + (size_t)buf * nterm * RMAX;
-        const int k0 = dc.row_start[ra], k1 = dc.row_start[rb];
-        for (int k = k0 + threadIdx.x; k < k1; k += NT) {
-            const uint32_t kp = dc.kpack[k];
-            const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, iz = kp >> 21;
+        const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
+        for (int i = i0 + threadIdx.x; i < i1; i += NT) {
+            const int2 it = dc.kitem[i];
+            const uint32_t kp = (uint32_t)it.x;
+            const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, kz = (kp >> 21) & 1023u;
             const int rl = ix * ny + iy - ra;
-            const double2 a0 = A[k];
-            const double w = dc.fw[k];
-            double sre = 0.0, sim = 0.0;
+            const int kpl = it.y, kmi = kpl - 2 * kz + (int)(kp >> 31);
+            const bool two = kz != 0;
+            const double2 ap = A[kpl];
+            const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
+            const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz
+            // sum_t P_t Z_t and sum_t P_t conj(Z_t) from the four real product sums
+            double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+            const double2* zt = s.Z + kmz + kz;
 #pragma unroll 3
             for (int t = 0; t < nterm; t++) {
-                const double2 P = xy[t * RMAX + rl], Z = s.Z[t * nz + iz];
-                sre = fma(P.x, Z.x, sre); sre = fma(-P.y, Z.y, sre);
-                sim = fma(P.x, Z.y, sim); sim = fma(P.y, Z.x, sim);
+                const double2 P = xy[t * RMAX + rl], Z = zt[t * nz];
+                s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
+                s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
             }
-            const double2 a1 = make_double2(a0.x + sre, a0.y + sim);
-            An[k] = a1;
-            acc[0] = fma(w, fma(a0.x, a0.x, a0.y * a0.y), acc[0]);  // amplitude_squared helper_utils.f90:125
-            acc[1] = fma(w, fma(a1.x, a1.x, a1.y * a1.y), acc[1]);
+            const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
+            An[kpl] = bp;
+            acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
+            acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
+            if (two) {
+                const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
+                An[kmi] = bm;
+                acc[0] = fma(w, fma(am.x, am.x, am.y * am.y), acc[0]);
+                acc[1] = fma(w, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
+            }
         }
         __syncthreads();
         buf ^= 1;
+    }
+}
+
+// executed-work counters of the real-space sweep (bench.py's executed-flop figure): cs.pair_count[0] += distances
+// formed, [1] += pairs inside reach (Coulomb table and/or LJ evaluated).  One atomic pair per warp per launch.
+__device__ __forceinline__ void pair_count_flush(const ChainState& cs, const unsigned (&cnt)[2]) {
+    const unsigned a = __reduce_add_sync(0xffffffffu, cnt[0]), b = __reduce_add_sync(0xffffffffu, cnt[1]);
+    if ((threadIdx.x & 31) == 0 && (a | b)) {
+        atomicAdd(cs.pair_count, (unsigned long long)a);
+        atomicAdd(cs.pair_count + 1, (unsigned long long)b);
     }
 }
 
@@ -383,11 +409,13 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     double v[6] = {0, 0, 0, 0, 0, 0};
     double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
     double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
-    pair_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, pa);
+    unsigned cnt[2] = {0u, 0u};
+    pair_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, pa, cnt);
     recip_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, ra);
     block_sum<6, SWEEP_THREADS>(v, s.red);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
         for (int i = 0; i < 6; i++) out[i] = v[i];
     }
+    pair_count_flush(cs, cnt);
 }

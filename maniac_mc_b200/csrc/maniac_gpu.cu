@@ -250,7 +250,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
             tbox[(size_t)t * 6 + 3 + k] = 0.5 * (hi[k] - lo[k]) * (1.0 + 1e-12) + 1e-9;   // never under-estimate the box
         }
     }
-    double *px, *py, *pz, *pq, *pb, *pe, *prq; int *pt, *prt; uint32_t* pk;
+    double *px, *py, *pz, *pq, *pb, *pe, *prq; int *pt, *prt;
     CK(dalloc(h, &px, np)); CK(dalloc(h, &py, np)); CK(dalloc(h, &pz, np)); CK(dalloc(h, &pq, np)); CK(dalloc(h, &pt, np));
     CK(dalloc(h, &pb, (size_t)n_tiles * 6));
     if (np) {
@@ -274,18 +274,41 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
         CK(cudaMemcpy(prq, rq.data(), rq.size() * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(prt, rt.data(), rt.size() * 4, cudaMemcpyHostToDevice));
         dc.res_q = prq; dc.res_type = prt;
     }
-    {   // table indices of every k-vector: ix = kx, iy = ky + kmax_y, iz = kz + kmax_z
-        std::vector<uint32_t> kp(dc.nk);
-        for (int i = 0; i < dc.nk; i++)
-            kp[i] = (uint32_t)h->h_kx[i] | ((uint32_t)(h->h_ky[i] + dc.kmax[1]) << 10) | ((uint32_t)(h->h_kz[i] + dc.kmax[2]) << 21);
-        CK(dalloc(h, &pk, kp.size())); CK(cudaMemcpy(pk, kp.data(), kp.size() * 4, cudaMemcpyHostToDevice));
-        dc.kpack = pk;
+    {   // Reciprocal work items.  The k list (PrecomputeValidReciprocalVectors, ewald_kvectors.f90:44-103) is
+        // ordered kx, ky, kz with kz fastest, so a (kx, ky) row holds kz = -m..m contiguously (row (0,0) lacks
+        // kz = 0) and +kz / -kz share X(kx) Y(ky), |Z(kz)| and f W.  One item = {row, kz >= 0} -> k(+kz), k(-kz).
+        if (dc.kmax[0] > 1023 || dc.kmax[1] > 1023 || dc.kmax[2] > 1023) return fail("mmc_init: kmax above 1023 is not supported");
         const int ny = 2 * dc.kmax[1] + 1, nrows = (dc.kmax[0] + 1) * ny;
         std::vector<int> rs(nrows + 1, dc.nk);
         for (int i = dc.nk - 1; i >= 0; i--) rs[h->h_kx[i] * ny + h->h_ky[i] + dc.kmax[1]] = i;
         for (int r = nrows - 1; r >= 0; r--) if (rs[r] > rs[r + 1]) rs[r] = rs[r + 1];   // empty rows point at the next one
-        int* prs; CK(dalloc(h, &prs, rs.size())); CK(cudaMemcpy(prs, rs.data(), rs.size() * 4, cudaMemcpyHostToDevice));
-        dc.row_start = prs;
+        std::vector<int2> items; items.reserve(dc.nk / 2 + nrows);
+        std::vector<int> irs(nrows + 1, 0);
+        for (int r = 0; r < nrows; r++) {
+            irs[r] = (int)items.size();
+            const int k0 = rs[r], k1 = rs[r + 1];
+            for (int kpl = k0; kpl < k1; kpl++) {
+                const int kz = h->h_kz[kpl];
+                if (kz < 0) continue;
+                uint32_t flag = 0;
+                if (kz > 0) {
+                    int kmi = kpl - 2 * kz;
+                    if (kmi < k0 || h->h_kz[kmi] != -kz) { kmi++; flag = 1u; }
+                    if (kmi < k0 || kmi >= k1 || h->h_kz[kmi] != -kz || h->h_kx[kmi] != h->h_kx[kpl] || h->h_ky[kmi] != h->h_ky[kpl])
+                        return fail("mmc_init: k list is not symmetric in kz inside row %d", r);
+                }
+                const uint32_t pack = (uint32_t)h->h_kx[kpl] | ((uint32_t)(h->h_ky[kpl] + dc.kmax[1]) << 10) | ((uint32_t)kz << 21) | (flag << 31);
+                items.push_back(make_int2((int)pack, kpl));
+            }
+        }
+        irs[nrows] = (int)items.size();
+        size_t covered = 0;
+        for (const int2& it : items) covered += (((uint32_t)it.x >> 21) & 1023u) ? 2 : 1;
+        if (covered != (size_t)dc.nk) return fail("mmc_init: reciprocal items cover %zu of %d k-vectors", covered, dc.nk);
+        int2* pit; int* pirs;
+        CK(dalloc(h, &pit, items.size() + 1)); CK(cudaMemcpy(pit, items.data(), items.size() * sizeof(int2), cudaMemcpyHostToDevice));
+        CK(dalloc(h, &pirs, irs.size())); CK(cudaMemcpy(pirs, irs.data(), irs.size() * 4, cudaMemcpyHostToDevice));
+        dc.kitem = pit; dc.item_row_start = pirs; dc.n_items = (int)items.size();
     }
     // reach of the real-space sweep
     bool any_charge = false;
@@ -450,7 +473,7 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
     CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
     CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
-    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.error_flag, 1));
+    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 2));
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
     CKB(cudaMallocHost((void**)&h->h_tape_pos, C * sizeof(long long)));
@@ -909,6 +932,15 @@ extern "C" int mmc_dbg_table_lookup(mmc_t* h, int which, const double* r, int n,
 extern "C" int mmc_dbg_erfc(mmc_t* h, const double* x, int n, double* out) { return run_elementwise(h, -1, x, n, out); }
 extern "C" void* mmc_stream(mmc_t* h) { return h ? (void*)h->stream : nullptr; }
 extern "C" int64_t mmc_launch_count(const mmc_t* h) { return h ? h->launches : -1; }
+extern "C" int mmc_pair_work(mmc_t* h, int64_t out[2]) {
+    if (!h || !out) return fail("mmc_pair_work: null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    unsigned long long v[2];
+    CK(cudaMemcpy(v, h->cs.pair_count, sizeof v, cudaMemcpyDeviceToHost));
+    out[0] = (int64_t)v[0]; out[1] = (int64_t)v[1];
+    return 0;
+}
 
 extern "C" int mmc_measure_fp64_peak(int device, double* tflops) {
     if (!tflops) return fail("null output");

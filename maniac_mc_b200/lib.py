@@ -47,7 +47,7 @@ ABI_SYMBOLS = [
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
-    "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels",
+    "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
 ]
 
 _lib = None
@@ -88,6 +88,7 @@ def load():
     L.mmc_dbg_erfc.argtypes = [vp, dp, C.c_int, dp]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
+    L.mmc_pair_work.argtypes = [vp, C.POINTER(C.c_int64)]
     L.mmc_measure_fp64_peak.argtypes = [C.c_int, dp]
     L.mmc_chain_capacity.argtypes = [vp, ip, ip]
     L.mmc_upload_chains.argtypes = [vp, vp, vp, vp]
@@ -293,3 +294,9 @@ class ManiacGPU:
 
     def launch_count(self):
         return load().mmc_launch_count(self.h)
+
+    def pair_work(self):
+        """(distances formed, pairs inside reach) by the per-move sweeps since mmc_init"""
+        v = (C.c_int64 * 2)()
+        _ck(load().mmc_pair_work(self.h, v))
+        return int(v[0]), int(v[1])

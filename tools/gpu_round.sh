@@ -1,6 +1,6 @@
 #!/bin/bash
 # one GPU-box session: tests, bench (both arms), ncu launch list + full capture of the chain kernel.
-# usage (under gpurun): bash tools/gpu_round.sh <tag> [notests] [noref]
+# usage (under gpurun): bash tools/gpu_round.sh <tag> [notests|tests] [noref|ref] [noncu]
 tag=${1:-rX}
 mkdir -p gpurun_out
 if [ "$2" != "notests" ]; then
@@ -10,6 +10,7 @@ python bench.py --steps 5 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_ou
 if [ "$3" != "noref" ]; then
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2>&1; cat gpurun_out/${tag}_bench_ref.json
 fi
+if [ "$4" == "noncu" ]; then exit 0; fi
 CMD="python bench.py --moves 32 --steps 1 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'k_chain_run|k_sweep|k_advance' -c 300 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu1.log 2>&1
