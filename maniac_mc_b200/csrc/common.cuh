@@ -54,10 +54,10 @@ struct DevConst {
     double tab_dx;
     // ---- per-move sweep layout (kernels_sweep.cuh) ----
     // framework atoms in Morton order of their cell, padded to whole tiles of 32 atoms; tile t owns
-    // atoms [32 t, 32 t + 32).  tbox[t] = {centre xyz, half extent xyz} of the tile's wrapped positions.
+    // atoms [32 t, 32 t + 32).  tbox[c][t], c = centre xyz, half extent xyz of the tile's wrapped positions (SoA: coalesced in the cull).
     const double *sx, *sy, *sz, *sq;
     const int* stype;
-    const double* tbox;            // [n_tiles][6]
+    const double* tbox;            // [6][n_tiles]
     int n_tiles;
     const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
     int gtab_base;                 // segment index of s = gtab_smin
@@ -66,6 +66,7 @@ struct DevConst {
     // .x = kx | (ky+kmax_y)<<10 | kz<<21 | flag<<31, .y = index of k(+kz); index of k(-kz) = .y - 2 kz + flag
     const int2* kitem;
     const int* item_row_start;     // [nx*ny + 1] first item of every flattened (kx, ky) row
+    const int* row_kstart;         // [nx*ny + 1] first k-vector of every row (the k list is kz-fastest)
     int n_items;
     const double* res_q;           // [MMC_MAX_RES][MMC_MAX_MOL_ATOMS] charges of the active residues
     const int* res_type;           // same, 0-based atom types

@@ -219,8 +219,8 @@ __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s
 
 // can tile `t` hold an atom within reach of the moved molecule?  periodic point-to-box distance per axis
 __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m, int t, bool use_old, bool use_new) {
-    const double* b = dc.tbox + (size_t)t * 6;
-    const double bx = b[0], by = b[1], bz = b[2], hx = b[3], hy = b[4], hz = b[5];
+    const double* b = dc.tbox + t; const size_t nt = (size_t)dc.n_tiles;
+    const double bx = b[0], by = b[nt], bz = b[2 * nt], hx = b[3 * nt], hy = b[4 * nt], hz = b[5 * nt];
     bool hit = false;
 #pragma unroll
     for (int g = 0; g < 2; g++) {
@@ -355,8 +355,16 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
         if (rb < r1) recip_stage_rows<NT>(s, nterm, rb, min(r1, rb + RMAX), s.XY + (size_t)(buf ^ 1) * nterm * RMAX);
         const double2* xy = s.XY + (size_t)buf * nterm * RMAX;
         const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
+        if (rb < r1) {  // pull the next chunk's A(k) lines from HBM into L2 while this chunk is computed
+            const char* pa = (const char*)(A + dc.row_kstart[rb]);
+            const char* pe = (const char*)(A + dc.row_kstart[min(r1, rb + RMAX)]);
+            const char* pl = (const char*)((uintptr_t)pa & ~(uintptr_t)127) + (size_t)threadIdx.x * 128;
+            for (; pl < pe; pl += (size_t)NT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(pl));
+        }
+        int2 it_next = (i0 + (int)threadIdx.x < i1) ? dc.kitem[i0 + threadIdx.x] : make_int2(0, 0);
         for (int i = i0 + threadIdx.x; i < i1; i += NT) {
-            const int2 it = dc.kitem[i];
+            const int2 it = it_next;
+            if (i + NT < i1) it_next = dc.kitem[i + NT];
             const uint32_t kp = (uint32_t)it.x;
             const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, kz = (kp >> 21) & 1023u;
             const int rl = ix * ny + iy - ra;

@@ -246,8 +246,8 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
             for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], w[k]); hi[k] = std::max(hi[k], w[k]); }
         }
         for (int k = 0; k < 3; k++) {
-            tbox[(size_t)t * 6 + k] = 0.5 * (lo[k] + hi[k]);
-            tbox[(size_t)t * 6 + 3 + k] = 0.5 * (hi[k] - lo[k]) * (1.0 + 1e-12) + 1e-9;   // never under-estimate the box
+            tbox[(size_t)k * n_tiles + t] = 0.5 * (lo[k] + hi[k]);
+            tbox[(size_t)(3 + k) * n_tiles + t] = 0.5 * (hi[k] - lo[k]) * (1.0 + 1e-12) + 1e-9;   // never under-estimate the box
         }
     }
     double *px, *py, *pz, *pq, *pb, *pe, *prq; int *pt, *prt;
@@ -305,7 +305,9 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
         size_t covered = 0;
         for (const int2& it : items) covered += (((uint32_t)it.x >> 21) & 1023u) ? 2 : 1;
         if (covered != (size_t)dc.nk) return fail("mmc_init: reciprocal items cover %zu of %d k-vectors", covered, dc.nk);
-        int2* pit; int* pirs;
+        int2* pit; int *pirs, *prs;
+        CK(dalloc(h, &prs, rs.size())); CK(cudaMemcpy(prs, rs.data(), rs.size() * 4, cudaMemcpyHostToDevice));
+        dc.row_kstart = prs;
         CK(dalloc(h, &pit, items.size() + 1)); CK(cudaMemcpy(pit, items.data(), items.size() * sizeof(int2), cudaMemcpyHostToDevice));
         CK(dalloc(h, &pirs, irs.size())); CK(cudaMemcpy(pirs, irs.data(), irs.size() * 4, cudaMemcpyHostToDevice));
         dc.kitem = pit; dc.item_row_start = pirs; dc.n_items = (int)items.size();

@@ -248,3 +248,111 @@ def test_large_framework_identities():
         _, _, _, tracked = g.sync_to_host(c)
         assert rel_err(tracked, g.system_energy(c)) < 1e-9
     g.close()
+
+
+# ---- BASELINE configs[1]: rigid-water GCMC insertion/deletion in an otherwise empty periodic box ----------------
+def water_box_500():
+    s = builders.synthetic_water_box(n_mol=500, box=30.0, cutoff=14.0, tol=1e-5, seed=1, capacity=1024,
+                                     fugacity_atm=0.05, p_translation=0.25, p_rotation=0.25)
+    assert s.num_kvectors == 518          # alpha = 0.199263, kmax = 6
+    return s
+
+
+@pytest.mark.parametrize("init_sk,deletion", [(0, 0), (1, 1)])
+def test_c2_water_box_strict_mode(init_sk, deletion):
+    """~500 TIP4P molecules, no framework: the guest-guest part of the real-space sweep carries all the work.
+    Strict mode (host proposals from the tape) against the oracle move for move, both quirk settings."""
+    s = water_box_500(); s.init_sk, s.deletion_mode = init_sk, deletion
+    tape = np.random.default_rng(11).random(4000)
+    o = orc.Oracle(s); o.system_energy(); ref = o.run(300, tape=tape)
+    g = ManiacGPU(s); drv = StrictDriver(s, g); drv.ComputeSystemEnergy()
+    rng = TapeRng(tape); got = drv.MonteCarloLoop(rng, 1, 300)
+    compare_records(got, ref)
+    assert rng.pos == o.tape_used
+    assert set(np.unique(ref["kind"])) >= {MMC_CREATION, MMC_DELETION, MMC_TRANSLATION, MMC_ROTATION}
+    cnt, com, off, e = g.sync_to_host(); c2, com2, off2 = o.state()
+    assert np.array_equal(cnt, c2)
+    np.testing.assert_allclose(com, com2, atol=1e-12); np.testing.assert_allclose(off, off2, atol=1e-12)
+    assert rel_err(e, o.energy()) < TOL
+    g.close()
+
+
+def test_c2_water_box_batched_and_identities():
+    """Batched mode on the same box: on-device proposals from recorded streams == oracle; afterwards the tracked
+    energies equal a fresh single-point evaluation and tracked A(k) equals the freshly summed S(k)."""
+    s = water_box_500(); s.init_sk, s.deletion_mode = 1, 1
+    n = 250
+    tape = np.random.default_rng(12).random((2, 12 * n))
+    g = ManiacGPU(s, n_chains=2)
+    for c in range(2):
+        g.system_energy(c)
+    recs = g.run_batch(n, tape=tape, records=True)
+    for c in range(2):
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(recs[c], o.run(n, tape=tape[c]))
+        assert g.counters[c] == o.counters()
+    g.run_batch(2000, seed=3)
+    for c in range(2):
+        _, _, _, tracked = g.sync_to_host(c)
+        a_tracked = g.sk(c)
+        fresh = g.system_energy(c)          # recomputes S(k) from the coordinates
+        assert rel_err(tracked, fresh) < 1e-9
+        np.testing.assert_allclose(a_tracked, g.sk(c), atol=1e-8)
+    g.close()
+
+
+def test_culled_sweep_equals_every_pair_sweep():
+    """coulomb_xcut < 0 evaluates every minimum-image pair literally as the reference loop does (Q3); the default
+    tile-culled sweep (alpha r < 6.5) must agree to rounding on a framework large enough for the cull to bite."""
+    s = builders.synthetic_framework(n_framework=20000, n_guests=48, box=72.0, cutoff=12.0, tol=1e-6, seed=9, capacity=96)
+    s.init_sk, s.deletion_mode = 1, 1
+    full = s.copy(); full.coulomb_xcut = -1.0
+    tape = np.random.default_rng(5).random((1, 600))
+    out = []
+    for sys_ in (s, full):
+        g = ManiacGPU(sys_); g.system_energy()
+        out.append(g.run_batch(40, tape=tape, records=True)[0])
+        work = g.pair_work()
+        out.append(work)
+        g.close()
+    compare_records(out[0], out[2], tol=1e-12)
+    assert out[1][0] < 0.5 * out[3][0]        # the culled sweep formed far fewer distances
+    o = orc.Oracle(s); o.system_energy()
+    compare_records(out[2], o.run(40, tape=tape[0]))
+
+
+def test_c4_large_k_full_size_identities():
+    """BASELINE configs[3] at bench size (50 000-atom framework, r_c = 12, tol 1e-6 -> K = 37 782): too big for the
+    oracle to step through in seconds, so parity goes through size-independent identities: tracked energies == fresh
+    single-point energies after a batch, tracked A(k) == fresh S(k), insertion followed by deletion of the same
+    molecule restores A(k), and a rejected move leaves every component untouched."""
+    s = builders.synthetic_framework(n_framework=50000, n_guests=200, box=96.0, cutoff=12.0, tol=1e-6, seed=4, capacity=512,
+                                     p_translation=0.4, p_rotation=0.4)
+    s.init_sk, s.deletion_mode = 1, 1
+    assert s.num_kvectors == 37782
+    g = ManiacGPU(s, n_chains=3)
+    for c in range(3):
+        g.system_energy(c)
+    a0 = g.sk(0); e0 = g.sync_to_host(0)[3]
+    # insertion then deletion of the same molecule (strict entry points), chain 0
+    n0 = int(s.count[0])
+    com = np.array([11.0, 47.0, 80.5]); off = s.offsets[:4].copy()
+    old, new = g.trial_energy(MMC_CREATION, 0, n0, com, off, chain=0); g.trial_commit(True, chain=0)
+    old2, new2 = g.trial_energy(MMC_DELETION, 0, n0, chain=0); g.trial_commit(True, chain=0)
+    np.testing.assert_allclose(g.sk(0), a0, atol=1e-10)
+    assert rel_err(new[E_TOTAL], old2[E_TOTAL]) < 1e-11 and rel_err(new2[E_RECIP], old[E_RECIP]) < 1e-11
+    assert rel_err(g.sync_to_host(0)[3], e0) < 1e-11
+    # a rejected translation changes nothing
+    a1 = g.sk(0); e1 = g.sync_to_host(0)[3]
+    g.trial_energy(MMC_TRANSLATION, 0, 3, s.com[3] + 0.3, s.offsets[12:16], chain=0); g.trial_commit(False, chain=0)
+    np.testing.assert_array_equal(g.sk(0), a1)
+    np.testing.assert_array_equal(g.sync_to_host(0)[3], e1)
+    # batched moves on all chains, then tracked == fresh
+    g.run_batch(300, seed=21)
+    for c in range(3):
+        _, _, _, tracked = g.sync_to_host(c)
+        a_tracked = g.sk(c)
+        fresh = g.system_energy(c)
+        assert rel_err(tracked, fresh) < 1e-9
+        np.testing.assert_allclose(a_tracked, g.sk(c), atol=1e-7)
+    g.close()
