@@ -84,7 +84,8 @@ typedef struct mmc_desc {
     int device;            /* CUDA device ordinal */
     double coulomb_xcut;   /* real-space Coulomb terms with alpha*r >= xcut are skipped by the per-move sweep:
                             * erfc(xcut) is below one ulp of the sums the reference forms over all minimum-image
-                            * pairs (energy_utils.f90:425-433).  0 = default 6.5 (erfc = 3.8e-20), max 7;
+                            * pairs (energy_utils.f90:425-433).  0 = default 6.0 (erfc = 2.2e-17, below the
+                            * 1.1e-16 rounding of a unit term), max 7;
                             * negative = evaluate every pair literally as the reference does */
 } mmc_desc;
 

@@ -5,7 +5,7 @@
 // Real-space sweep = ComputePairInteractionEnergy_singlemol (energy_utils.f90:374-442) for the old and
 // the proposed geometry in ONE pass.  The framework is stored in Morton order in tiles of 32 atoms with a
 // bounding box each; a tile is visited only if it can hold an atom within `reach` of the moved molecule
-// (reach = max(r_c, x_cut/alpha): LJ needs r < r_c, and erfc(alpha r) < erfc(x_cut) ~ 4e-20 beyond it, which is
+// (reach = max(r_c, x_cut/alpha): LJ needs r < r_c, and erfc(alpha r) < erfc(x_cut) = 2e-17 (x_cut = 6) beyond it, which is
 // below one ulp of the sums the reference forms over ALL minimum-image pairs, Q3).  With culling disabled
 // (reach2 = inf) every pair is evaluated exactly as the reference does.
 //
@@ -31,30 +31,31 @@ struct MolS {
 struct SweepCtx {
     double* gtab;    // [MMC_GTAB_DEG+1][MMC_GTAB_MAXSEG] Coulomb kernel table
     double2* lj;     // [max_nat][ntypes] {sigma^2, 4 eps} rows of the moved molecule's atom types
-    double2 *X, *Y, *Z;  // [2 max_nat][nx | ny | nz]
-    double2* XY;     // [2 buffers][2 max_nat][threads / 4 rows] products X_t(kx) Y_t(ky) of a chunk of (kx, ky) rows
+    double2 *X, *Y;  // [2 max_nat][nx | ny] 1-D phase tables, one row per reciprocal term
+    double2* Z;      // [kmax_z + 1][zs] q_t Z_t(kz), kz >= 0 only, term fastest; zs = 2 max_nat + 1 (odd: no bank conflicts)
+    double2* XY;     // [2 buffers][threads / 4 rows][zs] products X_t(kx) Y_t(ky) of a chunk of (kx, ky) rows, term fastest
     uint32_t* mask;  // [CULL_CHUNK / 32]
     int* prefix;     // [CULL_CHUNK / 32]
     uint16_t* list;  // [CULL_CHUNK]
     double* red;     // [6 * warps]
     MolS* mol;
-    int nx, ny, nz;
+    int nx, ny, nz, zs;   // nz = kmax_z + 1
 };
 
 __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[10]) {
     size_t o = 0;
-    const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = 2 * kmax[2] + 1;
+    const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = kmax[2] + 1, zs = 2 * max_nat + 1;
     off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
     off[1] = o; o += (size_t)max_nat * ntypes * sizeof(double2);
     off[2] = o; o += (size_t)2 * max_nat * nx * sizeof(double2);
     off[3] = o; o += (size_t)2 * max_nat * ny * sizeof(double2);
-    off[4] = o; o += (size_t)2 * max_nat * nz * sizeof(double2);
+    off[4] = o; o += (size_t)nz * zs * sizeof(double2);
     off[5] = o; o += (size_t)6 * (threads / 32) * sizeof(double);
     off[6] = o; o += (sizeof(MolS) + 15) / 16 * 16;
     off[7] = o; o += (CULL_CHUNK / 32) * sizeof(uint32_t) * 2;
     off[8] = o; o += CULL_CHUNK * sizeof(uint16_t);
     o = (o + 15) / 16 * 16;
-    off[9] = o; o += (size_t)2 * 2 * max_nat * (threads / 4) * sizeof(double2);
+    off[9] = o; o += (size_t)2 * (threads / 4) * zs * sizeof(double2);
     return o;
 }
 
@@ -68,7 +69,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
     s.list = (uint16_t*)(smem + off[8]);
     s.XY = (double2*)(smem + off[9]);
-    s.nx = dc.kmax[0] + 1; s.ny = 2 * dc.kmax[1] + 1; s.nz = 2 * dc.kmax[2] + 1;
+    s.nx = dc.kmax[0] + 1; s.ny = 2 * dc.kmax[1] + 1; s.nz = dc.kmax[2] + 1; s.zs = 2 * dc.max_nat + 1;
     return s;
 }
 
@@ -147,7 +148,7 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
         int ax, k; double2* dst;
         if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
         else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
-        else { j -= s.nx + s.ny; ax = 2; k = j - dc.kmax[2]; dst = s.Z + term * s.nz + j; }
+        else { j -= s.nx + s.ny; ax = 2; k = j; dst = s.Z + j * s.zs + term; }
         const double pos = plus ? t.p_plus[a][ax] : t.p_old[a][ax];
         const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
         double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
@@ -324,13 +325,60 @@ __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int 
 // -kz (both coalesced), A' goes to the other half of the double buffer.  acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
 template <int NT>
 __device__ __forceinline__ void recip_stage_rows(const SweepCtx& s, int nterm, int r_a, int r_b, double2* buf) {
-    constexpr int RMAX = NT / 4;
     const int nrow = r_b - r_a;
     for (int i = threadIdx.x; i < nrow * nterm; i += NT) {
         const int t = i / nrow, rl = i - t * nrow;
         const int r = r_a + rl, ix = r / s.ny, iy = r - ix * s.ny;
         const double2 X = s.X[t * s.nx + ix], Y = s.Y[t * s.ny + iy];
-        buf[t * RMAX + rl] = make_double2(fma(X.x, Y.x, -X.y * Y.y), fma(X.x, Y.y, X.y * Y.x));
+        buf[rl * s.zs + t] = make_double2(fma(X.x, Y.x, -X.y * Y.y), fma(X.x, Y.y, X.y * Y.x));
+    }
+}
+
+// the items [i0, i1) of one staged chunk of rows.  NTERM > 0: term count known at compile time (the shared loads get
+// immediate offsets and the loop disappears); NTERM == 0: generic loop over nterm.
+template <int NT, int NTERM>
+__device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& s, const double2* __restrict__ A, double2* __restrict__ An,
+                                            const double2* xy, int ra, int i0, int i1, int nterm, double (&acc)[2]) {
+    const int ny = s.ny, zs = s.zs;
+    int2 it_next = (i0 + (int)threadIdx.x < i1) ? dc.kitem[i0 + threadIdx.x] : make_int2(0, 0);
+    for (int i = i0 + threadIdx.x; i < i1; i += NT) {
+        const int2 it = it_next;
+        if (i + NT < i1) it_next = dc.kitem[i + NT];
+        const uint32_t kp = (uint32_t)it.x;
+        const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, kz = (kp >> 21) & 1023u;
+        const int kpl = it.y, kmi = kpl - 2 * kz + (int)(kp >> 31);
+        const bool two = kz != 0;
+        const double2 ap = A[kpl];
+        const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
+        const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz
+        const double2* pt = xy + (ix * ny + iy - ra) * zs;
+        const double2* zt = s.Z + kz * zs;
+        // sum_t P_t Z_t and sum_t P_t conj(Z_t) from the four real product sums
+        double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
+        if (NTERM > 0) {
+#pragma unroll
+            for (int t = 0; t < NTERM; t++) {
+                const double2 P = pt[t], Z = zt[t];
+                s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
+                s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
+            }
+        } else {
+            for (int t = 0; t < nterm; t++) {
+                const double2 P = pt[t], Z = zt[t];
+                s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
+                s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
+            }
+        }
+        const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
+        An[kpl] = bp;
+        acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
+        acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
+        if (two) {
+            const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
+            An[kmi] = bm;
+            acc[0] = fma(w, fma(am.x, am.x, am.y * am.y), acc[0]);
+            acc[1] = fma(w, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
+        }
     }
 }
 
@@ -340,58 +388,38 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
     constexpr int RMAX = NT / 4;
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
-    const int nterm = m.nterm, ny = s.ny, nz = s.nz, kmz = dc.kmax[2];
+    const int nterm = m.nterm;
     const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
     double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
-    const int nrows = s.nx * ny;
+    const int nrows = s.nx * s.ny;
     const int rpp = (nrows + n_parts - 1) / n_parts;
     const int r0 = min(nrows, part * rpp), r1 = min(nrows, r0 + rpp);
     if (r0 >= r1) return;
+    const size_t bufsz = (size_t)RMAX * s.zs;
     int buf = 0;
     recip_stage_rows<NT>(s, nterm, r0, min(r1, r0 + RMAX), s.XY);
     __syncthreads();
     for (int ra = r0; ra < r1; ra += RMAX) {
         const int rb = min(r1, ra + RMAX);
-        if (rb < r1) recip_stage_rows<NT>(s, nterm, rb, min(r1, rb + RMAX), s.XY + (size_t)(buf ^ 1) * nterm * RMAX);
-        const double2* xy = s.XY + (size_t)buf * nterm * RMAX;
-        const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
-        if (rb < r1) {  // pull the next chunk's A(k) lines from HBM into L2 while this chunk is computed
-            const char* pa = (const char*)(A + dc.row_kstart[rb]);
-            const char* pe = (const char*)(A + dc.row_kstart[min(r1, rb + RMAX)]);
-            const char* pl = (const char*)((uintptr_t)pa & ~(uintptr_t)127) + (size_t)threadIdx.x * 128;
-            for (; pl < pe; pl += (size_t)NT * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(pl));
+        if (rb < r1) {
+            recip_stage_rows<NT>(s, nterm, rb, min(r1, rb + RMAX), s.XY + (buf ^ 1) * bufsz);
+            // pull the next chunk's A(k) from HBM into L2 while this chunk is computed: ONE bulk prefetch by one thread
+            // (no LSU wavefronts, unlike a prefetch per line)
+            if (threadIdx.x == 0) {
+                const int ka = dc.row_kstart[rb], kb = dc.row_kstart[min(r1, rb + RMAX)];
+                if (kb > ka) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + ka), "r"((kb - ka) * 16) : "memory");
+            }
         }
-        int2 it_next = (i0 + (int)threadIdx.x < i1) ? dc.kitem[i0 + threadIdx.x] : make_int2(0, 0);
-        for (int i = i0 + threadIdx.x; i < i1; i += NT) {
-            const int2 it = it_next;
-            if (i + NT < i1) it_next = dc.kitem[i + NT];
-            const uint32_t kp = (uint32_t)it.x;
-            const int ix = kp & 1023u, iy = (kp >> 10) & 2047u, kz = (kp >> 21) & 1023u;
-            const int rl = ix * ny + iy - ra;
-            const int kpl = it.y, kmi = kpl - 2 * kz + (int)(kp >> 31);
-            const bool two = kz != 0;
-            const double2 ap = A[kpl];
-            const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
-            const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz
-            // sum_t P_t Z_t and sum_t P_t conj(Z_t) from the four real product sums
-            double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
-            const double2* zt = s.Z + kmz + kz;
-#pragma unroll 3
-            for (int t = 0; t < nterm; t++) {
-                const double2 P = xy[t * RMAX + rl], Z = zt[t * nz];
-                s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
-                s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
-            }
-            const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
-            An[kpl] = bp;
-            acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
-            acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
-            if (two) {
-                const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
-                An[kmi] = bm;
-                acc[0] = fma(w, fma(am.x, am.x, am.y * am.y), acc[0]);
-                acc[1] = fma(w, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
-            }
+        const double2* xy = s.XY + buf * bufsz;
+        const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
+        switch (nterm) {   // 3 / 6 = rigid water insertion-deletion / move; the others cover 1..4 charged sites
+            case 1: recip_items<NT, 1>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 2: recip_items<NT, 2>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 3: recip_items<NT, 3>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 4: recip_items<NT, 4>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 6: recip_items<NT, 6>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 8: recip_items<NT, 8>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            default: recip_items<NT, 0>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
         }
         __syncthreads();
         buf ^= 1;

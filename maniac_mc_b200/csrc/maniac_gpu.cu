@@ -317,7 +317,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     for (size_t j = 0; j < n; j++) if (std::fabs(fq[j]) >= MMC_ERR) any_charge = true;
     for (int r = 0; r < dc.nres; r++) if (dc.is_active[r]) for (int a = 0; a < dc.natoms[r]; a++) if (std::fabs(dc.q[r][a]) >= MMC_ERR) any_charge = true;
     dc.rc2 = dc.rc * dc.rc; dc.alpha2 = dc.alpha * dc.alpha;
-    double xcut = d->coulomb_xcut == 0.0 ? 6.5 : d->coulomb_xcut;
+    double xcut = d->coulomb_xcut == 0.0 ? 6.0 : d->coulomb_xcut;
     if (xcut > 7.0) xcut = 7.0;
     if (xcut < 0.0) { dc.reach = 1e200; dc.reach2 = INFINITY; }
     else { dc.reach = any_charge ? std::max(dc.rc, xcut / dc.alpha) : dc.rc; dc.reach2 = dc.reach * dc.reach; }

@@ -100,7 +100,7 @@ class System:
     init_sk: int = 0
     deletion_mode: int = 0
     use_table: int = 0
-    coulomb_xcut: float = 0.0   # 0 = library default (6.5), negative = evaluate every pair
+    coulomb_xcut: float = 0.0   # 0 = library default (6.0), negative = evaluate every pair
     names: list = field(default_factory=list)
     ewald_tolerance: float = 1e-5
 

@@ -303,7 +303,7 @@ def test_c2_water_box_batched_and_identities():
 
 def test_culled_sweep_equals_every_pair_sweep():
     """coulomb_xcut < 0 evaluates every minimum-image pair literally as the reference loop does (Q3); the default
-    tile-culled sweep (alpha r < 6.5) must agree to rounding on a framework large enough for the cull to bite."""
+    tile-culled sweep (alpha r < 6) must agree to rounding on a framework large enough for the cull to bite."""
     s = builders.synthetic_framework(n_framework=20000, n_guests=48, box=72.0, cutoff=12.0, tol=1e-6, seed=9, capacity=96)
     s.init_sk, s.deletion_mode = 1, 1
     full = s.copy(); full.coulomb_xcut = -1.0
