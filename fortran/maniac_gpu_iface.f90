@@ -7,7 +7,9 @@ module maniac_gpu_iface
     implicit none
     private
     public :: mmc_desc, mmc_init, mmc_destroy, mmc_last_error, mmc_system_energy, mmc_trial_energy, &
-              mmc_trial_commit, mmc_sync_to_host, mmc_run_batch, mmc_ewald_setup, mmc_check
+              mmc_trial_commit, mmc_sync_to_host, mmc_run_batch, mmc_ewald_setup, mmc_check, &
+              mmc_set_chain_params, mmc_run_batch_async, mmc_synchronize, mmc_download_chains, mmc_upload_chains, &
+              mmc_shard_step_begin, mmc_shard_step_end, mmc_shard_trial_begin, mmc_shard_trial_end
 
     integer(c_int), parameter, public :: MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4
     integer(c_int), parameter, public :: MMC_NE = 6
@@ -23,6 +25,8 @@ module maniac_gpu_iface
         integer(c_int) :: kmax(3)
         real(c_double) :: translation_step, rotation_step, p_translation, p_rotation
         integer(c_int) :: init_sk, deletion_mode, use_table, device
+        real(c_double) :: coulomb_xcut
+        integer(c_int) :: shard_rank, shard_count
     end type mmc_desc
 
     interface
@@ -77,6 +81,55 @@ module maniac_gpu_iface
             type(c_ptr), value :: handle
             integer(c_int64_t), value :: n_steps, seed, tape_stride
             type(c_ptr), value :: tape, records, counters
+        end function
+        integer(c_int) function mmc_set_chain_params(handle, chain, fugacity, temperature) bind(C, name="mmc_set_chain_params")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle
+            integer(c_int), value :: chain
+            real(c_double), intent(in) :: fugacity(*)
+            real(c_double), value :: temperature
+        end function
+        integer(c_int) function mmc_run_batch_async(handle, n_steps, seed) bind(C, name="mmc_run_batch_async")
+            import :: c_int, c_ptr, c_int64_t
+            type(c_ptr), value :: handle
+            integer(c_int64_t), value :: n_steps, seed
+        end function
+        integer(c_int) function mmc_synchronize(handle) bind(C, name="mmc_synchronize")
+            import :: c_int, c_ptr
+            type(c_ptr), value :: handle
+        end function
+        !> bulk per-block exchange of all chains (fixed-capacity arrays, see include/maniac_gpu.h); null = skip
+        integer(c_int) function mmc_upload_chains(handle, count, com, offsets) bind(C, name="mmc_upload_chains")
+            import :: c_int, c_ptr
+            type(c_ptr), value :: handle, count, com, offsets
+        end function
+        integer(c_int) function mmc_download_chains(handle, count, com, offsets, energies, counters) &
+                bind(C, name="mmc_download_chains")
+            import :: c_int, c_ptr
+            type(c_ptr), value :: handle, count, com, offsets, energies, counters
+        end function
+        !> k-sharded mode: dev_sums is a DEVICE buffer (6 doubles per chain) all-reduced by the caller between begin and end
+        integer(c_int) function mmc_shard_step_begin(handle, seed, dev_sums) bind(C, name="mmc_shard_step_begin")
+            import :: c_int, c_ptr, c_int64_t
+            type(c_ptr), value :: handle, dev_sums
+            integer(c_int64_t), value :: seed
+        end function
+        integer(c_int) function mmc_shard_step_end(handle, dev_sums, records) bind(C, name="mmc_shard_step_end")
+            import :: c_int, c_ptr
+            type(c_ptr), value :: handle, dev_sums, records
+        end function
+        integer(c_int) function mmc_shard_trial_begin(handle, chain, kind, res, mol, com_new, offs_new, dev_sums) &
+                bind(C, name="mmc_shard_trial_begin")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle, dev_sums
+            integer(c_int), value :: chain, kind, res, mol
+            real(c_double), intent(in) :: com_new(3), offs_new(*)
+        end function
+        integer(c_int) function mmc_shard_trial_end(handle, chain, dev_sums, old_e, new_e) bind(C, name="mmc_shard_trial_end")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle, dev_sums
+            integer(c_int), value :: chain
+            real(c_double), intent(out) :: old_e(6), new_e(6)
         end function
     end interface
 

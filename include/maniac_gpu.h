@@ -87,6 +87,8 @@ typedef struct mmc_desc {
                             * pairs (energy_utils.f90:425-433).  0 = default 6.0 (erfc = 2.2e-17, below the
                             * 1.1e-16 rounding of a unit term), max 7;
                             * negative = evaluate every pair literally as the reference does */
+    int shard_rank;        /* k-sharded mode (ONE large system over several GPUs, one handle per GPU): this handle */
+    int shard_count;       /* sweeps part shard_rank of shard_count of the tiles and of the k rows; 0 or 1 = off    */
 } mmc_desc;
 
 /* One record per trial move of a batched run (optional output). */
@@ -204,6 +206,24 @@ int mmc_run_batch_async(mmc_t* handle, int64_t n_steps, uint64_t seed);
 int mmc_synchronize(mmc_t* handle);
 /* number of uniforms chain consumed from its tape in the last mmc_run_batch */
 int64_t mmc_tape_used(mmc_t* handle, int chain);
+
+/* ---- k-sharded mode: one very large system (or a few chains of it) spread over G GPUs ----------------------------
+ * (no reference counterpart: the reference is a single-threaded CPU code; SURVEY.md 8e "optional single-huge-system
+ * mode").  Every rank creates a handle from the SAME description with shard_rank = r, shard_count = G: it holds all
+ * coordinates, sweeps 1/G of the framework tiles and owns 1/G of the (kx, ky) rows of A(k).  One MC step of all
+ * chains = begin (proposal from the shared Philox counters + partial sweeps, six partial sums per chain left in the
+ * caller's DEVICE buffer, all enqueued on mmc_stream) -> caller all-reduces dev_sums in place (ncclAllReduce, sum,
+ * double, 6 x n_chains) on that stream -> end (energy assembly, accept draw, commit: identical on every rank, so no
+ * broadcast follows).  records (host, [n_chains], may be NULL) receives the step's move records. */
+int mmc_shard_step_begin(mmc_t* handle, uint64_t seed, double* dev_sums);
+int mmc_shard_step_end(mmc_t* handle, const double* dev_sums, mmc_move_record* records);
+/* strict-mode variant (host proposal, host decision): mmc_trial_energy split around the all-reduce of dev_sums[6];
+ * follow with mmc_trial_commit on every rank. */
+int mmc_shard_trial_begin(mmc_t* handle, int chain, int kind, int res, int mol,
+                          const double* com_new, const double* offs_new, double* dev_sums);
+int mmc_shard_trial_end(mmc_t* handle, int chain, const double* dev_sums, double old_e[MMC_NE], double new_e[MMC_NE]);
+/* k-vectors whose A(k) this handle owns and keeps current: [k_first, k_first + k_count) of the k list */
+int mmc_shard_range(const mmc_t* handle, int* k_first, int* k_count);
 
 /* ---- kernel-level entry points for parity tests (mmc_dbg_*) -------------------------------- */
 

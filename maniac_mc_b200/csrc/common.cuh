@@ -74,6 +74,7 @@ struct DevConst {
     // far below one ulp of the sums); reach2 = inf when culling is off (every pair evaluated, Q3 literally)
     double rc2, alpha2, reach, reach2;
     int max_nat, sweep_parts;      // largest active molecule; CTAs per chain of the strict-mode sweep
+    int shard_rank, shard_count;   // k/tile sharding of ONE system over several GPUs (1 handle per GPU); 0, 1 = off
 };
 
 // one pending trial move of one chain

@@ -274,6 +274,8 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
     t.kind = -t.kind;
 }
 
+struct BatchCtl { RngSrc rng; mmc_move_record* recs; long long rec_stride; long long rec_base; };
+
 // strict mode: sums the per-CTA partials of k_sweep in a fixed order -> Trial.old_e/new_e ; the host decides
 __global__ void __launch_bounds__(TAIL_THREADS) k_finalize(DevConst dc, ChainState cs, int chain, double* out /* 13 doubles */) {
     __shared__ double red[6 * TAIL_THREADS / 32];
@@ -295,7 +297,60 @@ __global__ void k_commit(DevConst dc, ChainState cs, int chain, int accept) {
     if (threadIdx.x == 0) commit_trial(dc, cs, chain, accept);
 }
 
-struct BatchCtl { RngSrc rng; mmc_move_record* recs; long long rec_stride; long long rec_base; };
+// ---- k-sharded mode: ONE system (or a few chains) spread over several GPUs (optional mode) ------------
+// Every rank holds the coordinates and makes the SAME proposal from the same Philox counters; rank r sweeps 1/G of the
+// framework tiles and owns 1/G of the (kx, ky) rows of A(k) (k_sweep with dc.shard_rank / dc.shard_count).  The six
+// partial sums of every chain's trial are all-reduced by the caller (NCCL over NVLink, 6 x chains doubles per MC
+// step); every rank then takes the identical accept decision, so no broadcast follows.
+//   k_propose_all : grid = chains, proposal of this step
+//   k_part_sum    : grid = chains, this rank's sweep partials -> sums[chain][6] (fixed order)
+//   k_finish      : grid = chains, energy assembly from the REDUCED sums, accept draw, commit
+__global__ void k_propose_all(DevConst dc, ChainState cs, const BatchCtl* ctl, int c0) {
+    if (threadIdx.x != 0) return;
+    const int c = c0 + blockIdx.x;
+    RngSrc rs = ctl->rng;
+    propose_move(dc, cs, rs, c);
+    if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
+}
+__global__ void __launch_bounds__(TAIL_THREADS) k_part_sum(DevConst dc, ChainState cs, int c0, double* sums /* [chains][6] */) {
+    __shared__ double red[6 * TAIL_THREADS / 32];
+    const int c = c0 + blockIdx.x;
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    const double* pp = cs.part + (size_t)c * dc.sweep_parts * 6;
+    if (cs.trial[c].kind > 0)
+        for (int i = threadIdx.x; i < dc.sweep_parts; i += TAIL_THREADS)
+            for (int k = 0; k < 6; k++) v[k] += pp[i * 6 + k];
+    block_sum<6, TAIL_THREADS>(v, red);
+    if (threadIdx.x == 0) for (int k = 0; k < 6; k++) sums[(size_t)blockIdx.x * 6 + k] = v[k];
+}
+// decide != 0: draw the accept uniform after the proposal's draws and commit (batched sharded step);
+// decide == 0: only assemble old/new energies into out (strict sharded trial, the host decides)
+__global__ void k_finish(DevConst dc, ChainState cs, const BatchCtl* ctl, int c0, const double* sums, int decide, double* out) {
+    if (threadIdx.x != 0) return;
+    const int c = c0 + blockIdx.x;
+    Trial& t = cs.trial[c];
+    const int kind = t.kind;
+    if (kind > 0) {
+        finalize_trial(dc, cs, c, sums + (size_t)blockIdx.x * 6);
+        if (decide) {
+            RngSrc rs = ctl->rng;
+            Rng rng{&rs, cs, c, t.draw};
+            const double u = rng.next();
+            commit_trial(dc, cs, c, u <= t.prob ? 1 : 0);
+        }
+    }
+    if (out) {
+        for (int i = 0; i < MMC_NE; i++) { out[i] = t.old_e[i]; out[MMC_NE + i] = t.new_e[i]; }
+        out[2 * MMC_NE] = t.prob;
+    }
+    if (decide && ctl->recs) {
+        mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base];
+        rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
+        rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
+        for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
+    }
+}
+
 
 // positions = COM + offset for every guest slot of every chain (after a bulk upload); grid = (tiles, n_chains)
 __global__ void k_rebuild_positions(DevConst dc, ChainState cs) {

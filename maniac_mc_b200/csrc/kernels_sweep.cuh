@@ -436,9 +436,14 @@ __device__ __forceinline__ void pair_count_flush(const ChainState& cs, const uns
     }
 }
 
-// strict mode: grid = dc.sweep_parts CTAs on the pending trial of chain c; partial sums -> cs.part
-__global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState cs, int c) {
+// strict mode / sharded step: grid = (dc.sweep_parts, chains) CTAs; the sweep_parts CTAs of one row share the pending
+// trial of chain c0 + blockIdx.y; partial sums -> cs.part.  With a k/tile-sharded handle (dc.shard_count > 1, one
+// handle per GPU) this rank's CTAs are parts [shard_rank * sweep_parts, (shard_rank + 1) * sweep_parts) of
+// shard_count * sweep_parts: it visits 1/shard_count of the tiles and owns 1/shard_count of the (kx, ky) rows of A(k).
+__global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState cs, int c0) {
     extern __shared__ __align__(16) unsigned char smem[];
+    const int c = c0 + blockIdx.y;
+    const int part = dc.shard_rank * gridDim.x + blockIdx.x, n_parts = dc.shard_count * gridDim.x;
     const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
     sweep_load_tables(dc, s);
     sweep_stage(dc, cs, c, s);
@@ -446,8 +451,8 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
     double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
     unsigned cnt[2] = {0u, 0u};
-    pair_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, pa, cnt);
-    recip_phase<SWEEP_THREADS>(dc, cs, c, s, blockIdx.x, gridDim.x, ra);
+    pair_phase<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, pa, cnt);
+    recip_phase<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, ra);
     block_sum<6, SWEEP_THREADS>(v, s.red);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;

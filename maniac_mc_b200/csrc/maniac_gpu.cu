@@ -42,6 +42,7 @@ struct mmc_handle {
     std::vector<void*> allocs;
     std::vector<int> h_res_is_fw;          // per residue: 1 = inactive (framework)
     std::vector<int> h_kx, h_ky, h_kz;
+    std::vector<int> h_row_kstart;         // first k of every (kx, ky) row (+ end)
     double* d_w = nullptr;                 // W(k) without the form factor (mmc_get_kvectors)
     double* d_out = nullptr;               // 16 doubles of results
     double* h_out = nullptr;               // pinned mirror
@@ -307,7 +308,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
         if (covered != (size_t)dc.nk) return fail("mmc_init: reciprocal items cover %zu of %d k-vectors", covered, dc.nk);
         int2* pit; int *pirs, *prs;
         CK(dalloc(h, &prs, rs.size())); CK(cudaMemcpy(prs, rs.data(), rs.size() * 4, cudaMemcpyHostToDevice));
-        dc.row_kstart = prs;
+        dc.row_kstart = prs; h->h_row_kstart = rs;
         CK(dalloc(h, &pit, items.size() + 1)); CK(cudaMemcpy(pit, items.data(), items.size() * sizeof(int2), cudaMemcpyHostToDevice));
         CK(dalloc(h, &pirs, irs.size())); CK(cudaMemcpy(pirs, irs.data(), irs.size() * 4, cudaMemcpyHostToDevice));
         dc.kitem = pit; dc.item_row_start = pirs; dc.n_items = (int)items.size();
@@ -361,6 +362,9 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     memset(&dc, 0, sizeof dc);
     dc.nres = d->nres; dc.ntypes = d->ntypes; dc.n_chains = d->n_chains;
     dc.deletion_mode = d->deletion_mode; dc.use_table = d->use_table;
+    dc.shard_count = d->shard_count > 1 ? d->shard_count : 1;
+    dc.shard_rank = d->shard_count > 1 ? d->shard_rank : 0;
+    if (dc.shard_rank < 0 || dc.shard_rank >= dc.shard_count) { delete h; return fail("mmc_init: shard_rank %d outside [0,%d)", d->shard_rank, dc.shard_count); }
     dc.alpha = d->alpha; dc.rc = d->cutoff;
     dc.coul_const = MMC_EPS0_INV_eVA / MMC_KB_eVK;
     dc.p_translation = d->p_translation; dc.p_rotation = d->p_rotation;
@@ -692,32 +696,41 @@ extern "C" int mmc_system_energy(mmc_t* h, int c, double out[MMC_NE]) {
 
 // ---------------------------------------------------------------------------------------------
 static void launch_sweeps(mmc_handle* h, cudaStream_t st, int chain) {
-    k_sweep<<<h->dc.sweep_parts, SWEEP_THREADS, h->sweep_smem, st>>>(h->dc, h->cs, chain);
+    k_sweep<<<dim3(h->dc.sweep_parts, 1), SWEEP_THREADS, h->sweep_smem, st>>>(h->dc, h->cs, chain);
     h->launches += 1;
 }
 
 // ---- strict mode ------------------------------------------------------------------------------
-extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
-                                double old_e[MMC_NE], double new_e[MMC_NE]) {
+static int check_trial(mmc_handle* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new, HostTrial& ht,
+                       const char* who) {
     CHECK_CHAIN(h, c);
     const DevConst& dc = h->dc;
-    if (h->pending_chain >= 0) return fail("mmc_trial_energy: a trial is already pending on chain %d (call mmc_trial_commit first)", h->pending_chain);
+    if (h->pending_chain >= 0) return fail("%s: a trial is already pending on chain %d (call mmc_trial_commit first)", who, h->pending_chain);
+    if (h->pending_chain == -2) return fail("%s: a sharded step is open (call mmc_shard_step_end first)", who);
     if (kind < MMC_CREATION || kind > MMC_ROTATION) return fail("Unknown move_type %d", kind);  // monte_carlo_utils.f90:218
-    if (res < 0 || res >= dc.nres || !dc.is_active[res]) return fail("mmc_trial_energy: residue %d is not an active residue type", res);
+    if (res < 0 || res >= dc.nres || !dc.is_active[res]) return fail("%s: residue %d is not an active residue type", who, res);
     const int cnt = h->h_count[(size_t)c * MMC_MAX_RES + res];
     if (kind == MMC_CREATION) {
-        if (mol != cnt) return fail("mmc_trial_energy: creation must target slot %d (got %d)", cnt, mol);
+        if (mol != cnt) return fail("%s: creation must target slot %d (got %d)", who, cnt, mol);
         if (mol >= dc.cap[res]) return fail("molecule index %d exceeds the maximum allowed = %d", mol + 1, dc.cap[res]);  // CheckMoleculeIndex
-    } else if (mol < 0 || mol >= cnt) return fail("mmc_trial_energy: molecule %d out of range [0,%d)", mol, cnt);
-    if (kind != MMC_DELETION && (!com_new || !offs_new)) return fail("mmc_trial_energy: proposed geometry missing");
-    CK(cudaSetDevice(h->device));
-    HostTrial ht;
+    } else if (mol < 0 || mol >= cnt) return fail("%s: molecule %d out of range [0,%d)", who, mol, cnt);
+    if (kind != MMC_DELETION && (!com_new || !offs_new)) return fail("%s: proposed geometry missing", who);
     memset(&ht, 0, sizeof ht);
     ht.chain = c; ht.kind = kind; ht.res = res; ht.mol = mol;
     if (kind != MMC_DELETION) {
         for (int d = 0; d < 3; d++) ht.com[d] = com_new[d];
         for (int a = 0; a < dc.natoms[res]; a++) for (int d = 0; d < 3; d++) ht.off[a][d] = offs_new[a * 3 + d];
     }
+    return 0;
+}
+
+extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
+                                double old_e[MMC_NE], double new_e[MMC_NE]) {
+    HostTrial ht;
+    if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_trial_energy")) return 1;
+    const DevConst& dc = h->dc;
+    if (dc.shard_count > 1) return fail("mmc_trial_energy: this handle is shard %d of %d; use mmc_shard_trial_begin/_end", dc.shard_rank, dc.shard_count);
+    CK(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
     k_set_trial<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht);
     launch_sweeps(h, st, c);
@@ -729,6 +742,39 @@ extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, con
     if (old_e) memcpy(old_e, h->h_out, MMC_NE * sizeof(double));
     if (new_e) memcpy(new_e, h->h_out + MMC_NE, MMC_NE * sizeof(double));
     h->pending_chain = c; h->pending_kind = kind; h->pending_res = res;
+    return 0;
+}
+
+// k-sharded strict mode: the same trial on every rank; begin leaves this rank's six partial sums in dev_sums (device,
+// enqueued on mmc_stream), the caller all-reduces them in place, end assembles old/new.  mmc_trial_commit as usual.
+extern "C" int mmc_shard_trial_begin(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
+                                     double* dev_sums) {
+    HostTrial ht;
+    if (!dev_sums) return fail("mmc_shard_trial_begin: dev_sums must be a device buffer of 6 doubles");
+    if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_shard_trial_begin")) return 1;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    k_set_trial<<<1, TAIL_THREADS, 0, st>>>(h->dc, h->cs, ht);
+    launch_sweeps(h, st, c);
+    k_part_sum<<<1, TAIL_THREADS, 0, st>>>(h->dc, h->cs, c, dev_sums);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    h->pending_chain = c; h->pending_kind = kind; h->pending_res = res;
+    return 0;
+}
+extern "C" int mmc_shard_trial_end(mmc_t* h, int c, const double* dev_sums, double old_e[MMC_NE], double new_e[MMC_NE]) {
+    CHECK_CHAIN(h, c);
+    if (!dev_sums) return fail("mmc_shard_trial_end: dev_sums missing");
+    if (h->pending_chain != c) return fail("mmc_shard_trial_end: no trial pending on chain %d", c);
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    k_finish<<<1, 32, 0, st>>>(h->dc, h->cs, h->d_ctl, c, dev_sums, 0, h->d_out);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(h->h_out, h->d_out, (2 * MMC_NE + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (old_e) memcpy(old_e, h->h_out, MMC_NE * sizeof(double));
+    if (new_e) memcpy(new_e, h->h_out + MMC_NE, MMC_NE * sizeof(double));
     return 0;
 }
 
@@ -767,6 +813,8 @@ static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
 static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const double* d_tape, int64_t tape_stride,
                          mmc_move_record* d_recs) {
     cudaStream_t st = h->stream;
+    if (h->dc.shard_count > 1) return fail("mmc_run_batch: this handle is shard %d of %d; use mmc_shard_step_begin/_end", h->dc.shard_rank, h->dc.shard_count);
+    if (h->pending_chain == -2) return fail("mmc_run_batch: a sharded step is open");
     BatchCtl ctl;
     ctl.rng.tape = d_tape; ctl.rng.tape_stride = tape_stride; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
     ctl.recs = d_recs; ctl.rec_stride = n_steps; ctl.rec_base = 0;
@@ -882,6 +930,70 @@ extern "C" int mmc_run_batch(mmc_t* h, int64_t n_steps, uint64_t seed, const dou
     CK(cudaMemcpyAsync(h->h_tape_pos, h->cs.tape_pos, C * sizeof(long long), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     return refresh_counts(h);
+}
+
+// ---- k-sharded mode (one handle per GPU, dc.shard_rank / dc.shard_count) ---------------------------------------
+static int shard_check(mmc_handle* h, const void* dev_sums, const char* who) {
+    if (!h) return fail("null handle");
+    if (!dev_sums) return fail("%s: dev_sums must be a device buffer of 6 doubles per trial", who);
+    return 0;
+}
+static int shard_ctl(mmc_handle* h, uint64_t seed, int with_records) {
+    const size_t C = h->dc.n_chains;
+    if (with_records && C > h->recs_cap) {
+        if (h->d_recs) cudaFree(h->d_recs);
+        h->d_recs = nullptr; h->recs_cap = 0;
+        CK(cudaMalloc((void**)&h->d_recs, C * sizeof(mmc_move_record))); h->recs_cap = C;
+    }
+    BatchCtl ctl;
+    ctl.rng.tape = nullptr; ctl.rng.tape_stride = 0; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
+    ctl.recs = with_records ? h->d_recs : nullptr; ctl.rec_stride = 1; ctl.rec_base = 0;
+    CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, h->stream));
+    return 0;
+}
+
+extern "C" int mmc_shard_range(const mmc_t* h, int* k_first, int* k_count) {
+    if (!h) return fail("null handle");
+    const DevConst& dc = h->dc;
+    const int ny = 2 * dc.kmax[1] + 1, nrows = (dc.kmax[0] + 1) * ny;
+    const int n_parts = dc.shard_count * dc.sweep_parts, rpp = (nrows + n_parts - 1) / n_parts;
+    const int r0 = std::min(nrows, dc.shard_rank * dc.sweep_parts * rpp), r1 = std::min(nrows, (dc.shard_rank + 1) * dc.sweep_parts * rpp);
+    if (k_first) *k_first = h->h_row_kstart[r0];
+    if (k_count) *k_count = h->h_row_kstart[r1] - h->h_row_kstart[r0];
+    return 0;
+}
+
+extern "C" int mmc_shard_step_begin(mmc_t* h, uint64_t seed, double* dev_sums) {
+    if (shard_check(h, dev_sums, "mmc_shard_step_begin")) return 1;
+    if (h->pending_chain >= 0) return fail("mmc_shard_step_begin: a strict-mode trial is pending on chain %d", h->pending_chain);
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; const int C = dc.n_chains; cudaStream_t st = h->stream;
+    if (shard_ctl(h, seed, 1)) return 1;
+    k_propose_all<<<C, 32, 0, st>>>(dc, h->cs, h->d_ctl, 0);
+    k_sweep<<<dim3(dc.sweep_parts, C), SWEEP_THREADS, h->sweep_smem, st>>>(dc, h->cs, 0);
+    k_part_sum<<<C, TAIL_THREADS, 0, st>>>(dc, h->cs, 0, dev_sums);
+    h->launches += 3;
+    CK(cudaGetLastError());
+    h->pending_chain = -2;   // a sharded step is open
+    return 0;
+}
+
+extern "C" int mmc_shard_step_end(mmc_t* h, const double* dev_sums, mmc_move_record* records) {
+    if (shard_check(h, dev_sums, "mmc_shard_step_end")) return 1;
+    if (h->pending_chain != -2) return fail("mmc_shard_step_end: no sharded step is open");
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; const int C = dc.n_chains; cudaStream_t st = h->stream;
+    k_finish<<<C, 32, 0, st>>>(dc, h->cs, h->d_ctl, 0, dev_sums, 1, nullptr);
+    h->launches++;
+    CK(cudaGetLastError());
+    h->steps_done += 1;
+    h->pending_chain = -1;
+    if (records) {
+        CK(cudaMemcpyAsync(records, h->d_recs, (size_t)C * sizeof(mmc_move_record), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return refresh_counts(h);
+    }
+    return 0;
 }
 
 extern "C" int64_t mmc_tape_used(mmc_t* h, int c) {

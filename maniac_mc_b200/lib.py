@@ -48,6 +48,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
+    "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
 ]
 
 _lib = None
@@ -89,6 +90,11 @@ def load():
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
     L.mmc_pair_work.argtypes = [vp, C.POINTER(C.c_int64)]
+    L.mmc_shard_step_begin.argtypes = [vp, C.c_uint64, vp]
+    L.mmc_shard_step_end.argtypes = [vp, vp, vp]
+    L.mmc_shard_trial_begin.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, vp]
+    L.mmc_shard_trial_end.argtypes = [vp, C.c_int, vp, dp, dp]
+    L.mmc_shard_range.argtypes = [vp, ip, ip]
     L.mmc_measure_fp64_peak.argtypes = [C.c_int, dp]
     L.mmc_chain_capacity.argtypes = [vp, ip, ip]
     L.mmc_upload_chains.argtypes = [vp, vp, vp, vp]
@@ -135,10 +141,10 @@ def measure_fp64_peak(device=0):
 class ManiacGPU:
     """Device-resident state of n_chains chains of one system."""
 
-    def __init__(self, system: System, n_chains=1, device=0):
+    def __init__(self, system: System, n_chains=1, device=0, shard_rank=0, shard_count=1):
         self.sys = system
         self.n_chains = n_chains
-        self._desc = system.to_desc(n_chains=n_chains, device=device)
+        self._desc = system.to_desc(n_chains=n_chains, device=device, shard_rank=shard_rank, shard_count=shard_count)
         self.h = C.c_void_p()
         _ck(load().mmc_init(C.byref(self.h), C.byref(self._desc)))
         self.nres = system.nres
@@ -294,6 +300,30 @@ class ManiacGPU:
 
     def launch_count(self):
         return load().mmc_launch_count(self.h)
+
+    # ---- k-sharded mode (device buffers are raw addresses, e.g. torch tensor.data_ptr())
+    def shard_step_begin(self, seed, dev_sums):
+        _ck(load().mmc_shard_step_begin(self.h, seed, dev_sums))
+
+    def shard_step_end(self, dev_sums, records=False):
+        recs = np.zeros(self.n_chains, dtype=RECORD_DTYPE) if records else None
+        _ck(load().mmc_shard_step_end(self.h, dev_sums, recs.ctypes.data if records else None))
+        return recs
+
+    def shard_trial_begin(self, kind, res, mol, com_new, offs_new, dev_sums, chain=0):
+        c = None if com_new is None else np.ascontiguousarray(com_new, dtype=np.float64)
+        o = None if offs_new is None else np.ascontiguousarray(offs_new, dtype=np.float64)
+        _ck(load().mmc_shard_trial_begin(self.h, chain, kind, res, mol, _dp(c), _dp(o), dev_sums))
+
+    def shard_trial_end(self, dev_sums, chain=0):
+        old, new = np.zeros(MMC_NE), np.zeros(MMC_NE)
+        _ck(load().mmc_shard_trial_end(self.h, chain, dev_sums, _dp(old), _dp(new)))
+        return old, new
+
+    def shard_range(self):
+        a, b = C.c_int(), C.c_int()
+        _ck(load().mmc_shard_range(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def pair_work(self):
         """(distances formed, pairs inside reach) by the per-move sweeps since mmc_init"""

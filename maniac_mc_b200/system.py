@@ -35,6 +35,8 @@ class MmcDesc(C.Structure):
         ("p_translation", C.c_double), ("p_rotation", C.c_double),
         ("init_sk", C.c_int), ("deletion_mode", C.c_int), ("use_table", C.c_int), ("device", C.c_int),
         ("coulomb_xcut", C.c_double),
+        ("shard_rank", C.c_int),
+        ("shard_count", C.c_int),
     ]
 
 
@@ -136,7 +138,7 @@ class System:
             out[ao[r]:ao[r] + n * na] = c + self.offsets[ao[r]:ao[r] + n * na]
         return out
 
-    def to_desc(self, n_chains=1, device=0):
+    def to_desc(self, n_chains=1, device=0, shard_rank=0, shard_count=1):
         """ctypes mmc_desc; keeps the backing arrays alive on the returned object."""
         d = MmcDesc()
         keep = {}
@@ -166,6 +168,7 @@ class System:
         d.p_translation, d.p_rotation = self.p_translation, self.p_rotation
         d.init_sk, d.deletion_mode, d.use_table, d.device = self.init_sk, self.deletion_mode, self.use_table, device
         d.coulomb_xcut = float(self.coulomb_xcut)
+        d.shard_rank, d.shard_count = int(shard_rank), int(shard_count)
         d._keep = keep
         return d
 

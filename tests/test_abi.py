@@ -65,3 +65,38 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in txt.replace("oracle/maniac_oracle.c:orc_philox_uniform", ""), f"{f} mentions the oracle"
+
+
+def test_fortran_interface_matches_header():
+    """fortran/maniac_gpu_iface.f90 cannot be compiled here (no Fortran compiler): check by text that its bind(C)
+    mmc_desc lists the header's fields in the header's order with matching kinds, and that every bind(C, name=...)
+    it declares is a symbol the library exports."""
+    hdr = open(os.path.join(ROOT, "include", "maniac_gpu.h")).read()
+    body = re.search(r"typedef struct mmc_desc \{(.*?)\} mmc_desc;", hdr, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    c_fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        m = re.match(r"(const\s+)?(int|double)\s*(\*?)\s*(\w+)(\[\d+\])?$", decl)
+        assert m, decl
+        kind = "ptr" if m.group(3) else m.group(2)
+        c_fields.append((m.group(4), kind))
+    f90 = open(os.path.join(ROOT, "fortran", "maniac_gpu_iface.f90")).read()
+    tbody = re.search(r"type, bind\(C\) :: mmc_desc(.*?)end type mmc_desc", f90, re.S).group(1)
+    f_fields = []
+    for line in tbody.splitlines():
+        line = line.split("!")[0].strip()
+        if "::" not in line:
+            continue
+        typ, names = line.split("::")
+        kind = "ptr" if "c_ptr" in typ else "int" if "c_int" in typ else "double"
+        for n in re.findall(r"(\w+)(?:\(\d+\))?", names):
+            f_fields.append((n, kind))
+    assert f_fields == c_fields
+    L = lib.load()
+    names = re.findall(r'bind\(C, name="(\w+)"\)', f90)
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(L, n), f"{n} bound in the Fortran interface but not exported"

@@ -356,3 +356,57 @@ def test_c4_large_k_full_size_identities():
         assert rel_err(tracked, fresh) < 1e-9
         np.testing.assert_allclose(a_tracked, g.sk(c), atol=1e-7)
     g.close()
+
+
+# ---- k-sharded mode (SURVEY 8e optional mode): two emulated ranks on one GPU, the all-reduce replaced by a sum -----
+def test_k_sharded_steps_match_oracle_and_unsharded():
+    from maniac_mc_b200.sharded import emulate_ranks
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    n, seed, C = 80, 4321, 2
+    shards, step, _, _ = emulate_ranks(s, world=2, n_chains=C)
+    recs = np.stack([step(seed, records=True) for _ in range(n)], axis=1)
+    g = ManiacGPU(s, n_chains=C)
+    for c in range(C):
+        g.system_energy(c)
+    whole = g.run_batch(n, seed=seed, records=True)
+    for c in range(C):
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(recs[c], o.run(n, seed=seed, chain=c, step0=0))
+        compare_records(recs[c], whole[c], tol=1e-12)
+        # the shards' owned k ranges tile the k list and their A(k) equal the unsharded A(k)
+        a_ref = g.sk(c); covered = 0
+        for sh in shards:
+            k0, a = sh.owned_sk(c)
+            assert k0 == covered
+            np.testing.assert_allclose(a, a_ref[k0:k0 + len(a)], atol=1e-10)
+            covered += len(a)
+        assert covered == g.nk
+        for sh in shards:                      # every rank holds the same coordinates and tracked energies
+            cnt, com, off, e = sh.gpu.sync_to_host(c); c2, com2, off2, e2 = g.sync_to_host(c)
+            assert np.array_equal(cnt, c2)
+            np.testing.assert_allclose(com, com2, atol=1e-12); np.testing.assert_allclose(off, off2, atol=1e-12)
+            assert rel_err(e, e2) < 1e-11
+    for sh in shards:
+        sh.close()
+    g.close()
+
+
+def test_k_sharded_strict_trial_and_errors():
+    from maniac_mc_b200.sharded import emulate_ranks
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    shards, _, trial_energy, trial_commit = emulate_ranks(s, world=3)
+    g = ManiacGPU(s); g.system_energy()
+    n0 = int(s.count[0]); mo, ao = s.mol_offsets()
+    com = s.com[mo[0]] + np.array([0.4, -0.2, 0.1]); off = s.offsets[ao[0]:ao[0] + int(s.natoms[0])]
+    for kind, mol, cn, of, accept in ((MMC_TRANSLATION, 0, com, off, True), (MMC_CREATION, n0, com + 3.0, off, True),
+                                      (MMC_DELETION, 1, None, None, False), (MMC_DELETION, n0, None, None, True)):
+        o1, n1 = trial_energy(kind, 0, mol, cn, of); o2, n2 = g.trial_energy(kind, 0, mol, cn, of)
+        assert rel_err(o1, o2) < 1e-12 and rel_err(n1, n2) < 1e-12
+        trial_commit(accept); g.trial_commit(accept)
+    with pytest.raises(ManiacGpuError, match="shard"):
+        shards[0].gpu.trial_energy(MMC_DELETION, 0, 0)
+    with pytest.raises(ManiacGpuError, match="shard"):
+        shards[1].gpu.run_batch(4, seed=1)
+    for sh in shards:
+        sh.close()
+    g.close()
