@@ -207,6 +207,7 @@ def run_own(args, rank, world, local_rank):
     import torch.distributed as dist
     from maniac_mc_b200 import lib
     from maniac_mc_b200.lib import ManiacGPU
+    from maniac_mc_b200.system import N_COUNTERS
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -221,7 +222,7 @@ def run_own(args, rank, world, local_rank):
     g_mols, g_atoms = gpu.chain_capacity()
     pin = lambda *shape, dt=torch.float64: torch.zeros(*shape, dtype=dt).pin_memory()
     h_cnt, h_com, h_off = pin(C, s.nres, dt=torch.int32), pin(C, g_mols, 3), pin(C, g_atoms, 3)
-    h_e, h_ctr = pin(C, 6), pin(C, 8, dt=torch.int64)
+    h_e, h_ctr = pin(C, 6), pin(C, N_COUNTERS, dt=torch.int64)
 
     def barrier():
         if world > 1:
@@ -234,7 +235,7 @@ def run_own(args, rank, world, local_rank):
     def counters():
         download()
         names = ["translations", "rotations", "creations", "deletions", "trial_translations", "trial_rotations",
-                 "trial_creations", "trial_deletions"]
+                 "trial_creations", "trial_deletions", "swaps", "trial_swaps"]
         a = h_ctr.numpy().copy()
         return [dict(zip(names, (int(v) for v in row))) for row in a]
 

@@ -9,9 +9,9 @@ module maniac_gpu_iface
     public :: mmc_desc, mmc_init, mmc_destroy, mmc_last_error, mmc_system_energy, mmc_trial_energy, &
               mmc_trial_commit, mmc_sync_to_host, mmc_run_batch, mmc_ewald_setup, mmc_check, &
               mmc_set_chain_params, mmc_run_batch_async, mmc_synchronize, mmc_download_chains, mmc_upload_chains, &
-              mmc_shard_step_begin, mmc_shard_step_end, mmc_shard_trial_begin, mmc_shard_trial_end
+              mmc_shard_step_begin, mmc_shard_step_end, mmc_shard_trial_begin, mmc_shard_trial_end, mmc_trial_energy_swap
 
-    integer(c_int), parameter, public :: MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4
+    integer(c_int), parameter, public :: MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4, MMC_SWAP = 5
     integer(c_int), parameter, public :: MMC_NE = 6
 
     !> struct mmc_desc (field order and types must match include/maniac_gpu.h)
@@ -27,6 +27,7 @@ module maniac_gpu_iface
         integer(c_int) :: init_sk, deletion_mode, use_table, device
         real(c_double) :: coulomb_xcut
         integer(c_int) :: shard_rank, shard_count
+        real(c_double) :: p_swap
     end type mmc_desc
 
     interface
@@ -60,6 +61,14 @@ module maniac_gpu_iface
             import :: c_int, c_ptr, c_double
             type(c_ptr), value :: handle
             integer(c_int), value :: chain, kind, res, mol
+            real(c_double), intent(in) :: com_new(3), offs_new(*)
+            real(c_double), intent(out) :: old_e(6), new_e(6)
+        end function
+        integer(c_int) function mmc_trial_energy_swap(handle, chain, res_old, mol, res_new, com_new, offs_new, old_e, new_e) &
+                bind(C, name="mmc_trial_energy_swap")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle
+            integer(c_int), value :: chain, res_old, mol, res_new
             real(c_double), intent(in) :: com_new(3), offs_new(*)
             real(c_double), intent(out) :: old_e(6), new_e(6)
         end function

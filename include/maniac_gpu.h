@@ -37,7 +37,10 @@ extern "C" {
 #define MMC_NE 6             /* components of an energy vector */
 
 /* move types, parameters.f90:35-38 */
-enum { MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4 };
+enum { MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4,
+       MMC_SWAP = 5 /* identity exchange: advertised (README.md:22), parsed (input_parser.f90:446-452) and given an
+                     * acceptance rule (monte_carlo_utils.f90:228-268) by the reference but never called
+                     * (monte_carlo.f90:50-75); built here as SURVEY.md 8(f).1, off unless p_swap > 0 */ };
 
 /* quirk switches: defaults reproduce the reference */
 enum { MMC_INIT_SK_ZERO = 0, MMC_INIT_SK_FULL = 1 };           /* Q1 */
@@ -89,12 +92,13 @@ typedef struct mmc_desc {
                             * negative = evaluate every pair literally as the reference does */
     int shard_rank;        /* k-sharded mode (ONE large system over several GPUs, one handle per GPU): this handle */
     int shard_count;       /* sweeps part shard_rank of shard_count of the tiles and of the k rows; 0 or 1 = off    */
+    double p_swap;         /* proba%swap (input_parser.f90:446-452); 0 = the reference's de-facto behaviour */
 } mmc_desc;
 
 /* One record per trial move of a batched run (optional output). */
 typedef struct mmc_move_record {
     int32_t kind;     /* MMC_* move type, 0 = no move happened (e.g. translation with N==0) */
-    int32_t res;      /* residue type */
+    int32_t res;      /* residue type; swap: removed type + 256 * inserted type */
     int32_t mol;      /* molecule slot */
     int32_t accepted; /* 1/0 */
     double old_e[MMC_NE];
@@ -102,10 +106,11 @@ typedef struct mmc_move_record {
     double prob;      /* acceptance probability */
 } mmc_move_record;
 
-/* counter_type, simulation_state.f90:19-31 (swap omitted: no swap move exists, monte_carlo.f90:50-75) */
+/* counter_type, simulation_state.f90:19-31 */
 typedef struct mmc_counters {
     int64_t translations, rotations, creations, deletions;
     int64_t trial_translations, trial_rotations, trial_creations, trial_deletions;
+    int64_t swaps, trial_swaps;   /* counter%swap, counter%trial_swap (simulation_state.f90:24,29) */
 } mmc_counters;
 
 typedef struct mmc_handle mmc_t;
@@ -165,6 +170,11 @@ int mmc_trial_energy(mmc_t* handle, int chain, int kind, int res, int mol,
  * A(k) is double buffered: accept flips the buffer, reject costs nothing
  * (replaces Save/RestoreSingleMolFourier, ewald_phase.f90:134,205). */
 int mmc_trial_commit(mmc_t* handle, int chain, int accept);
+/* Strict-mode swap trial (MMC_SWAP): molecule (res_old, mol) is removed and a molecule of type res_new with the
+ * proposed geometry (com_new, offs_new: 3 and 3*natoms(res_new) doubles) is created in slot count(res_new).
+ * old_e / new_e as for a deletion / a creation; commit with mmc_trial_commit. */
+int mmc_trial_energy_swap(mmc_t* handle, int chain, int res_old, int mol, int res_new,
+                          const double* com_new, const double* offs_new, double old_e[MMC_NE], double new_e[MMC_NE]);
 
 /* once per block (PrintStatus / UpdateFiles, monte_carlo.f90:82-84): tracked energies,
  * counts and packed coordinates of one chain */

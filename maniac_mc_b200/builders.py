@@ -74,7 +74,7 @@ def from_files(maniac_path, data_path, inc_path, capacity=None) -> System:
                   box_lo=lo.copy(), box_len=L.copy(), alpha=alpha, cutoff=cutoff, temperature=inp.temperature,
                   fugacity=fug, kmax=kmax, translation_step=inp.translation_step,
                   rotation_step=inp.rotation_step_angle, p_translation=inp.p_translation,
-                  p_rotation=inp.p_rotation, names=[r.name for r in inp.residues],
+                  p_rotation=inp.p_rotation, p_swap=inp.p_swap, names=[r.name for r in inp.residues],
                   ewald_tolerance=inp.ewald_tolerance)
 
 

@@ -43,7 +43,7 @@ struct DevConst {
     double self_e[MMC_MAX_RES];                // ComputeEwaldSelfInteractionSingleMol per residue (K)
     double lo[3], L[3], invL[3], volume;
     double alpha, rc, coul_const, recip_const;  // coul_const = EPS0_INV_eVA/KB_eVK ; recip_const = coul_const*2pi/V
-    double p_translation, p_rotation;
+    double p_translation, p_rotation, p_swap;
     // pointers
     const double *fx, *fy, *fz, *fq;
     const int *ftype, *fmol;
@@ -80,13 +80,16 @@ struct DevConst {
 // one pending trial move of one chain
 struct Trial {
     int kind, res, mol, nat;
+    int res2, nat2;        // NEW atom set: == res, nat except for a swap (the inserted species)
     int do_old, do_new;    // real-space sweeps wanted (ComputeOldEnergy / ComputeNewEnergy pair calls)
     int r_plus, r_minus;   // reciprocal update: A' = A + sum q phi(plus) - sum q phi(minus)
     int excl;              // 1: exclude slot (res, mol) from the sweep
     int accepted, error, draw;
     double prob;
-    double q[MMC_MAX_MOL_ATOMS];
+    double q[MMC_MAX_MOL_ATOMS];          // OLD atom set (the selected molecule)
     int type[MMC_MAX_MOL_ATOMS];
+    double q2[MMC_MAX_MOL_ATOMS];         // NEW atom set
+    int type2[MMC_MAX_MOL_ATOMS];
     double p_old[MMC_MAX_MOL_ATOMS][3];   // absolute positions, old geometry
     double p_new[MMC_MAX_MOL_ATOMS][3];   // absolute positions, proposed geometry
     double p_plus[MMC_MAX_MOL_ATOMS][3];  // positions whose phases are added (== p_new except deletion/reference)

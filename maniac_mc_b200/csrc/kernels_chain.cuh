@@ -33,12 +33,8 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
         }
         __syncthreads();
-        sweep_stage(dc, cs, c, s);
         double v[6] = {0, 0, 0, 0, 0, 0};
-        double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
-        double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
-        if (phases & 1) pair_phase<NT>(dc, cs, c, s, 0, 1, pa, cnt);
-        if (phases & 2) recip_phase<NT>(dc, cs, c, s, 0, 1, ra);
+        sweep_trial<NT>(dc, cs, c, s, 0, 1, phases, v, cnt);
         block_sum<6, NT>(v, s.red);
         if (threadIdx.x == 0) {
             Trial& t = cs.trial[c];
@@ -51,7 +47,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             }
             if (ctl->recs) {
                 mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + st];
-                rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
+                rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? (kind == MMC_SWAP ? t.res + 256 * t.res2 : t.res) : 0; rec.mol = kind > 0 ? t.mol : 0;
                 rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
                 for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
             }

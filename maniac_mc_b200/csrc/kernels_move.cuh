@@ -37,11 +37,14 @@ __device__ inline void rotate_offsets(int axis, double theta, int nat, const dou
 // com_new/off_new (ignored for deletion).  Mirrors which sweeps ComputeOldEnergy /
 // ComputeNewEnergy (monte_carlo_utils.f90:347,275) request for each move type.  Single thread.
 __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int c, int kind, int r, int m,
-                                   const double* com_new, const double (*off_new)[3]) {
+                                   const double* com_new, const double (*off_new)[3], int r2 = -1) {
     Trial& t = cs.trial[c];
     const int nat = dc.natoms[r];
-    t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.accepted = 0; t.prob = 0.0;
+    if (kind != MMC_SWAP) r2 = r;
+    const int nat2 = dc.natoms[r2];
+    t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.res2 = r2; t.nat2 = nat2; t.accepted = 0; t.prob = 0.0;
     for (int a = 0; a < nat; a++) { t.q[a] = dc.q[r][a]; t.type[a] = dc.type[r][a]; }
+    for (int a = 0; a < nat2; a++) { t.q2[a] = dc.q[r2][a]; t.type2[a] = dc.type[r2][a]; }
     const int cnt = cs.count[c * MMC_MAX_RES + r];
     if (kind != MMC_CREATION) {  // old geometry of the selected slot
         const double* com = g_com(dc, cs, c, r, m);
@@ -52,7 +55,7 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
     }
     if (kind != MMC_DELETION) {
         for (int d = 0; d < 3; d++) t.com_new[d] = com_new[d];
-        for (int a = 0; a < nat; a++)
+        for (int a = 0; a < nat2; a++)
             for (int d = 0; d < 3; d++) {
                 t.off_new[a][d] = off_new[a][d];
                 t.p_new[a][d] = com_new[d] + off_new[a][d];
@@ -72,6 +75,21 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
                 for (int d = 0; d < 3; d++) com[d] = com_new[d];
                 for (int a = 0; a < nat; a++) {
                     size_t ia = g_atom(dc, c, r, m, a);
+                    for (int d = 0; d < 3; d++) cs.goff[ia * 3 + d] = off_new[a][d];
+                    cs.gx[ia] = t.p_new[a][0]; cs.gy[ia] = t.p_new[a][1]; cs.gz[ia] = t.p_new[a][2];
+                }
+            }
+            break;
+        case MMC_SWAP:
+            // removed molecule (r, m): old sweep with its own atoms, excluded from both sweeps; inserted molecule of type
+            // r2 in slot count(r2), outside the swept range; like a creation its geometry is written at proposal time
+            t.do_old = 1; t.do_new = 1; t.r_plus = 1; t.r_minus = 1; t.excl = 1;
+            {
+                const int m2 = cs.count[c * MMC_MAX_RES + r2];
+                double* com = g_com(dc, cs, c, r2, m2);
+                for (int d = 0; d < 3; d++) com[d] = com_new[d];
+                for (int a = 0; a < nat2; a++) {
+                    size_t ia = g_atom(dc, c, r2, m2, a);
                     for (int d = 0; d < 3; d++) cs.goff[ia * 3 + d] = off_new[a][d];
                     cs.gx[ia] = t.p_new[a][0]; cs.gy[ia] = t.p_new[a][1]; cs.gz[ia] = t.p_new[a][2];
                 }
@@ -100,10 +118,10 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
 // ----------------------------------------------------------------------------------------------
 // strict mode: the host made the proposal (Fortran RandomTranslation / ApplyRandomRotation /
 // InsertAndOrientMolecule); arguments by value, no H2D copy.
-struct HostTrial { int chain, kind, res, mol; double com[3]; double off[MMC_MAX_MOL_ATOMS][3]; };
+struct HostTrial { int chain, kind, res, mol, res2; double com[3]; double off[MMC_MAX_MOL_ATOMS][3]; };
 
 __global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
-    if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, ht.kind, ht.res, ht.mol, ht.com, ht.off);
+    if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, ht.kind, ht.res, ht.mol, ht.com, ht.off, ht.res2);
 }
 
 // batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
@@ -148,6 +166,31 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             const double* com = g_com(dc, cs, c, r, m);
             for (int d = 0; d < 3; d++) com_new[d] = com[d];
             build_trial(dc, cs, c, MMC_ROTATION, r, m, com_new, off_new);
+        }
+    } else if (draw <= dc.p_rotation + dc.p_translation + dc.p_swap) {
+        // swap (identity exchange): remove (r, m), insert a molecule of another active type at the same
+        // centre of mass with that type's slot-1 template geometry in a random orientation (draws: type pick when more
+        // than two active types, angle, axis)
+        if (dc.n_active >= 2 && m >= 0) {
+            int pick = dc.n_active > 2 ? (int)(rng.next() * (dc.n_active - 1)) : 0;
+            if (pick > dc.n_active - 2) pick = dc.n_active - 2;
+            int r2 = -1;
+            for (int i = 0, k = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (rr == r) continue; if (k == pick) { r2 = rr; break; } k++; }
+            const int m2 = cs.count[c * MMC_MAX_RES + r2], nat2 = dc.natoms[r2];
+            if (m2 >= dc.cap[r2]) { t.error = 1; }
+            else {
+                ctr.trial_swaps++;
+                const double* com = g_com(dc, cs, c, r, m);
+                for (int d = 0; d < 3; d++) com_new[d] = com[d];
+                double tmpl[MMC_MAX_MOL_ATOMS][3];
+                for (int a = 0; a < nat2; a++) for (int d = 0; d < 3; d++) tmpl[a][d] = cs.goff[g_atom(dc, c, r2, 0, a) * 3 + d];
+                if (nat2 != 1) {
+                    const double theta = rng.next() * MMC_TWOPI;
+                    const int axis = (int)(rng.next() * 3.0) + 1;
+                    rotate_offsets(axis, theta, nat2, tmpl, off_new);
+                } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
+                build_trial(dc, cs, c, MMC_SWAP, r, m, com_new, off_new, r2);
+            }
         }
     } else {
         if (rng.next() <= MMC_PROB_CREATE_DELETE) {  // CreateMolecule create_molecule.f90:41-207
@@ -203,6 +246,11 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
         o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
         n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res]; n[4] = intra_energy(dc, t.nat, t.q, t.p_new);
         n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
+    } else if (t.kind == MMC_SWAP) {
+        o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
+        o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
+        n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res2]; n[4] = intra_energy(dc, t.nat2, t.q2, t.p_new);
+        n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
     } else if (t.kind == MMC_DELETION) {
         o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
         o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
@@ -216,6 +264,10 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
     const int cnt = cs.count[c * MMC_MAX_RES + t.res];
     const double V = dc.volume, phi = cs.fug[c * MMC_MAX_RES + t.res], T = cs.temp[c];
     const double de = n[5] - o[5];
+    if (t.kind == MMC_SWAP) {  // mc_acceptance_probability_swap monte_carlo_utils.f90:228-268, counts before the move
+        const double phi2 = cs.fug[c * MMC_MAX_RES + t.res2], n2 = (double)cs.count[c * MMC_MAX_RES + t.res2];
+        t.prob = fmin(1.0, (phi2 / phi) * ((double)cnt / (n2 + 1.0)) * exp(-de / T));
+    } else
     if (t.kind == MMC_CREATION) t.prob = fmin(1.0, (phi * V / (double)(cnt + 1)) * exp(-de / T));
     else if (t.kind == MMC_DELETION) t.prob = fmin(1.0, (((double)(cnt - 1) + 1.0) / (phi * V)) * exp(-de / T));
     else t.prob = fmin(1.0, exp(-de / T));
@@ -256,7 +308,8 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
         E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
         if (t.kind == MMC_CREATION) { ctr.creations++; cnt = cnt + 1; }  // geometry already in the slot
         else {
-            ctr.deletions++;
+            if (t.kind == MMC_SWAP) { ctr.swaps++; cs.count[c * MMC_MAX_RES + t.res2] += 1; }  // inserted geometry already in its slot
+            else ctr.deletions++;
             const int last = cnt - 1;  // RemoveMolecule delete_molecule.f90:99-118: slot[m] <- slot[last]
             if (m != last) {
                 double* com = g_com(dc, cs, c, r, m); const double* cl = g_com(dc, cs, c, r, last);
@@ -345,7 +398,7 @@ __global__ void k_finish(DevConst dc, ChainState cs, const BatchCtl* ctl, int c0
     }
     if (decide && ctl->recs) {
         mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base];
-        rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? t.res : 0; rec.mol = kind > 0 ? t.mol : 0;
+        rec.kind = kind > 0 ? kind : 0; rec.res = kind > 0 ? (kind == MMC_SWAP ? t.res + 256 * t.res2 : t.res) : 0; rec.mol = kind > 0 ? t.mol : 0;
         rec.accepted = kind > 0 ? t.accepted : 0; rec.prob = kind > 0 ? t.prob : 0.0;
         for (int i = 0; i < MMC_NE; i++) { rec.old_e[i] = kind > 0 ? t.old_e[i] : 0.0; rec.new_e[i] = kind > 0 ? t.new_e[i] : 0.0; }
     }

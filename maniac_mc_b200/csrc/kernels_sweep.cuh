@@ -78,29 +78,29 @@ __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const Swee
     for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG; i += blockDim.x) s.gtab[i] = dc.gtab[i];
 }
 
-// Stages the pending Trial of chain c: positions, charges, LJ rows, bounding spheres and the 1-D phase
-// tables (ComputeAtomPhase + ComputePhaseFactors1D, ewald_phase.f90:41-109: direct cos/sin(k theta)).
+// Stages the moved molecule of the pending Trial of chain c for the real-space sweep: positions, charges, LJ rows,
+// bounding spheres.  The Trial carries an OLD atom set (nat, q, type, p_old) and a NEW atom set (nat2, q2, type2,
+// p_new); they are the same molecule for translation / rotation / insertion / deletion and differ for a swap.
+//   pass 0: both sets in one sweep (every move but the swap)
+//   pass 1: swap, removed molecule only (old geometry)      pass 2: swap, inserted molecule only (new geometry)
 // All threads; ends with a barrier.
-__device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
+__device__ inline void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int pass) {
     const Trial& t = cs.trial[c];
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
-    const int nat = t.nat;
+    const bool use_new_set = pass == 2;
+    const int nat = use_new_set ? t.nat2 : t.nat;
+    const double* q = use_new_set ? t.q2 : t.q;
+    const int* type = use_new_set ? t.type2 : t.type;
+    const bool uo = pass == 0 ? t.do_old != 0 : pass == 1, un = pass == 0 ? t.do_new != 0 : pass == 2;
     if (tid == 0) {
-        m.nat = nat; m.kind = t.kind; m.do_old = t.do_old; m.do_new = t.do_new; m.excl = t.excl; m.res = t.res; m.mol = t.mol;
+        m.nat = nat; m.kind = t.kind; m.do_old = uo; m.do_new = un; m.excl = t.excl; m.res = t.res; m.mol = t.mol;
         m.cur = cs.cur[c];
-        // atoms with q == 0 add exactly zero to A(k) (ewald_energy.f90:241-256 multiplies by the charge): no term
-        int n = 0;
-        if (t.kind > 0) {
-            if (t.r_plus) for (int a = 0; a < nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(a + 1);
-            if (t.r_minus) for (int a = 0; a < nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(-(a + 1));
-        }
-        m.nterm = n;
     }
     if (t.kind <= 0) { __syncthreads(); return; }
     if (tid < nat) {
         for (int d = 0; d < 3; d++) { m.po[tid][d] = t.p_old[tid][d]; m.pn[tid][d] = t.p_new[tid][d]; }
-        m.q[tid] = t.q[tid]; m.type[tid] = t.type[tid];
+        m.q[tid] = q[tid]; m.type[tid] = type[tid];
     }
     if (tid < 2) {  // bounding sphere of one geometry: centroid + largest distance + reach
         const double (*p)[3] = tid == 0 ? t.p_old : t.p_new;
@@ -115,7 +115,6 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
         m.cen[tid][0] = cx; m.cen[tid][1] = cy; m.cen[tid][2] = cz; m.cen[tid][3] = sqrt(r2) * (1.0 + 1e-12) + dc.reach;
     }
     if (tid == 32) {  // common sphere of the swept geometries, and whether the single-shift path is exact
-        const bool uo = t.do_old, un = t.do_new;
         double cx = 0, cy = 0, cz = 0; int n = 0;
         for (int a = 0; a < nat; a++) {
             if (uo) { cx += t.p_old[a][0]; cy += t.p_old[a][1]; cz += t.p_old[a][2]; n++; }
@@ -133,11 +132,31 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
     }
     for (int i = tid; i < nat * dc.ntypes; i += blockDim.x) {
         const int a = i / dc.ntypes, tj = i % dc.ntypes;
-        const double2 v = dc.lj[t.type[a] * dc.ntypes + tj];
+        const double2 v = dc.lj[type[a] * dc.ntypes + tj];
         s.lj[i] = make_double2(v.x * v.x, v.y);
     }
-    __syncthreads();  // term map
-    // phase tables, one row per reciprocal term (charge and sign folded into Z)
+    __syncthreads();
+}
+
+// Stages the reciprocal terms of the pending Trial: the term map and the 1-D phase tables (ComputeAtomPhase +
+// ComputePhaseFactors1D, ewald_phase.f90:41-109: direct cos/sin(k theta)), one row per term with the charge and the
+// sign folded into Z.  Added atoms come from the NEW set (p_plus, q2), removed atoms from the OLD set (p_old, q).
+// All threads; ends with a barrier.
+__device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
+    const Trial& t = cs.trial[c];
+    MolS& m = *s.mol;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        // atoms with q == 0 add exactly zero to A(k) (ewald_energy.f90:241-256 multiplies by the charge): no term
+        int n = 0;
+        if (t.kind > 0) {
+            if (t.r_plus) for (int a = 0; a < t.nat2; a++) if (t.q2[a] != 0.0) m.term[n++] = (signed char)(a + 1);
+            if (t.r_minus) for (int a = 0; a < t.nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(-(a + 1));
+        }
+        m.nterm = n;
+    }
+    __syncthreads();
+    if (t.kind <= 0) return;
     const int nterm = m.nterm;
     const int per = s.nx + s.ny + s.nz;
     for (int i = tid; i < nterm * per; i += blockDim.x) {
@@ -153,7 +172,7 @@ __device__ inline void sweep_stage(const DevConst& dc, const ChainState& cs, int
         const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
         double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
         if (k < 0) sn = -sn;
-        if (ax == 2) { const double q = plus ? t.q[a] : -t.q[a]; co *= q; sn *= q; }
+        if (ax == 2) { const double q = plus ? t.q2[a] : -t.q[a]; co *= q; sn *= q; }
         *dst = make_double2(co, sn);
     }
     __syncthreads();
@@ -426,6 +445,26 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
     }
 }
 
+// One trial of chain c, all threads of the CTA: stage, real-space sweep(s), reciprocal sweep.  `part` of `n_parts`
+// CTAs share the trial (1 of 1 in batched mode).  phases: bit 0 real space, bit 1 reciprocal.
+// v = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} (per-thread partials).
+template <int NT>
+__device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                   int phases, double (&v)[6], unsigned (&cnt)[2]) {
+    double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
+    double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
+    const bool swap = cs.trial[c].kind == MMC_SWAP;
+    stage_terms(dc, cs, c, s);
+    stage_molecule(dc, cs, c, s, swap ? 1 : 0);
+    if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
+    if (swap) {   // second real-space sweep: the inserted molecule (different atom set) against everything but the removed one
+        __syncthreads();
+        stage_molecule(dc, cs, c, s, 2);
+        if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
+    }
+    if (phases & 2) recip_phase<NT>(dc, cs, c, s, part, n_parts, ra);
+}
+
 // executed-work counters of the real-space sweep (bench.py's executed-flop figure): cs.pair_count[0] += distances
 // formed, [1] += pairs inside reach (Coulomb table and/or LJ evaluated).  One atomic pair per warp per launch.
 __device__ __forceinline__ void pair_count_flush(const ChainState& cs, const unsigned (&cnt)[2]) {
@@ -446,13 +485,9 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     const int part = dc.shard_rank * gridDim.x + blockIdx.x, n_parts = dc.shard_count * gridDim.x;
     const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
     sweep_load_tables(dc, s);
-    sweep_stage(dc, cs, c, s);
     double v[6] = {0, 0, 0, 0, 0, 0};
-    double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
-    double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
     unsigned cnt[2] = {0u, 0u};
-    pair_phase<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, pa, cnt);
-    recip_phase<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, ra);
+    sweep_trial<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, 3, v, cnt);
     block_sum<6, SWEEP_THREADS>(v, s.red);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;

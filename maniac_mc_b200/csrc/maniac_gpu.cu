@@ -55,7 +55,7 @@ struct mmc_handle {
     cudaGraphExec_t graph = nullptr; int graph_steps = 0;
     BatchCtl* d_ctl = nullptr;
     std::vector<int> h_count;              // host mirror of count[C][MMC_MAX_RES]
-    int pending_kind = 0, pending_res = 0;
+    int pending_kind = 0, pending_res = 0, pending_res2 = 0;
     int64_t launches = 0;
     unsigned long long steps_done = 0;     // Philox step counter across batches
     int pending_chain = -1;
@@ -367,7 +367,7 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     if (dc.shard_rank < 0 || dc.shard_rank >= dc.shard_count) { delete h; return fail("mmc_init: shard_rank %d outside [0,%d)", d->shard_rank, dc.shard_count); }
     dc.alpha = d->alpha; dc.rc = d->cutoff;
     dc.coul_const = MMC_EPS0_INV_eVA / MMC_KB_eVK;
-    dc.p_translation = d->p_translation; dc.p_rotation = d->p_rotation;
+    dc.p_translation = d->p_translation; dc.p_rotation = d->p_rotation; dc.p_swap = d->p_swap;
     dc.volume = d->box_len[0] * d->box_len[1] * d->box_len[2];
     dc.recip_const = MMC_EPS0_INV_eVA / MMC_KB_eVK * MMC_TWOPI / dc.volume;
     int kmaxmax = 0;
@@ -702,47 +702,66 @@ static void launch_sweeps(mmc_handle* h, cudaStream_t st, int chain) {
 
 // ---- strict mode ------------------------------------------------------------------------------
 static int check_trial(mmc_handle* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new, HostTrial& ht,
-                       const char* who) {
+                       const char* who, int res2 = -1) {
     CHECK_CHAIN(h, c);
     const DevConst& dc = h->dc;
     if (h->pending_chain >= 0) return fail("%s: a trial is already pending on chain %d (call mmc_trial_commit first)", who, h->pending_chain);
     if (h->pending_chain == -2) return fail("%s: a sharded step is open (call mmc_shard_step_end first)", who);
-    if (kind < MMC_CREATION || kind > MMC_ROTATION) return fail("Unknown move_type %d", kind);  // monte_carlo_utils.f90:218
+    if (kind < MMC_CREATION || kind > MMC_SWAP) return fail("Unknown move_type %d", kind);  // monte_carlo_utils.f90:218
     if (res < 0 || res >= dc.nres || !dc.is_active[res]) return fail("%s: residue %d is not an active residue type", who, res);
     const int cnt = h->h_count[(size_t)c * MMC_MAX_RES + res];
+    int nat_new = dc.natoms[res];
+    if (kind == MMC_SWAP) {
+        if (res2 < 0 || res2 >= dc.nres || !dc.is_active[res2] || res2 == res) return fail("%s: swap needs a second, different active residue type (got %d)", who, res2);
+        const int cnt2 = h->h_count[(size_t)c * MMC_MAX_RES + res2];
+        if (cnt2 >= dc.cap[res2]) return fail("molecule index %d exceeds the maximum allowed = %d", cnt2 + 1, dc.cap[res2]);
+        nat_new = dc.natoms[res2];
+    }
     if (kind == MMC_CREATION) {
         if (mol != cnt) return fail("%s: creation must target slot %d (got %d)", who, cnt, mol);
         if (mol >= dc.cap[res]) return fail("molecule index %d exceeds the maximum allowed = %d", mol + 1, dc.cap[res]);  // CheckMoleculeIndex
     } else if (mol < 0 || mol >= cnt) return fail("%s: molecule %d out of range [0,%d)", who, mol, cnt);
     if (kind != MMC_DELETION && (!com_new || !offs_new)) return fail("%s: proposed geometry missing", who);
     memset(&ht, 0, sizeof ht);
-    ht.chain = c; ht.kind = kind; ht.res = res; ht.mol = mol;
+    ht.chain = c; ht.kind = kind; ht.res = res; ht.mol = mol; ht.res2 = kind == MMC_SWAP ? res2 : res;
     if (kind != MMC_DELETION) {
         for (int d = 0; d < 3; d++) ht.com[d] = com_new[d];
-        for (int a = 0; a < dc.natoms[res]; a++) for (int d = 0; d < 3; d++) ht.off[a][d] = offs_new[a * 3 + d];
+        for (int a = 0; a < nat_new; a++) for (int d = 0; d < 3; d++) ht.off[a][d] = offs_new[a * 3 + d];
     }
+    h->pending_res2 = ht.res2;
     return 0;
 }
 
-extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
-                                double old_e[MMC_NE], double new_e[MMC_NE]) {
-    HostTrial ht;
-    if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_trial_energy")) return 1;
+static int trial_energy_impl(mmc_handle* h, const HostTrial& ht, double old_e[MMC_NE], double new_e[MMC_NE], const char* who) {
     const DevConst& dc = h->dc;
-    if (dc.shard_count > 1) return fail("mmc_trial_energy: this handle is shard %d of %d; use mmc_shard_trial_begin/_end", dc.shard_rank, dc.shard_count);
+    if (dc.shard_count > 1) return fail("%s: this handle is shard %d of %d; use mmc_shard_trial_begin/_end", who, dc.shard_rank, dc.shard_count);
     CK(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
     k_set_trial<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht);
-    launch_sweeps(h, st, c);
-    k_finalize<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, c, h->d_out);
+    launch_sweeps(h, st, ht.chain);
+    k_finalize<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht.chain, h->d_out);
     h->launches += 2;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(h->h_out, h->d_out, (2 * MMC_NE + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (old_e) memcpy(old_e, h->h_out, MMC_NE * sizeof(double));
     if (new_e) memcpy(new_e, h->h_out + MMC_NE, MMC_NE * sizeof(double));
-    h->pending_chain = c; h->pending_kind = kind; h->pending_res = res;
+    h->pending_chain = ht.chain; h->pending_kind = ht.kind; h->pending_res = ht.res;
     return 0;
+}
+
+extern "C" int mmc_trial_energy(mmc_t* h, int c, int kind, int res, int mol, const double* com_new, const double* offs_new,
+                                double old_e[MMC_NE], double new_e[MMC_NE]) {
+    HostTrial ht;
+    if (kind == MMC_SWAP) return fail("mmc_trial_energy: a swap names two residue types; use mmc_trial_energy_swap");
+    if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_trial_energy")) return 1;
+    return trial_energy_impl(h, ht, old_e, new_e, "mmc_trial_energy");
+}
+extern "C" int mmc_trial_energy_swap(mmc_t* h, int c, int res_old, int mol, int res_new, const double* com_new, const double* offs_new,
+                                     double old_e[MMC_NE], double new_e[MMC_NE]) {
+    HostTrial ht;
+    if (check_trial(h, c, MMC_SWAP, res_old, mol, com_new, offs_new, ht, "mmc_trial_energy_swap", res_new)) return 1;
+    return trial_energy_impl(h, ht, old_e, new_e, "mmc_trial_energy_swap");
 }
 
 // k-sharded strict mode: the same trial on every rank; begin leaves this rank's six partial sums in dev_sums (device,
@@ -751,6 +770,7 @@ extern "C" int mmc_shard_trial_begin(mmc_t* h, int c, int kind, int res, int mol
                                      double* dev_sums) {
     HostTrial ht;
     if (!dev_sums) return fail("mmc_shard_trial_begin: dev_sums must be a device buffer of 6 doubles");
+    if (kind == MMC_SWAP) return fail("mmc_shard_trial_begin: swap trials are not available through the sharded strict entry point");
     if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_shard_trial_begin")) return 1;
     CK(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
@@ -788,6 +808,7 @@ extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
     if (accept) {
         if (h->pending_kind == MMC_CREATION) h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res]++;
         if (h->pending_kind == MMC_DELETION) h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res]--;
+        if (h->pending_kind == MMC_SWAP) { h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res]--; h->h_count[(size_t)c * MMC_MAX_RES + h->pending_res2]++; }
     }
     h->pending_chain = -1;
     return 0;

@@ -22,7 +22,7 @@ import math
 import numpy as np
 
 from .lib import ManiacGPU
-from .system import (E_COUL, E_INTRA, E_NONCOUL, E_RECIP, E_SELF, E_TOTAL, MMC_CREATION, MMC_DELETION, MMC_ROTATION,
+from .system import (E_COUL, E_INTRA, E_NONCOUL, E_RECIP, E_SELF, E_TOTAL, MMC_CREATION, MMC_DELETION, MMC_ROTATION, MMC_SWAP,
                      MMC_TRANSLATION, RECORD_DTYPE, System)
 
 TWOPI = 2.0 * 3.14159265358979323846
@@ -69,7 +69,7 @@ class StrictDriver:
         self.translation_step, self.rotation_step = s.translation_step, s.rotation_step
         self.recalibrate = recalibrate
         self.counter = dict(translations=0, rotations=0, creations=0, deletions=0, trial_translations=0,
-                            trial_rotations=0, trial_creations=0, trial_deletions=0)
+                            trial_rotations=0, trial_creations=0, trial_deletions=0, swaps=0, trial_swaps=0)
         self.energy = np.zeros(6)
 
     # ComputeSystemEnergy energy_utils.f90:18
@@ -197,6 +197,44 @@ class StrictDriver:
         self.gpu.trial_commit(acc, chain=self.chain)
         return self._record(MMC_DELETION, r, m, acc, old, new, p)
 
+    # mc_acceptance_probability_swap monte_carlo_utils.f90:228-268 (counts before the move)
+    def mc_acceptance_probability_swap(self, old, new, type_old, type_new):
+        de = new[E_TOTAL] - old[E_TOTAL]
+        try:
+            ex = math.exp(-de / self.sys.temperature)
+        except OverflowError:
+            ex = math.inf
+        comb = float(self.count[type_old]) / (float(self.count[type_new]) + 1.0)
+        return min(1.0, (float(self.sys.fugacity[type_new]) / float(self.sys.fugacity[type_old])) * comb * ex)
+
+    def SwapMolecule(self, rng, r, m):
+        """Identity exchange: the reference ships only the acceptance rule above and never calls the move
+        (monte_carlo.f90:50-75); the move is composed from its deletion and creation steps: remove (r, m), insert a
+        molecule of another active type at the same centre of mass (slot-1 template, random orientation)."""
+        s = self.sys
+        active = [i for i in range(s.nres) if s.is_active[i] == 1]
+        if len(active) < 2 or m < 0:
+            return None
+        pick = min(int(rng() * (len(active) - 1)), len(active) - 2) if len(active) > 2 else 0
+        r2 = [i for i in active if i != r][pick]
+        m2 = int(self.count[r2])
+        if m2 >= s.capacity[r2]:
+            raise RuntimeError("molecule index exceeds NB_MAX_MOLECULE")
+        self.counter["trial_swaps"] += 1
+        com = self.com[r][m].copy()
+        off = self.ApplyRandomRotation(rng, self.off[r2][0], full=True)
+        self.com[r2][m2] = com; self.off[r2][m2] = off
+        old, new = self.gpu.trial_energy_swap(r, m, r2, com, off, chain=self.chain)
+        p = self.mc_acceptance_probability_swap(old, new, r, r2)
+        acc = rng() <= p
+        if acc:
+            self._accept_insdel(old, new); self.counter["swaps"] += 1
+            last = self.count[r] - 1
+            self.com[r][m] = self.com[r][last]; self.off[r][m] = self.off[r][last]
+            self.count[r] -= 1; self.count[r2] += 1
+        self.gpu.trial_commit(acc, chain=self.chain)
+        return self._record(MMC_SWAP, r + 256 * r2, m, acc, old, new, p)
+
     def AdjustMoveStepSizes(self):  # monte_carlo_utils.f90:99-129 (single-precision ratios, Q6)
         if not self.recalibrate:
             return
@@ -226,6 +264,8 @@ class StrictDriver:
             return self.Translation(rng, r, m)
         if draw <= s.p_rotation + s.p_translation:
             return self.Rotation(rng, r, m)
+        if draw <= s.p_rotation + s.p_translation + s.p_swap:
+            return self.SwapMolecule(rng, r, m)
         if rng() <= PROB_CREATE_DELETE:
             return self.CreateMolecule(rng, r, int(self.count[r]))
         return self.DeleteMolecule(rng, r, m)

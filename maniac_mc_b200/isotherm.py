@@ -16,6 +16,8 @@ from dataclasses import dataclass
 
 import numpy as np
 
+from .system import N_COUNTERS
+
 
 def fugacity_points(n_points=64, lo_atm=1.0e-2, hi_atm=1.0e4):
     """log-spaced fugacities in atm"""
@@ -59,7 +61,7 @@ class BlockAverages:
         self.sum_n = np.zeros(n_chains)
         self.sum_e = np.zeros(n_chains)
         self.sum_n2 = np.zeros(n_chains)
-        self.counters = np.zeros((n_chains, 8), dtype=np.int64)
+        self.counters = np.zeros((n_chains, N_COUNTERS), dtype=np.int64)
 
     def add(self, counts, energies, counters=None):
         c = np.asarray(counts, dtype=np.float64)
@@ -71,7 +73,7 @@ class BlockAverages:
             self.counters = np.asarray(counters, dtype=np.int64).copy()
 
     def rows(self):
-        """[n_chains, 4 + 8]: mean N, var N, mean E_total, blocks, then the 8 move counters"""
+        """[n_chains, 4 + N_COUNTERS]: mean N, var N, mean E_total, blocks, then the move counters"""
         m = max(self.n, 1)
         mean_n = self.sum_n / m
         var_n = np.maximum(self.sum_n2 / m - mean_n ** 2, 0.0)
@@ -139,7 +141,7 @@ class IsothermSweep:
         g_mols, g_atoms = self.gpu.chain_capacity()
         C = self.gpu.n_chains
         self._cnt = np.zeros((C, system.nres), dtype=np.int32)
-        self._e = np.zeros((C, 6)); self._ctr = np.zeros((C, 8), dtype=np.int64)
+        self._e = np.zeros((C, 6)); self._ctr = np.zeros((C, N_COUNTERS), dtype=np.int64)
 
     def run_block(self, n_steps, seed=0):
         """one block of `n_steps` MC steps on every local chain, then one sample of N, E and the counters

@@ -43,7 +43,7 @@ def build(force=False, verbose=False):
 ABI_SYMBOLS = [
     "mmc_ewald_setup", "mmc_init", "mmc_destroy", "mmc_last_error", "mmc_num_kvectors", "mmc_get_kvectors",
     "mmc_set_chain_params", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
-    "mmc_system_energy", "mmc_trial_energy", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk",
+    "mmc_system_energy", "mmc_trial_energy", "mmc_trial_energy_swap", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk",
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
@@ -76,6 +76,7 @@ def load():
     L.mmc_system_energy.argtypes = [vp, C.c_int, dp]
     L.mmc_trial_energy.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_trial_commit.argtypes = [vp, C.c_int, C.c_int]
+    L.mmc_trial_energy_swap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_sync_to_host.argtypes = [vp, C.c_int, ip, dp, dp, dp]
     L.mmc_get_sk.argtypes = [vp, C.c_int, dp]
     L.mmc_run_batch.argtypes = [vp, C.c_int64, C.c_uint64, dp, C.c_int64, vp, vp]
@@ -229,6 +230,12 @@ class ManiacGPU:
         c = None if com_new is None else np.ascontiguousarray(com_new, dtype=np.float64)
         o = None if offs_new is None else np.ascontiguousarray(offs_new, dtype=np.float64)
         _ck(load().mmc_trial_energy(self.h, chain, kind, res, mol, _dp(c), _dp(o), _dp(old), _dp(new)))
+        return old, new
+
+    def trial_energy_swap(self, res_old, mol, res_new, com_new, offs_new, chain=0):
+        old, new = np.zeros(MMC_NE), np.zeros(MMC_NE)
+        c = np.ascontiguousarray(com_new, dtype=np.float64); o = np.ascontiguousarray(offs_new, dtype=np.float64)
+        _ck(load().mmc_trial_energy_swap(self.h, chain, res_old, mol, res_new, _dp(c), _dp(o), _dp(old), _dp(new)))
         return old, new
 
     def trial_commit(self, accept, chain=0):

@@ -15,7 +15,7 @@ import numpy as np
 from . import readers
 
 MMC_NE = 6
-MMC_CREATION, MMC_DELETION, MMC_TRANSLATION, MMC_ROTATION = 1, 2, 3, 4
+MMC_CREATION, MMC_DELETION, MMC_TRANSLATION, MMC_ROTATION, MMC_SWAP = 1, 2, 3, 4, 5
 E_NONCOUL, E_COUL, E_RECIP, E_SELF, E_INTRA, E_TOTAL = range(6)
 
 
@@ -37,6 +37,7 @@ class MmcDesc(C.Structure):
         ("coulomb_xcut", C.c_double),
         ("shard_rank", C.c_int),
         ("shard_count", C.c_int),
+        ("p_swap", C.c_double),
     ]
 
 
@@ -47,11 +48,14 @@ class MoveRecord(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [(n, C.c_int64) for n in ("translations", "rotations", "creations", "deletions",
-                                         "trial_translations", "trial_rotations", "trial_creations", "trial_deletions")]
+                                         "trial_translations", "trial_rotations", "trial_creations", "trial_deletions",
+                                         "swaps", "trial_swaps")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
+
+N_COUNTERS = len(Counters._fields_)   # int64 words of one mmc_counters
 
 RECORD_DTYPE = np.dtype([("kind", "<i4"), ("res", "<i4"), ("mol", "<i4"), ("accepted", "<i4"),
                          ("old_e", "<f8", (MMC_NE,)), ("new_e", "<f8", (MMC_NE,)), ("prob", "<f8")])
@@ -99,6 +103,7 @@ class System:
     rotation_step: float = 0.685
     p_translation: float = 0.25
     p_rotation: float = 0.25
+    p_swap: float = 0.0         # proba%swap; 0 = the reference's de-facto behaviour (the move is never called there)
     init_sk: int = 0
     deletion_mode: int = 0
     use_table: int = 0
@@ -166,6 +171,7 @@ class System:
         d.alpha, d.cutoff, d.temperature = self.alpha, self.cutoff, self.temperature
         d.translation_step, d.rotation_step = self.translation_step, self.rotation_step
         d.p_translation, d.p_rotation = self.p_translation, self.p_rotation
+        d.p_swap = float(self.p_swap)
         d.init_sk, d.deletion_mode, d.use_table, d.device = self.init_sk, self.deletion_mode, self.use_table, device
         d.coulomb_xcut = float(self.coulomb_xcut)
         d.shard_rank, d.shard_count = int(shard_rank), int(shard_count)
@@ -176,7 +182,7 @@ class System:
     _ARRS = ("natoms", "is_active", "count", "capacity", "charges", "types", "sigma", "epsilon", "com",
              "offsets", "box_lo", "box_len", "fugacity")
     _SCAL = ("alpha", "cutoff", "temperature", "translation_step", "rotation_step", "p_translation",
-             "p_rotation", "init_sk", "deletion_mode", "use_table", "ewald_tolerance")
+             "p_rotation", "p_swap", "init_sk", "deletion_mode", "use_table", "ewald_tolerance")
 
     def save(self, path):
         d = {k: getattr(self, k) for k in self._ARRS}
@@ -189,6 +195,8 @@ class System:
         z = np.load(path)
         kw = {k: z[k] for k in cls._ARRS}
         for k in cls._SCAL:
+            if k not in z.files:
+                continue
             v = z[k].item()
             kw[k] = int(v) if k in ("init_sk", "deletion_mode", "use_table") else float(v)
         kw["kmax"] = [int(v) for v in z["kmax"]]

@@ -59,7 +59,7 @@ typedef struct orc {
     double **off;  /* off[r][(m*natoms[r] + a)*3 + d]      primary%site_offset(d,r,m,a)  */
     double lo[3], L[3], volume;
     double alpha, rc, T; double* fugacity;
-    double translation_step, rotation_step, p_translation, p_rotation;
+    double translation_step, rotation_step, p_translation, p_rotation, p_swap;
     int kmax[3], nk; int *kx, *ky, *kz; double *ksq_mag, *form, *W;
     cplx *A, *A_old;                     /* ewald%recip_amplitude(_old) */
     cplx **px, **py, **pz;               /* ewald%phase_factor_{x,y,z}(r, m, a, -kmax:kmax) */
@@ -232,7 +232,7 @@ orc_t* orc_create(const mmc_desc* d) {
     o->volume = o->L[0] * o->L[1] * o->L[2];
     o->alpha = d->alpha; o->rc = d->cutoff; o->T = d->temperature;
     o->translation_step = d->translation_step; o->rotation_step = d->rotation_step;
-    o->p_translation = d->p_translation; o->p_rotation = d->p_rotation;
+    o->p_translation = d->p_translation; o->p_rotation = d->p_rotation; o->p_swap = d->p_swap;
     o->init_sk = d->init_sk; o->deletion_mode = d->deletion_mode; o->use_table = d->use_table;
     /* coordinates */
     o->com = malloc(nr * sizeof(double*)); o->off = malloc(nr * sizeof(double*));
@@ -730,6 +730,62 @@ static void delete_molecule(orc_t* o, int r, int m, mmc_move_record* rec) {
     fill_record(rec, MMC_DELETION, r, m, acc, old, nw, p);
 }
 
+/* Swap (identity exchange), SURVEY 8(f).1.  The reference only ships the acceptance rule
+ * (mc_acceptance_probability_swap, monte_carlo_utils.f90:228-268: min(1, phi_new/phi_old * N_old/(N_new+1) * exp(-dE/T)),
+ * counts read before the move); the move itself is composed here from the reference's own deletion and creation
+ * building blocks: ComputeOldEnergy(deletion) of (rA, m), physical removal (is_deletion branch of
+ * ComputeRecipEnergySingleMol + RemoveMolecule), insertion of a type-rB molecule at the SAME centre of mass with the
+ * slot-1 template geometry and a random orientation (create_molecule.f90:195-199), ComputeNewEnergy(creation).
+ * Draws: type pick (only if more than two active types exist), rotation angle, axis, accept. */
+static int swap_molecule(orc_t* o, int rA, int m, mmc_move_record* rec) {
+    int n_active = 0;
+    for (int i = 0; i < o->nres; i++) if (o->is_active[i] == 1) n_active++;
+    if (n_active < 2 || m < 0) return 0;
+    int pick = n_active > 2 ? (int)(rand_uniform(o) * (n_active - 1)) : 0;
+    if (pick > n_active - 2) pick = n_active - 2;
+    int rB = -1;
+    for (int i = 0, k = 0; i < o->nres; i++) if (o->is_active[i] == 1 && i != rA) { if (k == pick) { rB = i; break; } k++; }
+    const int mB = o->count[rB], naA = o->natoms[rA], naB = o->natoms[rB];
+    if (mB >= o->cap[rB]) return 1;
+    double old[MMC_NE], nw[MMC_NE];
+    o->cnt.trial_swaps++;
+    const double N_old = (double)o->count[rA], N_new = (double)o->count[rB];
+    orc_compute_old_energy(o, rA, m, old, 0, 1);
+    orc_save_fourier(o, rA, m);                       /* phases of (rA, m) and A(k) */
+    memcpy(o->com_old, o->com[rA] + 3 * m, sizeof(double) * 3);
+    memcpy(o->off_old, o->off[rA] + (size_t)m * naA * 3, sizeof(double) * 3 * naA);
+    orc_recip_singlemol(o, rA, m, 0, 1);              /* A(k) -= sum q phi(old) */
+    const int last = o->count[rA] - 1;
+    memmove(o->com[rA] + 3 * m, o->com[rA] + 3 * last, sizeof(double) * 3);
+    memmove(o->off[rA] + (size_t)m * naA * 3, o->off[rA] + (size_t)last * naA * 3, sizeof(double) * 3 * naA);
+    orc_replace_fourier(o, rA, m, last);
+    o->count[rA]--;
+    /* the new molecule: same COM, template geometry of slot 1 of its type, random orientation */
+    memcpy(o->com[rB] + 3 * mB, o->com_old, sizeof(double) * 3);
+    if (mB != 0) memcpy(o->off[rB] + (size_t)mB * naB * 3, o->off[rB], sizeof(double) * 3 * naB);
+    o->count[rB]++;
+    apply_random_rotation(o, rB, mB, 1);
+    orc_single_mol_fourier(o, rB, mB);
+    nw[MMC_E_RECIP] = orc_recip_singlemol(o, rB, mB, 1, 0);
+    orc_pair_singlemol(o, rB, mB, &nw[MMC_E_NONCOUL], &nw[MMC_E_COUL]);
+    nw[MMC_E_SELF] = orc_self_singlemol(o, rB);
+    nw[MMC_E_INTRA] = orc_intra_singlemol(o, rB, mB);
+    set_total(nw, 1);
+    const double de = nw[MMC_E_TOTAL] - old[MMC_E_TOTAL];
+    const double p = fmin(1.0, (o->fugacity[rB] / o->fugacity[rA]) * (N_old / (N_new + 1.0)) * exp(-de / o->T));
+    const int acc = rand_uniform(o) <= p;
+    if (acc) { accept_insdel(o, old, nw); o->cnt.swaps++; }
+    else {
+        o->count[rB]--;
+        o->count[rA]++;
+        memcpy(o->com[rA] + 3 * m, o->com_old, sizeof(double) * 3);
+        memcpy(o->off[rA] + (size_t)m * naA * 3, o->off_old, sizeof(double) * 3 * naA);
+        orc_restore_fourier(o, rA, m);
+    }
+    fill_record(rec, MMC_SWAP, rA + 256 * rB, m, acc, old, nw, p);
+    return 0;
+}
+
 /* AdjustMoveStepSizes monte_carlo_utils.f90:99-129 (single-precision ratios, Q6) */
 void orc_adjust_step_sizes(orc_t* o) {
     if (!o->recalibrate) return;
@@ -760,6 +816,7 @@ static int mc_step(orc_t* o, mmc_move_record* rec) {
     double draw = rand_uniform(o);
     if (draw <= o->p_translation) translation(o, r, m, rec);
     else if (draw <= o->p_rotation + o->p_translation) rotation(o, r, m, rec);
+    else if (draw <= o->p_rotation + o->p_translation + o->p_swap) return swap_molecule(o, r, m, rec);
     else {
         if (rand_uniform(o) <= PROB_CREATE_DELETE) return create_molecule(o, r, o->count[r], rec);
         else delete_molecule(o, r, m, rec);
@@ -791,6 +848,7 @@ int orc_single_move(orc_t* o, int kind, int r, int m, const double* tape, int64_
         case MMC_ROTATION: rotation(o, r, m, rec); break;
         case MMC_CREATION: return create_molecule(o, r, o->count[r], rec);
         case MMC_DELETION: delete_molecule(o, r, m, rec); break;
+        case MMC_SWAP: return swap_molecule(o, r, m, rec);
         default: return 3;
     }
     return 0;

@@ -410,3 +410,79 @@ def test_k_sharded_strict_trial_and_errors():
     for sh in shards:
         sh.close()
     g.close()
+
+
+# ---- swap move on the reference's two-species example ZIF8-CH4O-H2O ---------------------------------
+def two_species(**over):
+    s = load_system("zif8_ch4o_h2o", init_sk=1, deletion_mode=1, **over)
+    s.p_translation, s.p_rotation, s.p_swap = 0.25, 0.25, 0.3
+    return s
+
+
+def test_swap_strict_mode_trajectory():
+    s = two_species()
+    tape = np.random.default_rng(8).random(6000)
+    o = orc.Oracle(s); o.system_energy(); ref = o.run(400, tape=tape)
+    g = ManiacGPU(s); drv = StrictDriver(s, g); drv.ComputeSystemEnergy()
+    rng = TapeRng(tape); got = drv.MonteCarloLoop(rng, 1, 400)
+    compare_records(got, ref)
+    assert rng.pos == o.tape_used
+    sw = ref[ref["kind"] == 5]
+    assert len(sw) > 40 and 0 < sw["accepted"].sum() < len(sw)
+    cnt, com, off, e = g.sync_to_host(); c2, com2, off2 = o.state()
+    assert np.array_equal(cnt, c2) and np.array_equal(drv.count, c2)
+    np.testing.assert_allclose(com, com2, atol=1e-12); np.testing.assert_allclose(off, off2, atol=1e-12)
+    assert rel_err(e, o.energy()) < TOL and rel_err(drv.energy, o.energy()) < TOL
+    np.testing.assert_allclose(g.sk(), o.sk(), atol=1e-9)
+    assert {k: drv.counter[k] for k in ("swaps", "trial_swaps")} == {k: o.counters()[k] for k in ("swaps", "trial_swaps")}
+    g.close()
+
+
+def test_swap_batched_modes():
+    """on-device proposals: recorded streams and Philox, then tracked == fresh; two emulated k-shards agree too"""
+    from maniac_mc_b200.sharded import emulate_ranks
+    s = two_species()
+    n = 300
+    tape = np.random.default_rng(9).random((2, 12 * n))
+    g = ManiacGPU(s, n_chains=2)
+    for c in range(2):
+        g.system_energy(c)
+    recs = g.run_batch(n, tape=tape, records=True)
+    for c in range(2):
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(recs[c], o.run(n, tape=tape[c]))
+        assert g.tape_used(c) == o.tape_used and g.counters[c] == o.counters()
+        assert (recs[c]["kind"] == 5).sum() > 30
+        cnt, com, off, e = g.sync_to_host(c); c2, com2, off2 = o.state()
+        assert np.array_equal(cnt, c2)
+        np.testing.assert_allclose(com, com2, atol=1e-12); np.testing.assert_allclose(off, off2, atol=1e-12)
+        np.testing.assert_allclose(g.sk(c), o.sk(), atol=1e-9)
+    r2 = g.run_batch(200, seed=77, records=True)
+    shards, step, _, _ = emulate_ranks(s, world=2, n_chains=2)
+    for c in range(2):
+        _, _, _, tracked = g.sync_to_host(c)
+        assert rel_err(tracked, g.system_energy(c)) < 1e-9
+    # sharded steps from the initial state with the same Philox seed == oracle
+    rs = np.stack([step(77, records=True) for _ in range(120)], axis=1)
+    for c in range(2):
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(rs[c], o.run(120, seed=77, chain=c, step0=0))
+    assert (rs["kind"] == 5).sum() > 20
+    for sh in shards:
+        sh.close()
+    g.close()
+
+
+def test_swap_error_behaviour():
+    s = two_species()
+    g = ManiacGPU(s); g.system_energy()
+    com = np.zeros(3); off6 = np.zeros((6, 3)); off4 = np.zeros((4, 3))
+    with pytest.raises(ManiacGpuError, match="mmc_trial_energy_swap"):
+        g.trial_energy(5, 1, 0, com, off4)                      # a swap needs both residue types
+    with pytest.raises(ManiacGpuError, match="different active"):
+        g.trial_energy_swap(1, 0, 1, com, off6)
+    with pytest.raises(ManiacGpuError, match="different active"):
+        g.trial_energy_swap(1, 0, 0, com, off6)                  # the framework is not an active type
+    with pytest.raises(ManiacGpuError, match="out of range"):
+        g.trial_energy_swap(1, 99, 2, com, off4)
+    g.close()

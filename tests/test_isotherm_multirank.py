@@ -43,12 +43,12 @@ def test_deal_chains_is_a_partition(n_points, replicas, world):
 
 def test_block_averages():
     a = iso.BlockAverages(3)
-    a.add([1, 2, 3], [10.0, 20.0, 30.0], np.arange(24).reshape(3, 8))
-    a.add([3, 2, 1], [30.0, 20.0, 10.0], np.arange(24).reshape(3, 8) + 1)
+    a.add([1, 2, 3], [10.0, 20.0, 30.0], np.arange(30).reshape(3, 10))
+    a.add([3, 2, 1], [30.0, 20.0, 10.0], np.arange(30).reshape(3, 10) + 1)
     r = a.rows()
-    assert r.shape == (3, 12)
+    assert r.shape == (3, 14)
     assert np.allclose(r[:, 0], [2, 2, 2]) and np.allclose(r[:, 1], [1, 0, 1]) and np.allclose(r[:, 2], [20, 20, 20])
-    assert np.all(r[:, 3] == 2) and np.array_equal(r[:, 4:], np.arange(24).reshape(3, 8) + 1)
+    assert np.all(r[:, 3] == 2) and np.array_equal(r[:, 4:], np.arange(30).reshape(3, 10) + 1)
 
 
 def fake_rows(ids):

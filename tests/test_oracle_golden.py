@@ -191,3 +191,44 @@ def test_reader_matches_fixture():
         if f.startswith("bad") and f.endswith(".data") and "04" not in f:
             with pytest.raises(Exception):
                 readers.read_lammps_data(os.path.join(d, f))
+
+
+def two_species(**over):
+    s = load_system("zif8_ch4o_h2o", init_sk=1, deletion_mode=1, **over)
+    s.p_translation, s.p_rotation, s.p_swap = 0.25, 0.25, 0.3
+    return s
+
+
+def test_two_species_fixture_and_reader():
+    """mc-topology/testcase-adsorption/ZIF8-CH4O-H2O: framework + methanol (6 sites) + water (4 sites), swap_proba 0.2."""
+    s = load_system("zif8_ch4o_h2o")
+    assert s.natoms.tolist() == [2208, 6, 4] and s.is_active.tolist() == [0, 1, 1] and s.count.tolist() == [1, 5, 5]
+    assert s.num_kvectors == 297 and abs(s.p_swap - 0.2 / 1.2) < 1e-12     # probabilities renormalised (input_parser.f90:98-111)
+
+
+def test_swap_move_identities():
+    """Swap has no reference trajectory (never called, monte_carlo.f90:50-75).  Checked through identities: the old
+    side of a swap is the deletion old energy of the same molecule, counts move by (-1, +1) on accept and not at all
+    on reject, tracked energies equal a fresh single-point evaluation afterwards, p_swap = 0 never draws a swap."""
+    s = two_species()
+    o = orc.Oracle(s); o.system_energy()
+    ref = o.run(500, seed=5, chain=0)
+    sw = ref[ref["kind"] == 5]
+    assert len(sw) > 50 and 0 < sw["accepted"].sum() < len(sw)
+    assert set(np.unique(sw["res"])) <= {1 + 256 * 2, 2 + 256 * 1}
+    c = o.counters()
+    assert c["trial_swaps"] == len(sw) and c["swaps"] == int(sw["accepted"].sum())
+    cnt, com, off = o.state()
+    assert cnt[1] + cnt[2] == 10 + c["creations"] - c["deletions"]        # swaps conserve the number of guests
+    s2 = s.copy(); s2.count, s2.com, s2.offsets = cnt, com, off
+    assert rel_err(o.energy(), orc.Oracle(s2).system_energy()) < 1e-10
+    # old side == deletion old side for the same molecule and the same state
+    a = orc.Oracle(s); a.system_energy(); b = orc.Oracle(s); b.system_energy()
+    tape = np.array([0.7, 0.3, 0.99])
+    ra = a.single_move(5, 1, 2, tape); rb = b.single_move(2, 1, 2, np.array([0.99]))
+    assert rel_err(ra["old_e"], rb["old_e"]) < 1e-14 and ra["accepted"] == 0
+    assert np.array_equal(a.counts(), s.count) and rel_err(a.energy(), b.energy()) < 1e-14
+    np.testing.assert_allclose(a.sk(), b.sk(), atol=1e-12)                 # rejected swap restores A(k)
+    s0 = two_species(); s0.p_swap = 0.0
+    o0 = orc.Oracle(s0); o0.system_energy()
+    assert not (o0.run(300, seed=5)["kind"] == 5).any()

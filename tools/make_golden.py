@@ -20,6 +20,8 @@ CASES = {
     "h2o_gas": ("testcase-energy/H2O-gas", "input.maniac", "topology.data", "parameters.inc", 512),
     "h2o_ads": ("testcase-adsorption/H2O", "input.maniac", "topology.data", "parameters.inc", 512),
     "zif8_h2o": ("testcase-adsorption/ZIF8-H2O", "zif8-water.maniac", "zif8-water.data", "zif8-water.inc", 512),
+    # two active species (methanol 6 sites, water 4 sites) in ZIF-8, swap_proba 0.2: the swap-move fixture
+    "zif8_ch4o_h2o": ("testcase-adsorption/ZIF8-CH4O-H2O", "input.maniac", "topology.data", "parameters.inc", 256),
 }
 
 # Known answers held by the reference's own tests (kcal/mol):
