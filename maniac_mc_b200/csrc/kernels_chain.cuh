@@ -23,24 +23,23 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
     const SweepCtx s = sweep_carve(dc, smem, NT);
     const int c = chain0 + blockIdx.x;
     sweep_load_tables(dc, s);
-    RngSrc rs = ctl->rng;
-    const unsigned long long step0 = rs.step;
-    unsigned cnt[2] = {0u, 0u};
+    pair_count_init(s);
     for (int st = 0; st < n_steps; st++) {
-        rs.step = step0 + (unsigned long long)st;
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0) {   // the RNG source is re-read here: it must not occupy registers during the sweeps
+            RngSrc rs = ctl->rng;
+            rs.step += (unsigned long long)st;
             propose_move(dc, cs, rs, c);
             if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
         }
         __syncthreads();
-        double v[6] = {0, 0, 0, 0, 0, 0};
-        sweep_trial<NT>(dc, cs, c, s, 0, 1, phases, v, cnt);
-        block_sum<6, NT>(v, s.red);
+        sweep_trial<NT>(dc, cs, c, s, 0, 1, phases);
         if (threadIdx.x == 0) {
             Trial& t = cs.trial[c];
             const int kind = t.kind;
             if (kind > 0) {
-                finalize_trial(dc, cs, c, v);
+                finalize_trial(dc, cs, c, s.mol->sums);
+                RngSrc rs = ctl->rng;
+                rs.step += (unsigned long long)st;
                 Rng rng{&rs, cs, c, t.draw};  // the accept draw follows the proposal's draws
                 const double u = rng.next();
                 commit_trial(dc, cs, c, (phases == 3 && u <= t.prob) ? 1 : 0);
@@ -54,5 +53,5 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         }
         __syncthreads();
     }
-    pair_count_flush(cs, cnt);
+    pair_count_flush(cs, s);
 }

@@ -26,6 +26,8 @@ struct MolS {
     int type[MMC_MAX_MOL_ATOMS];
     int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
     signed char term[2 * MMC_MAX_MOL_ATOMS];  // reciprocal terms: +(a+1) = atom a added, -(a+1) = atom a removed
+    double sums[6];        // block sums of this trial: parked here between the phases so they hold no registers
+    unsigned int work[2];  // executed real-space work of this CTA (distances formed, pairs inside reach)
 };
 
 struct SweepCtx {
@@ -447,31 +449,47 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
 
 // One trial of chain c, all threads of the CTA: stage, real-space sweep(s), reciprocal sweep.  `part` of `n_parts`
 // CTAs share the trial (1 of 1 in batched mode).  phases: bit 0 real space, bit 1 reciprocal.
-// v = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} (per-thread partials).
+// Result: s.mol->sums = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} of this CTA (block sums in a
+// fixed order), valid after the trailing barrier.  The real-space sums are reduced and parked in shared memory BEFORE
+// the reciprocal sweep so that its item loop does not carry them in registers (64 registers per thread at 4 CTAs/SM).
 template <int NT>
-__device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                   int phases, double (&v)[6], unsigned (&cnt)[2]) {
-    double (&pa)[4] = *reinterpret_cast<double (*)[4]>(&v[0]);
-    double (&ra)[2] = *reinterpret_cast<double (*)[2]>(&v[4]);
+__device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts, int phases) {
     const bool swap = cs.trial[c].kind == MMC_SWAP;
     stage_terms(dc, cs, c, s);
     stage_molecule(dc, cs, c, s, swap ? 1 : 0);
-    if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
-    if (swap) {   // second real-space sweep: the inserted molecule (different atom set) against everything but the removed one
-        __syncthreads();
-        stage_molecule(dc, cs, c, s, 2);
+    {
+        double pa[4] = {0, 0, 0, 0};
+        unsigned cnt[2] = {0u, 0u};
         if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
+        if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
+            __syncthreads();
+            stage_molecule(dc, cs, c, s, 2);
+            if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
+        }
+        const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt[0]), w1 = __reduce_add_sync(0xffffffffu, cnt[1]);
+        if ((threadIdx.x & 31) == 0 && (w0 | w1)) { atomicAdd(&s.mol->work[0], w0); atomicAdd(&s.mol->work[1], w1); }
+        block_sum<4, NT>(pa, s.red);
+        if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];
     }
-    if (phases & 2) recip_phase<NT>(dc, cs, c, s, part, n_parts, ra);
+    {
+        double ra[2] = {0, 0};
+        if (phases & 2) recip_phase<NT>(dc, cs, c, s, part, n_parts, ra);
+        block_sum<2, NT>(ra, s.red);
+        if (threadIdx.x == 0) { s.mol->sums[4] = ra[0]; s.mol->sums[5] = ra[1]; }
+    }
+    __syncthreads();
 }
 
 // executed-work counters of the real-space sweep (bench.py's executed-flop figure): cs.pair_count[0] += distances
-// formed, [1] += pairs inside reach (Coulomb table and/or LJ evaluated).  One atomic pair per warp per launch.
-__device__ __forceinline__ void pair_count_flush(const ChainState& cs, const unsigned (&cnt)[2]) {
-    const unsigned a = __reduce_add_sync(0xffffffffu, cnt[0]), b = __reduce_add_sync(0xffffffffu, cnt[1]);
-    if ((threadIdx.x & 31) == 0 && (a | b)) {
-        atomicAdd(cs.pair_count, (unsigned long long)a);
-        atomicAdd(cs.pair_count + 1, (unsigned long long)b);
+// formed, [1] += pairs inside reach (Coulomb table and/or LJ evaluated).  One atomic pair per CTA per launch.
+__device__ __forceinline__ void pair_count_init(const SweepCtx& s) {
+    if (threadIdx.x == 0) { s.mol->work[0] = 0u; s.mol->work[1] = 0u; }
+}
+__device__ __forceinline__ void pair_count_flush(const ChainState& cs, const SweepCtx& s) {
+    __syncthreads();
+    if (threadIdx.x == 0 && (s.mol->work[0] | s.mol->work[1])) {
+        atomicAdd(cs.pair_count, (unsigned long long)s.mol->work[0]);
+        atomicAdd(cs.pair_count + 1, (unsigned long long)s.mol->work[1]);
     }
 }
 
@@ -485,13 +503,11 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     const int part = dc.shard_rank * gridDim.x + blockIdx.x, n_parts = dc.shard_count * gridDim.x;
     const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
     sweep_load_tables(dc, s);
-    double v[6] = {0, 0, 0, 0, 0, 0};
-    unsigned cnt[2] = {0u, 0u};
-    sweep_trial<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, 3, v, cnt);
-    block_sum<6, SWEEP_THREADS>(v, s.red);
+    pair_count_init(s);
+    sweep_trial<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, 3);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
-        for (int i = 0; i < 6; i++) out[i] = v[i];
+        for (int i = 0; i < 6; i++) out[i] = s.mol->sums[i];
     }
-    pair_count_flush(cs, cnt);
+    pair_count_flush(cs, s);
 }
