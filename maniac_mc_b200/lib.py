@@ -15,7 +15,7 @@ from .system import Counters, MmcDesc, MMC_NE, MoveRecord, RECORD_DTYPE, System
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-SO_PATH = os.path.join(_PKG, "libmaniacgpu.so")
+SO_PATH = os.environ.get("MANIAC_GPU_LIB") or os.path.join(_PKG, "libmaniacgpu.so")   # env override: A/B builds side by side
 SOURCES = [os.path.join(_PKG, "csrc", f) for f in ("maniac_gpu.cu", "common.cuh", "kernels_move.cuh", "kernels_sweep.cuh", "kernels_chain.cuh",
                                                         "kernels_system.cuh")] + \
           [os.path.join(_ROOT, "include", "maniac_gpu.h")]
