@@ -26,7 +26,7 @@ def compare_records(a, b, tol=TOL):
     assert np.max(np.abs(a["prob"] - b["prob"])) < 1e-8
 
 
-@pytest.mark.parametrize("name", ["lj_gas", "h2o_gas", "h2o_ads", "zif8_h2o"])
+@pytest.mark.parametrize("name", ["lj_gas", "h2o_gas", "h2o_ads", "zif8_h2o", "mfi_co2", "slit", "zif8_ch4o_h2o"])
 def test_system_energy(name):
     """ComputeSystemEnergy: configs[0] of BASELINE.json (the reference's own CPU-runnable cases)."""
     s = load_system(name)
@@ -94,7 +94,8 @@ def test_pair_self_intra_singlemol(name):
     g.close()
 
 
-@pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("zif8_h2o", 1, 1), ("h2o_ads", 0, 0), ("h2o_ads", 1, 1)])
+@pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("zif8_h2o", 1, 1), ("h2o_ads", 0, 0), ("h2o_ads", 1, 1),
+                                                   ("mfi_co2", 1, 1), ("slit", 0, 0)])
 def test_strict_mode_trajectory(name, init_sk, deletion):
     """Strict mode: host draws the uniforms and makes the proposals (as the Fortran driver does), one
     mmc_trial_energy + mmc_trial_commit per move; same tape through the oracle."""
@@ -114,7 +115,8 @@ def test_strict_mode_trajectory(name, init_sk, deletion):
     g.close()
 
 
-@pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("h2o_ads", 1, 1), ("lj_gas", 0, 0)])
+@pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("h2o_ads", 1, 1), ("lj_gas", 0, 0), ("mfi_co2", 0, 0),
+                                                   ("slit", 1, 1)])
 def test_batched_tape_replay(name, init_sk, deletion):
     """Batched mode with on-device proposals replaying recorded streams: 3 chains, 3 different tapes."""
     s = load_system(name, init_sk=init_sk, deletion_mode=deletion)

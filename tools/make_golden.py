@@ -21,6 +21,10 @@ CASES = {
     "h2o_ads": ("testcase-adsorption/H2O", "input.maniac", "topology.data", "parameters.inc", 512),
     "zif8_h2o": ("testcase-adsorption/ZIF8-H2O", "zif8-water.maniac", "zif8-water.data", "zif8-water.inc", 512),
     # two active species (methanol 6 sites, water 4 sites) in ZIF-8, swap_proba 0.2: the swap-move fixture
+    # non-cubic orthorhombic zeolite cell (40.18 x 39.48 x 26.28 A -> kmax (11, 10, 7), K = 1697) + linear 3-site CO2
+    "mfi_co2": ("testcase-adsorption/MFI-CO2", "MFI-CO2.maniac", "MFI-CO2.data", "MFI-CO2.inc", 256),
+    # slit pore: 1912-atom wall + single-site fluid (no rotation moves, box origin at -20)
+    "slit": ("testcase-adsorption/SLIT", "input.maniac", "topology.data", "parameters.inc", 256),
     "zif8_ch4o_h2o": ("testcase-adsorption/ZIF8-CH4O-H2O", "input.maniac", "topology.data", "parameters.inc", 256),
 }
 
