@@ -216,6 +216,7 @@ def run_own(args, rank, world, local_rank):
     gpu = ManiacGPU(s, n_chains=C, device=local_rank)
     for c in range(C):
         gpu.set_chain_params(c, chain_fugacity(s, rank * C + c), s.temperature)
+        gpu.set_chain_id(c, rank * C + c)
         gpu.system_energy(c)
     stream = torch.cuda.ExternalStream(gpu.stream(), device=local_rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")

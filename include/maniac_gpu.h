@@ -141,6 +141,10 @@ int mmc_set_chain_params(mmc_t* handle, int chain, const double* fugacity, doubl
 int mmc_set_chain_state(mmc_t* handle, int chain, const int* count, const double* com, const double* offsets);
 int mmc_get_chain_state(mmc_t* handle, int chain, int* count, double* com, double* offsets);
 /* step sizes (input%translation_step / rotation_step_angle; AdjustMoveStepSizes stays on the host) */
+/* Philox stream of a chain in batched mode: draws are keyed by (seed; step, chain id, draw).  Default id = chain
+ * index.  Give every chain of a multi-GPU sweep its GLOBAL id (e.g. 1000 * point + replica) and its
+ * trajectory no longer depends on which GPU or which slot it was dealt to. */
+int mmc_set_chain_id(mmc_t* handle, int chain, uint32_t id);
 int mmc_set_step_sizes(mmc_t* handle, int chain, double translation_step, double rotation_step);
 
 /* ---- single-point energy ----------------------------------------------------------------- */

@@ -114,6 +114,7 @@ struct ChainState {
     Trial* trial;      // [C]
     double* part;      // [C][sweep_parts][6]  (lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2)
     long long* tape_pos;  // [C]
+    unsigned int* chain_id;  // [C] Philox stream of each chain (default: the chain index); global ids make a sweep independent of how chains are dealt to GPUs
     unsigned long long* pair_count;  // [2] executed real-space work since mmc_init: distances formed, pairs inside reach
     int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)
 };

@@ -16,7 +16,7 @@ struct Rng {
     const RngSrc* src; ChainState cs; int c; int draw;
     __device__ double next() {
         if (src->tape) { long long p = cs.tape_pos[c]++; return src->tape[(size_t)c * src->tape_stride + p]; }
-        return philox_uniform(src->seed, (uint32_t)c, src->step, (uint32_t)draw++);
+        return philox_uniform(src->seed, cs.chain_id[c], src->step, (uint32_t)draw++);
     }
 };
 

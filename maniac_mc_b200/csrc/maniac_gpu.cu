@@ -65,7 +65,10 @@ template <typename T>
 static cudaError_t dalloc(mmc_handle* h, T** p, size_t n) {
     void* q = nullptr;
     cudaError_t e = cudaMalloc(&q, (n ? n : 1) * sizeof(T));
-    if (e == cudaSuccess) { h->allocs.push_back(q); e = cudaMemsetAsync(q, 0, (n ? n : 1) * sizeof(T), h->stream); }
+    // zeroed on the NULL stream and waited for: the set-up copies that follow use both the NULL stream (cudaMemcpy) and the
+    // library's own NON-BLOCKING stream, which the NULL stream does not order against
+    if (e == cudaSuccess) { h->allocs.push_back(q); e = cudaMemset(q, 0, (n ? n : 1) * sizeof(T)); }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);   // set-up only: the zero fill is complete before any stream touches q
     *p = (T*)q;
     return e;
 }
@@ -479,11 +482,16 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
     CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
     CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
-    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 2));
+    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.chain_id, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 2));
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
     CKB(cudaMallocHost((void**)&h->h_tape_pos, C * sizeof(long long)));
     memset(h->h_tape_pos, 0, C * sizeof(long long));
+    {
+        std::vector<unsigned int> ids(C);
+        for (size_t c = 0; c < C; c++) ids[c] = (unsigned int)c;
+        CKB(cudaMemcpy(cs.chain_id, ids.data(), C * sizeof(unsigned int), cudaMemcpyHostToDevice));
+    }
     {
         std::vector<double> fug(C * MMC_MAX_RES, 0.0), tmp(C, d->temperature), ts(C, d->translation_step), rs(C, d->rotation_step);
         for (size_t c = 0; c < C; c++) for (int r = 0; r < d->nres; r++) fug[c * MMC_MAX_RES + r] = d->fugacity ? d->fugacity[r] : 0.0;
@@ -515,7 +523,7 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     dc.max_nat = max_nat;
     if (dc.kmax[0] > 1023 || dc.kmax[1] > 511 || dc.kmax[2] > 511) BAIL("kmax too large for the packed k-vector list");
     if (build_sweep_layout(h, d)) { std::string keep = g_err; mmc_destroy(h); g_err = keep; return 1; }
-    CKB(cudaStreamSynchronize(h->stream));
+    CKB(cudaDeviceSynchronize());   // set-up used both the NULL stream (copies) and the library stream (kernels)
     CKB(cudaGetLastError());
     *out = h;
     return 0;
@@ -544,18 +552,26 @@ extern "C" int mmc_set_chain_params(mmc_t* h, int c, const double* fugacity, dou
     if (!(temperature > 0.0)) return fail("temperature must be positive");
     double f[MMC_MAX_RES] = {0};
     for (int r = 0; r < h->dc.nres; r++) f[r] = fugacity ? fugacity[r] : 0.0;
+    // on the library's (non-blocking) stream, then waited for: ordered against the kernels before and after
+    if (fugacity) CK(cudaMemcpyAsync(h->cs.fug + (size_t)c * MMC_MAX_RES, f, sizeof f, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->cs.temp + c, &temperature, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    if (fugacity) CK(cudaMemcpy(h->cs.fug + (size_t)c * MMC_MAX_RES, f, sizeof f, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(h->cs.temp + c, &temperature, sizeof(double), cudaMemcpyHostToDevice));
     return 0;
 }
 
+extern "C" int mmc_set_chain_id(mmc_t* h, int c, uint32_t id) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(h->cs.chain_id + c, &id, sizeof id, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return 0;
+}
 extern "C" int mmc_set_step_sizes(mmc_t* h, int c, double tstep, double rstep) {
     CHECK_CHAIN(h, c);
     CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(h->cs.tstep + c, &tstep, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->cs.rstep + c, &rstep, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(h->cs.tstep + c, &tstep, sizeof(double), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(h->cs.rstep + c, &rstep, sizeof(double), cudaMemcpyHostToDevice));
     return 0;
 }
 
@@ -1050,7 +1066,7 @@ static int run_elementwise(mmc_handle* h, int which, const double* in, int n, do
     CK(cudaSetDevice(h->device));
     double *di = nullptr, *dout = nullptr;
     CK(cudaMalloc((void**)&di, n * sizeof(double))); CK(cudaMalloc((void**)&dout, n * sizeof(double)));
-    CK(cudaMemcpy(di, in, n * sizeof(double), cudaMemcpyHostToDevice));
+    CK(cudaMemcpyAsync(di, in, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     if (which < 0) k_erfc_test<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, di, n, dout);
     else k_table_lookup<<<(n + 255) / 256, 256, 0, h->stream>>>(h->dc, which, di, n, dout);
     h->launches++;

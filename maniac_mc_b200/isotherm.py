@@ -135,6 +135,7 @@ class IsothermSweep:
             f = system.fugacity.copy()
             f[self.res] = builders.fugacity_from_atm(self.f_atm[cid.point], system.temperature)
             self.gpu.set_chain_params(c, f, system.temperature)
+            self.gpu.set_chain_id(c, cid.seed)     # global Philox stream: the sweep does not depend on the dealing
             self.gpu.system_energy(c)
         self.avg = BlockAverages(len(self.ids))
         self.step = 0

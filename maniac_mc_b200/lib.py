@@ -42,7 +42,7 @@ def build(force=False, verbose=False):
 # every symbol declared in include/maniac_gpu.h
 ABI_SYMBOLS = [
     "mmc_ewald_setup", "mmc_init", "mmc_destroy", "mmc_last_error", "mmc_num_kvectors", "mmc_get_kvectors",
-    "mmc_set_chain_params", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
+    "mmc_set_chain_params", "mmc_set_chain_id", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
     "mmc_system_energy", "mmc_trial_energy", "mmc_trial_energy_swap", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk",
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
@@ -71,6 +71,7 @@ def load():
     L.mmc_get_kvectors.argtypes = [vp, ip, ip, ip, dp, dp]
     L.mmc_set_chain_params.argtypes = [vp, C.c_int, dp, C.c_double]
     L.mmc_set_chain_state.argtypes = [vp, C.c_int, ip, dp, dp]
+    L.mmc_set_chain_id.argtypes = [vp, C.c_int, C.c_uint32]
     L.mmc_get_chain_state.argtypes = [vp, C.c_int, ip, dp, dp]
     L.mmc_set_step_sizes.argtypes = [vp, C.c_int, C.c_double, C.c_double]
     L.mmc_system_energy.argtypes = [vp, C.c_int, dp]
@@ -172,6 +173,9 @@ class ManiacGPU:
     def set_chain_params(self, chain, fugacity, temperature):
         f = np.ascontiguousarray(fugacity, dtype=np.float64)
         _ck(load().mmc_set_chain_params(self.h, chain, _dp(f), float(temperature)))
+
+    def set_chain_id(self, chain, stream_id):
+        _ck(load().mmc_set_chain_id(self.h, chain, int(stream_id)))
 
     def set_step_sizes(self, chain, tstep, rstep):
         _ck(load().mmc_set_step_sizes(self.h, chain, float(tstep), float(rstep)))
