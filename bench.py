@@ -44,7 +44,7 @@ NCU_TRAFFIC_SOURCE = "profiles/r1n_ncu_summary.txt (23.62 GB per launch of 592 c
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="own", choices=["own", "reference"])
     p.add_argument("--chains", type=int, default=592, help="independent chains per GPU (4 resident CTAs x 148 SMs)")
