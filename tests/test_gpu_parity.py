@@ -536,3 +536,33 @@ def test_sweep_is_independent_of_the_dealing():
     cid = iso.deal_chains(3, 2)[4]
     o = orc.Oracle(s); o.system_energy()
     compare_records(whole[4], o.run(n, seed=seed, chain=cid.seed, step0=0))
+
+
+def test_ideal_gas_limit_is_poisson():
+    """Physics check of the whole batched GCMC loop (selection, Philox stream, insertion/deletion acceptance with the
+    reference's N-after-update convention, monte_carlo_utils.f90:199-214): with every interaction switched off the
+    stationary distribution of N is Poisson with mean = variance = phi V."""
+    s = builders.synthetic_water_box(n_mol=8, box=30.0, cutoff=14.0, tol=1e-5, seed=2, capacity=256, fugacity_atm=20.0,
+                                     p_translation=0.1, p_rotation=0.1)
+    s.charges[:] = 0.0; s.epsilon[:] = 0.0
+    s.init_sk, s.deletion_mode = 1, 1
+    expect = float(s.fugacity[0]) * s.volume
+    assert 12.0 < expect < 15.0
+    C = 64
+    g = ManiacGPU(s, n_chains=C)
+    for c in range(C):
+        g.set_chain_id(c, 1000 + c); g.system_energy(c)
+    g.run_batch(3000, seed=17)                                   # equilibration
+    cnt = np.zeros((C, s.nres), dtype=np.int32)
+    samples = []
+    for b in range(120):
+        g.run_batch_async(100, seed=17)
+        g.download_chains(cnt, None, None, None, None)
+        samples.append(cnt[:, 0].copy())
+    n = np.array(samples, dtype=np.float64)                      # [blocks, chains]
+    mean, var = n.mean(), n.var()
+    assert abs(mean - expect) < 0.03 * expect, (mean, expect)    # ~7700 weakly correlated samples: s.e. ~ 0.05
+    assert abs(var - expect) < 0.12 * expect, (var, expect)
+    e = np.zeros((C, 6)); g.download_chains(None, None, None, e, None)
+    assert np.all(np.abs(e[:, :3]) < 1e-9)                       # no interaction energy anywhere
+    g.close()
