@@ -1,13 +1,13 @@
 // common.cuh -- device-side data layout and helpers of libmaniacgpu (sm_100a).
 //
 // HBM layout (see DESIGN.md "Data layout"):
-//   shared, read-only : framework SoA fx/fy/fz/fq (double) + ftype/fmol (int), LJ table
-//                       lj[ti*ntypes+tj] = {sigma, 4*epsilon}, k-vector list kvec (int4: kx,ky,kz,0),
-//                       fw[k] = form_factor(k) * W(k)
-//   per chain, mutable: guest SoA gx/gy/gz (absolute positions, slot-major), gcom/goff (COM + site
-//                       offsets, the reference's mol_com/site_offset), count, A(k) double-buffered
-//                       (double2, 2*K per chain) with a parity bit, tracked energies, counters,
-//                       one Trial descriptor.
+//   shared, read-only : framework SoA fx/fy/fz/fq (double) + ftype/fmol (int) for the single-point kernels and, for the
+//                       per-move sweeps, the same atoms in Morton order in tiles of 32 (sx/sy/sz/sq/stype, tbox);
+//                       LJ table lj[ti*ntypes+tj] = {sigma, 4*epsilon}; k-vector list kvec (int4) and the reciprocal work
+//                       items kitem (one per (kx, ky) row and kz >= 0); fw[k] = form_factor(k) * W(k)
+//   per chain, mutable: guest SoA gx/gy/gz (absolute positions, slot-major), gcom/goff (COM + site offsets, the
+//                       reference's mol_com/site_offset), count, A(k) double-buffered (double2, 2*K per chain) with a
+//                       parity bit, tracked energies, counters, one Trial descriptor, a Philox stream id.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -184,8 +184,6 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
     __syncthreads();
 }
 
-// erfc used by the real-space sweeps.  Accuracy contract (tests/test_gpu_parity.py::test_erfc):
-// |device - glibc| <= 2e-15 absolute and <= 1e-13 relative on [0, 6].
 // ---- real-space Coulomb kernel g(s) = erfc(alpha sqrt(s)) / sqrt(s), s = r^2 ----------------------------
 // Piecewise degree-9 polynomials on segments that follow the binary representation of s: 8 segments per
 // octave (exponent + top 3 mantissa bits select the segment, the remaining mantissa bits give the local

@@ -1,5 +1,6 @@
-// kernels_move.cuh -- the per-move hot path: proposal, real-space pair sweep, reciprocal
-// Delta-S(k) sweep, and the accept/commit tail.  One launch serves all chains (grid.y = chain).
+// kernels_move.cuh -- the single-thread parts of one trial move: selection + proposal geometry (propose_move),
+// the Trial descriptor (build_trial), energy assembly and acceptance probability (finalize_trial), commit
+// (commit_trial), plus the small strict-mode / k-sharded kernels around them.  The sweeps are in kernels_sweep.cuh.
 #pragma once
 #include "common.cuh"
 
