@@ -28,6 +28,7 @@ module maniac_gpu_iface
         real(c_double) :: coulomb_xcut
         integer(c_int) :: shard_rank, shard_count
         real(c_double) :: p_swap
+        type(c_ptr) :: reservoir_count, reservoir_offsets
     end type mmc_desc
 
     interface

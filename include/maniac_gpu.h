@@ -93,6 +93,13 @@ typedef struct mmc_desc {
     int shard_rank;        /* k-sharded mode (ONE large system over several GPUs, one handle per GPU): this handle */
     int shard_count;       /* sweeps part shard_rank of shard_count of the tiles and of the k rows; 0 or 1 = off    */
     double p_swap;         /* proba%swap (input_parser.f90:446-452); 0 = the reference's de-facto behaviour */
+    /* Reservoir box (has_reservoir, data_parser.f90:60-62): a pool of molecule geometries per active type.  With a
+     * reservoir an insertion copies the site offsets of a randomly drawn pool molecule instead of rotating the slot-1
+     * template (create_molecule.f90:185-193), an accepted insertion removes that molecule from the pool (:118-130) and
+     * an accepted deletion appends one (delete_molecule.f90:148-166).  Batched mode keeps one pool per chain on the
+     * device; in strict mode the host owns the pool and these stay NULL.  NULL = no reservoir. */
+    const int* reservoir_count;      /* [nres] reservoir%num_residues */
+    const double* reservoir_offsets; /* [3 * sum(reservoir_count*natoms)] reservoir%site_offset, packed like offsets */
 } mmc_desc;
 
 /* One record per trial move of a batched run (optional output). */
@@ -200,6 +207,9 @@ int mmc_upload_chains(mmc_t* handle, const int* count, const double* com, const 
 int mmc_download_chains(mmc_t* handle, int* count, double* com, double* offsets, double* energies,
                         mmc_counters* counters);
 /* tracked A(k) as (re,im) pairs, 2*K doubles (ewald%recip_amplitude) */
+/* reservoir pool of one chain (batched mode): count[nres], offsets packed like mmc_desc.reservoir_offsets
+ * (capacity reservoir_count + capacity molecules per type) */
+int mmc_get_reservoir(mmc_t* handle, int chain, int* count, double* offsets);
 int mmc_get_sk(mmc_t* handle, int chain, double* sk);
 
 /* ---- batched mode: the inner `do current_step` loop of MonteCarloLoop on the device ------- */

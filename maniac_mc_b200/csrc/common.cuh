@@ -74,6 +74,8 @@ struct DevConst {
     // far below one ulp of the sums); reach2 = inf when culling is off (every pair evaluated, Q3 literally)
     double rc2, alpha2, reach, reach2;
     int max_nat, sweep_parts;      // largest active molecule; CTAs per chain of the strict-mode sweep
+    // reservoir pools (one per chain and active type): r_atom_base = first pool atom of residue r, r_cap = pool slots
+    int has_reservoir, r_atoms, r_atom_base[MMC_MAX_RES], r_cap[MMC_MAX_RES];
     int shard_rank, shard_count;   // k/tile sharding of ONE system over several GPUs (1 handle per GPU); 0, 1 = off
 };
 
@@ -85,6 +87,7 @@ struct Trial {
     int r_plus, r_minus;   // reciprocal update: A' = A + sum q phi(plus) - sum q phi(minus)
     int excl;              // 1: exclude slot (res, mol) from the sweep
     int accepted, error, draw;
+    int rsv;               // creation with a reservoir: pool slot the geometry was copied from
     double prob;
     double q[MMC_MAX_MOL_ATOMS];          // OLD atom set (the selected molecule)
     int type[MMC_MAX_MOL_ATOMS];
@@ -114,6 +117,8 @@ struct ChainState {
     Trial* trial;      // [C]
     double* part;      // [C][sweep_parts][6]  (lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2)
     long long* tape_pos;  // [C]
+    int* rcount;          // [C][MMC_MAX_RES] molecules in the reservoir pool (reservoir%num_residues)
+    double* roff;         // [C][r_atoms][3] their site offsets (reservoir%site_offset)
     unsigned int* chain_id;  // [C] Philox stream of each chain (default: the chain index); global ids make a sweep independent of how chains are dealt to GPUs
     unsigned long long* pair_count;  // [2] executed real-space work since mmc_init: distances formed, pairs inside reach
     int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)

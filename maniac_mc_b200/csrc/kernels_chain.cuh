@@ -42,7 +42,10 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
                 rs.step += (unsigned long long)st;
                 Rng rng{&rs, cs, c, t.draw};  // the accept draw follows the proposal's draws
                 const double u = rng.next();
-                commit_trial(dc, cs, c, (phases == 3 && u <= t.prob) ? 1 : 0);
+                const int acc = (phases == 3 && u <= t.prob) ? 1 : 0;
+                // AcceptDeletionMove draws three more uniforms to place the molecule in the reservoir box (delete_molecule.f90:150-151)
+                if (acc && kind == MMC_DELETION && dc.has_reservoir) { rng.next(); rng.next(); rng.next(); }
+                commit_trial(dc, cs, c, acc);
             }
             if (ctl->recs) {
                 mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + st];

@@ -43,7 +43,7 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
     const int nat = dc.natoms[r];
     if (kind != MMC_SWAP) r2 = r;
     const int nat2 = dc.natoms[r2];
-    t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.res2 = r2; t.nat2 = nat2; t.accepted = 0; t.prob = 0.0;
+    t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.res2 = r2; t.nat2 = nat2; t.accepted = 0; t.prob = 0.0; t.rsv = -1;
     for (int a = 0; a < nat; a++) { t.q[a] = dc.q[r][a]; t.type[a] = dc.type[r][a]; }
     for (int a = 0; a < nat2; a++) { t.q2[a] = dc.q[r2][a]; t.type2[a] = dc.type[r2][a]; }
     const int cnt = cs.count[c * MMC_MAX_RES + r];
@@ -200,14 +200,22 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             else {
                 ctr.trial_creations++;
                 for (int d = 0; d < 3; d++) com_new[d] = dc.lo[d] + dc.L[d] * rng.next();
-                double tmpl[MMC_MAX_MOL_ATOMS][3];  // geometry of slot 1 of this type (Q9)
-                for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) tmpl[a][d] = cs.goff[g_atom(dc, c, r, 0, a) * 3 + d];
-                if (nat != 1) {
-                    const double theta = rng.next() * MMC_TWOPI;
-                    const int axis = (int)(rng.next() * 3.0) + 1;
-                    rotate_offsets(axis, theta, nat, tmpl, off_new);
-                } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
+                int rsv = -1;
+                if (dc.has_reservoir) {  // InsertAndOrientMolecule create_molecule.f90:185-193: a random reservoir molecule's geometry, no rotation
+                    rsv = (int)(rng.next() * cs.rcount[c * MMC_MAX_RES + r]);
+                    const double* ro = cs.roff + ((size_t)c * dc.r_atoms + dc.r_atom_base[r] + (size_t)rsv * nat) * 3;
+                    for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_new[a][d] = ro[a * 3 + d];
+                } else {
+                    double tmpl[MMC_MAX_MOL_ATOMS][3];  // geometry of slot 1 of this type (Q9)
+                    for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) tmpl[a][d] = cs.goff[g_atom(dc, c, r, 0, a) * 3 + d];
+                    if (nat != 1) {
+                        const double theta = rng.next() * MMC_TWOPI;
+                        const int axis = (int)(rng.next() * 3.0) + 1;
+                        rotate_offsets(axis, theta, nat, tmpl, off_new);
+                    } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
+                }
                 build_trial(dc, cs, c, MMC_CREATION, r, m, com_new, off_new);
+                t.rsv = rsv;
             }
         } else if (cnt != 0) {  // DeleteMolecule delete_molecule.f90:41-199
             ctr.trial_deletions++;
@@ -307,11 +315,28 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
         E[MMC_E_SELF] = E[MMC_E_SELF] + n[3] - o[3];
         E[MMC_E_INTRA] = E[MMC_E_INTRA] + n[4] - o[4];
         E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
-        if (t.kind == MMC_CREATION) { ctr.creations++; cnt = cnt + 1; }  // geometry already in the slot
-        else {
+        if (t.kind == MMC_CREATION) {
+            ctr.creations++; cnt = cnt + 1;  // geometry already in the slot
+            int& nr = cs.rcount[c * MMC_MAX_RES + r];
+            if (dc.has_reservoir && nr > 0 && t.rsv >= 0) {  // (strict mode: the host owns the pool, rsv < 0)  AcceptCreationMove create_molecule.f90:118-130: pool slot <- last pool slot
+                double* ro = cs.roff + ((size_t)c * dc.r_atoms + dc.r_atom_base[r]) * 3;
+                for (int i = 0; i < nat * 3; i++) ro[(size_t)t.rsv * nat * 3 + i] = ro[(size_t)(nr - 1) * nat * 3 + i];
+                nr = nr - 1;
+            }
+        } else {
             if (t.kind == MMC_SWAP) { ctr.swaps++; cs.count[c * MMC_MAX_RES + t.res2] += 1; }  // inserted geometry already in its slot
             else ctr.deletions++;
             const int last = cnt - 1;  // RemoveMolecule delete_molecule.f90:99-118: slot[m] <- slot[last]
+            if (t.kind == MMC_DELETION && dc.has_reservoir) {
+                // AcceptDeletionMove delete_molecule.f90:148-166 appends the offsets of slot last_molecule_index (not of the
+                // deleted slot) to the pool; its three position draws are consumed by the caller
+                int& nr = cs.rcount[c * MMC_MAX_RES + r];
+                if (nr < dc.r_cap[r]) {
+                    double* ro = cs.roff + ((size_t)c * dc.r_atoms + dc.r_atom_base[r] + (size_t)nr * nat) * 3;
+                    for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) ro[a * 3 + d] = cs.goff[g_atom(dc, c, r, last, a) * 3 + d];
+                    nr = nr + 1;
+                }
+            }
             if (m != last) {
                 double* com = g_com(dc, cs, c, r, m); const double* cl = g_com(dc, cs, c, r, last);
                 for (int d = 0; d < 3; d++) com[d] = cl[d];
@@ -390,7 +415,9 @@ __global__ void k_finish(DevConst dc, ChainState cs, const BatchCtl* ctl, int c0
             RngSrc rs = ctl->rng;
             Rng rng{&rs, cs, c, t.draw};
             const double u = rng.next();
-            commit_trial(dc, cs, c, u <= t.prob ? 1 : 0);
+            const int acc = u <= t.prob ? 1 : 0;
+            if (acc && kind == MMC_DELETION && dc.has_reservoir) { rng.next(); rng.next(); rng.next(); }  // reservoir placement draws
+            commit_trial(dc, cs, c, acc);
         }
     }
     if (out) {

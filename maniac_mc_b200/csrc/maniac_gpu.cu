@@ -482,6 +482,30 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
     CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
     CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
+    {   // reservoir pools (mmc_desc.reservoir_*): one per chain, every chain starts from the same pool
+        dc.has_reservoir = (d->reservoir_count && d->reservoir_offsets) ? 1 : 0;
+        int ra = 0;
+        for (int r = 0; r < dc.nres; r++) {
+            dc.r_atom_base[r] = ra; dc.r_cap[r] = 0;
+            if (dc.has_reservoir && dc.is_active[r]) { dc.r_cap[r] = d->reservoir_count[r] + dc.cap[r] + 1; ra += dc.r_cap[r] * dc.natoms[r]; }
+        }
+        dc.r_atoms = ra;
+        CKB(dalloc(h, &cs.rcount, C * MMC_MAX_RES)); CKB(dalloc(h, &cs.roff, C * (size_t)std::max(ra, 1) * 3));
+        if (dc.has_reservoir) {
+            std::vector<int> rc(C * MMC_MAX_RES, 0); std::vector<double> ro(C * (size_t)std::max(ra, 1) * 3, 0.0);
+            size_t src = 0;
+            for (int r = 0; r < dc.nres; r++) {
+                const size_t n = (size_t)d->reservoir_count[r] * dc.natoms[r] * 3;
+                if (dc.is_active[r]) for (size_t c = 0; c < C; c++) {
+                    rc[c * MMC_MAX_RES + r] = d->reservoir_count[r];
+                    memcpy(ro.data() + (c * (size_t)ra + dc.r_atom_base[r]) * 3, d->reservoir_offsets + src, n * sizeof(double));
+                }
+                src += n;
+            }
+            CKB(cudaMemcpy(cs.rcount, rc.data(), rc.size() * sizeof(int), cudaMemcpyHostToDevice));
+            CKB(cudaMemcpy(cs.roff, ro.data(), ro.size() * sizeof(double), cudaMemcpyHostToDevice));
+        }
+    }
     CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.chain_id, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 2));
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
@@ -669,6 +693,22 @@ extern "C" int mmc_download_chains(mmc_t* h, int* count, double* com, double* of
     return 0;
 }
 
+extern "C" int mmc_get_reservoir(mmc_t* h, int c, int* count, double* offsets) {
+    CHECK_CHAIN(h, c);
+    const DevConst& dc = h->dc;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<int> rc(MMC_MAX_RES, 0);
+    CK(cudaMemcpy(rc.data(), h->cs.rcount + (size_t)c * MMC_MAX_RES, MMC_MAX_RES * sizeof(int), cudaMemcpyDeviceToHost));
+    size_t dst = 0;
+    for (int r = 0; r < dc.nres; r++) {
+        if (count) count[r] = rc[r];
+        const size_t n = (size_t)rc[r] * dc.natoms[r] * 3;
+        if (offsets && n) CK(cudaMemcpy(offsets + dst, h->cs.roff + ((size_t)c * dc.r_atoms + dc.r_atom_base[r]) * 3, n * sizeof(double), cudaMemcpyDeviceToHost));
+        dst += n;
+    }
+    return 0;
+}
 extern "C" int mmc_get_sk(mmc_t* h, int c, double* sk) {
     CHECK_CHAIN(h, c);
     if (!sk) return fail("mmc_get_sk: null output");

@@ -71,6 +71,14 @@ class StrictDriver:
         self.counter = dict(translations=0, rotations=0, creations=0, deletions=0, trial_translations=0,
                             trial_rotations=0, trial_creations=0, trial_deletions=0, swaps=0, trial_swaps=0)
         self.energy = np.zeros(6)
+        # reservoir box (has_reservoir): in strict mode the host owns the pool, as the Fortran driver does
+        self.has_reservoir = s.reservoir_count is not None
+        self.rsv = []
+        if self.has_reservoir:
+            ro = np.asarray(s.reservoir_offsets, dtype=np.float64).reshape(-1, 3); a0 = 0
+            for r in range(s.nres):
+                n, na = int(s.reservoir_count[r]), int(s.natoms[r])
+                self.rsv.append([ro[a0 + i * na:a0 + (i + 1) * na].copy() for i in range(n)]); a0 += n * na
 
     # ComputeSystemEnergy energy_utils.f90:18
     def ComputeSystemEnergy(self):
@@ -168,13 +176,19 @@ class StrictDriver:
         self.counter["trial_creations"] += 1
         self.count[r] += 1
         com = np.array([self.sys.box_lo[d] + self.sys.box_len[d] * rng() for d in range(3)])
-        off = self.ApplyRandomRotation(rng, self.off[r][0], full=True)  # geometry of slot 1 (Q9)
+        rsv = -1
+        if self.has_reservoir:   # InsertAndOrientMolecule create_molecule.f90:185-193
+            rsv = int(rng() * len(self.rsv[r])); off = self.rsv[r][rsv].copy()
+        else:
+            off = self.ApplyRandomRotation(rng, self.off[r][0], full=True)  # geometry of slot 1 (Q9)
         self.com[r][m] = com; self.off[r][m] = off  # written at proposal time, kept on reject
         old, new = self.gpu.trial_energy(MMC_CREATION, r, m, com, off, chain=self.chain)
         p = self.mc_acceptance_probability(old, new, r, MMC_CREATION)
         acc = rng() <= p
         if acc:
             self._accept_insdel(old, new); self.counter["creations"] += 1
+            if self.has_reservoir and self.rsv[r]:   # AcceptCreationMove :118-130: pool slot <- last pool slot
+                self.rsv[r][rsv] = self.rsv[r][-1]; self.rsv[r].pop()
         else:
             self.count[r] -= 1
         self.gpu.trial_commit(acc, chain=self.chain)
@@ -191,6 +205,9 @@ class StrictDriver:
         acc = rng() <= p
         if acc:
             self._accept_insdel(old, new); self.counter["deletions"] += 1
+            if self.has_reservoir:   # AcceptDeletionMove delete_molecule.f90:148-166 (appends slot `last`, three placement draws)
+                rng(); rng(); rng()
+                self.rsv[r].append(self.off[r][last].copy())
             self.com[r][m] = self.com[r][last]; self.off[r][m] = self.off[r][last]  # RemoveMolecule
         else:
             self.count[r] += 1

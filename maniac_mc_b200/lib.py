@@ -43,7 +43,7 @@ def build(force=False, verbose=False):
 ABI_SYMBOLS = [
     "mmc_ewald_setup", "mmc_init", "mmc_destroy", "mmc_last_error", "mmc_num_kvectors", "mmc_get_kvectors",
     "mmc_set_chain_params", "mmc_set_chain_id", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
-    "mmc_system_energy", "mmc_trial_energy", "mmc_trial_energy_swap", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk",
+    "mmc_system_energy", "mmc_trial_energy", "mmc_trial_energy_swap", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk", "mmc_get_reservoir",
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
@@ -80,6 +80,7 @@ def load():
     L.mmc_trial_energy_swap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_sync_to_host.argtypes = [vp, C.c_int, ip, dp, dp, dp]
     L.mmc_get_sk.argtypes = [vp, C.c_int, dp]
+    L.mmc_get_reservoir.argtypes = [vp, C.c_int, ip, dp]
     L.mmc_run_batch.argtypes = [vp, C.c_int64, C.c_uint64, dp, C.c_int64, vp, vp]
     L.mmc_run_batch_async.argtypes = [vp, C.c_int64, C.c_uint64]
     L.mmc_synchronize.argtypes = [vp]
@@ -217,6 +218,15 @@ class ManiacGPU:
         cnt, com, off = self._trim(cnt, com, off)
         self._fill_inactive(cnt, com, off)
         return cnt, com, off, e
+
+    def reservoir(self, chain=0):
+        """(count[nres], offsets [n, 3]) of the chain's reservoir pool"""
+        cnt = np.zeros(self.nres, dtype=np.int32)
+        _ck(load().mmc_get_reservoir(self.h, chain, _ip(cnt), None))
+        n = int((cnt * self.sys.natoms).sum())
+        off = np.zeros((max(n, 1), 3))
+        _ck(load().mmc_get_reservoir(self.h, chain, _ip(cnt), _dp(off)))
+        return cnt, off[:n]
 
     def sk(self, chain=0):
         a = np.zeros(2 * self.nk)

@@ -38,6 +38,7 @@ class MmcDesc(C.Structure):
         ("shard_rank", C.c_int),
         ("shard_count", C.c_int),
         ("p_swap", C.c_double),
+        ("reservoir_count", C.POINTER(C.c_int)), ("reservoir_offsets", C.POINTER(C.c_double)),
     ]
 
 
@@ -109,6 +110,8 @@ class System:
     use_table: int = 0
     coulomb_xcut: float = 0.0   # 0 = library default (6.0), negative = evaluate every pair
     names: list = field(default_factory=list)
+    reservoir_count: np.ndarray | None = None     # [nres] molecules in the reservoir box per type (None = no reservoir)
+    reservoir_offsets: np.ndarray | None = None   # [sum(count*natoms), 3] their site offsets, packed like `offsets`
     ewald_tolerance: float = 1e-5
 
     # ---- helpers ----
@@ -175,6 +178,10 @@ class System:
         d.init_sk, d.deletion_mode, d.use_table, d.device = self.init_sk, self.deletion_mode, self.use_table, device
         d.coulomb_xcut = float(self.coulomb_xcut)
         d.shard_rank, d.shard_count = int(shard_rank), int(shard_count)
+        if self.reservoir_count is not None:
+            d.reservoir_count = arr("reservoir_count", self.reservoir_count, np.int32)
+            ro = np.asarray(self.reservoir_offsets, dtype=np.float64)
+            d.reservoir_offsets = arr("reservoir_offsets", ro.reshape(-1) if ro.size else np.zeros(3), np.float64)
         d._keep = keep
         return d
 

@@ -67,6 +67,7 @@ typedef struct orc {
     double energy[MMC_NE];               /* type(energy_type) energy */
     double com_old[3]; double* off_old;  /* res%mol_com_old, res%site_offset_old */
     int init_sk, deletion_mode, use_table, recalibrate;
+    int has_reservoir; int *rsv_count, *rsv_cap; double** rsv_off;   /* reservoir%num_residues, reservoir%site_offset */
     orc_table erfc_r, r6, r12;
     mmc_counters cnt;
     orc_rng rng;
@@ -252,6 +253,19 @@ orc_t* orc_create(const mmc_desc* d) {
     o->py_old = calloc((size_t)o->max_atoms * (2 * o->kmax[1] + 1), sizeof(cplx));
     o->pz_old = calloc((size_t)o->max_atoms * (2 * o->kmax[2] + 1), sizeof(cplx));
     o->off_old = calloc((size_t)o->max_atoms * 3, sizeof(double));
+    /* reservoir box: only its site offsets matter to the path (data_parser.f90:60-62, create_molecule.f90:185-193) */
+    o->has_reservoir = d->reservoir_count != NULL && d->reservoir_offsets != NULL;
+    o->rsv_count = calloc(nr, sizeof(int)); o->rsv_cap = calloc(nr, sizeof(int)); o->rsv_off = calloc(nr, sizeof(double*));
+    if (o->has_reservoir) {
+        size_t ro = 0;
+        for (size_t r = 0; r < nr; r++) {
+            size_t na = o->natoms[r];
+            o->rsv_count[r] = d->reservoir_count[r]; o->rsv_cap[r] = d->reservoir_count[r] + o->cap[r] + 1;
+            o->rsv_off[r] = calloc((size_t)o->rsv_cap[r] * na * 3, sizeof(double));
+            memcpy(o->rsv_off[r], d->reservoir_offsets + 3 * ro, sizeof(double) * 3 * na * o->rsv_count[r]);
+            ro += (size_t)o->rsv_count[r] * na;
+        }
+    }
     precompute_kvectors(o);
     reciprocal_weights(o);
     o->A = calloc(o->nk, sizeof(cplx)); o->A_old = calloc(o->nk, sizeof(cplx)); /* Q1: de-facto zero */
@@ -270,6 +284,8 @@ void orc_destroy(orc_t* o) {
     free(o->charges); free(o->types); free(o->sigma); free(o->epsilon);
     free(o->kx); free(o->ky); free(o->kz); free(o->ksq_mag); free(o->form); free(o->W);
     free(o->A); free(o->A_old);
+    for (int r = 0; r < o->nres; r++) free(o->rsv_off[r]);
+    free(o->rsv_count); free(o->rsv_cap); free(o->rsv_off);
     free(o->erfc_r.x); free(o->erfc_r.f); free(o->r6.x); free(o->r6.f); free(o->r12.x); free(o->r12.f);
     free(o);
 }
@@ -298,6 +314,15 @@ void orc_get_state(orc_t* o, int* count, double* com, double* offsets) {
         if (com) memcpy(com + 3 * mo, o->com[r], sizeof(double) * 3 * o->count[r]);
         if (offsets) memcpy(offsets + 3 * ao, o->off[r], sizeof(double) * 3 * o->count[r] * na);
         mo += o->count[r]; ao += (size_t)o->count[r] * na;
+    }
+}
+void orc_get_reservoir(orc_t* o, int* count, double* offsets) {
+    size_t ao = 0;
+    for (int r = 0; r < o->nres; r++) {
+        size_t na = o->natoms[r];
+        if (count) count[r] = o->rsv_count[r];
+        if (offsets && o->rsv_off[r]) memcpy(offsets + 3 * ao, o->rsv_off[r], sizeof(double) * 3 * o->rsv_count[r] * na);
+        ao += (size_t)o->rsv_count[r] * na;
     }
 }
 void orc_get_sk(orc_t* o, double* sk) { memcpy(sk, o->A, sizeof(cplx) * o->nk); }
@@ -691,12 +716,25 @@ static int create_molecule(orc_t* o, int r, int m, mmc_move_record* rec) {
     o->count[r]++;
     orc_save_fourier(o, r, m);
     for (int d = 0; d < 3; d++) { double t = rand_uniform(o); o->com[r][3 * m + d] = o->lo[d] + o->L[d] * t; } /* :180-182 (diagonal matrix) */
-    if (m != 0) memcpy(o->off[r] + (size_t)m * na * 3, o->off[r], sizeof(double) * 3 * na); /* :198-199 */
-    apply_random_rotation(o, r, m, 1);
+    int rsv = -1;
+    if (o->has_reservoir) { /* :185-193: geometry of a randomly drawn reservoir molecule, no rotation */
+        rsv = (int)(rand_uniform(o) * o->rsv_count[r]);
+        memcpy(o->off[r] + (size_t)m * na * 3, o->rsv_off[r] + (size_t)rsv * na * 3, sizeof(double) * 3 * na);
+    } else {
+        if (m != 0) memcpy(o->off[r] + (size_t)m * na * 3, o->off[r], sizeof(double) * 3 * na); /* :198-199 */
+        apply_random_rotation(o, r, m, 1);
+    }
     orc_compute_new_energy(o, r, m, nw, 1, 0);
     double p = acceptance_probability(o, old, nw, r, MMC_CREATION);
     int acc = rand_uniform(o) <= p;
-    if (acc) { accept_insdel(o, old, nw); o->cnt.creations++; }
+    if (acc) {
+        accept_insdel(o, old, nw); o->cnt.creations++;
+        if (o->has_reservoir && o->rsv_count[r] > 0) { /* AcceptCreationMove :118-130: pool slot <- last pool slot */
+            const int last = o->rsv_count[r] - 1;
+            memmove(o->rsv_off[r] + (size_t)rsv * na * 3, o->rsv_off[r] + (size_t)last * na * 3, sizeof(double) * 3 * na);
+            o->rsv_count[r]--;
+        }
+    }
     else { o->count[r]--; orc_restore_fourier(o, r, m); } /* RejectCreationMove :141 */
     fill_record(rec, MMC_CREATION, r, m, acc, old, nw, p);
     return 0;
@@ -720,7 +758,17 @@ static void delete_molecule(orc_t* o, int r, int m, mmc_move_record* rec) {
     orc_compute_new_energy(o, r, m, nw, 0, 1);
     double p = acceptance_probability(o, old, nw, r, MMC_DELETION);
     int acc = rand_uniform(o) <= p;
-    if (acc) { accept_insdel(o, old, nw); o->cnt.deletions++; }
+    if (acc) {
+        accept_insdel(o, old, nw); o->cnt.deletions++;
+        if (o->has_reservoir) { /* AcceptDeletionMove :148-166: three draws place the molecule in the reservoir box (its COM
+                                  * is not used by the path); the offsets appended are those of slot last_molecule_index */
+            rand_uniform(o); rand_uniform(o); rand_uniform(o);
+            if (o->rsv_count[r] < o->rsv_cap[r]) {
+                memcpy(o->rsv_off[r] + (size_t)o->rsv_count[r] * na * 3, o->off[r] + (size_t)last * na * 3, sizeof(double) * 3 * na);
+                o->rsv_count[r]++;
+            }
+        }
+    }
     else { /* RejectDeletionMove :178-199 */
         o->count[r]++;
         memcpy(o->com[r] + 3 * m, o->com_old, sizeof(double) * 3);

@@ -40,6 +40,7 @@ def lib():
         L.orc_get_step_sizes.argtypes = [C.c_void_p, dp, dp]
         L.orc_get_state.argtypes = [C.c_void_p, ip, dp, dp]
         L.orc_get_sk.argtypes = [C.c_void_p, dp]
+        L.orc_get_reservoir.argtypes = [C.c_void_p, ip, dp]
         L.orc_get_energy.argtypes = [C.c_void_p, dp]
         L.orc_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
         L.orc_pair_singlemol.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp]
@@ -110,6 +111,15 @@ class Oracle:
         com = np.zeros((max(nm, 1), 3)); off = np.zeros((max(na, 1), 3))
         lib().orc_get_state(self.h, c.ctypes.data_as(C.POINTER(C.c_int)), _dp(com), _dp(off))
         return c, com[:nm], off[:na]
+
+    def reservoir(self):
+        """(count[nres], offsets [n, 3]) of the reservoir pool"""
+        s = self.sys
+        cnt = np.zeros(s.nres, dtype=np.int32)
+        lib().orc_get_reservoir(self.h, cnt.ctypes.data_as(C.POINTER(C.c_int)), None)
+        off = np.zeros((max(int((cnt * s.natoms).sum()), 1), 3))
+        lib().orc_get_reservoir(self.h, cnt.ctypes.data_as(C.POINTER(C.c_int)), _dp(off))
+        return cnt, off[:int((cnt * s.natoms).sum())]
 
     def sk(self):
         n = lib().orc_num_kvectors(self.h); a = np.zeros(2 * n); lib().orc_get_sk(self.h, _dp(a))

@@ -566,3 +566,41 @@ def test_ideal_gas_limit_is_poisson():
     e = np.zeros((C, 6)); g.download_chains(None, None, None, e, None)
     assert np.all(np.abs(e[:, :3]) < 1e-9)                       # no interaction energy anywhere
     g.close()
+
+
+# ---- reservoir box: insertion geometry from a pool, pool bookkeeping on accept ----------------------
+def test_reservoir_strict_and_batched():
+    from test_oracle_golden import with_reservoir
+    s = with_reservoir()
+    n = 400
+    tape = np.random.default_rng(21).random(8000)
+    o = orc.Oracle(s); o.system_energy(); ref = o.run(n, tape=tape)
+    # strict mode: the host owns the pool (the library is told nothing about it)
+    bare = s.copy(); bare.reservoir_count = None; bare.reservoir_offsets = None
+    g = ManiacGPU(bare); drv = StrictDriver(s, g); drv.ComputeSystemEnergy()
+    rng = TapeRng(tape); got = drv.MonteCarloLoop(rng, 1, n)
+    compare_records(got, ref)
+    assert rng.pos == o.tape_used
+    assert len(drv.rsv[0]) == o.reservoir()[0][0]
+    g.close()
+    # batched mode: pools on the device, one per chain
+    tapes = np.stack([tape, np.random.default_rng(22).random(8000)])
+    g = ManiacGPU(s, n_chains=2)
+    for c in range(2):
+        g.system_energy(c)
+    recs = g.run_batch(n, tape=tapes, records=True)
+    for c in range(2):
+        oc = orc.Oracle(s); oc.system_energy(); rc = oc.run(n, tape=tapes[c])
+        compare_records(recs[c], rc)
+        assert g.tape_used(c) == oc.tape_used and g.counters[c] == oc.counters()
+        cnt_g, off_g = g.reservoir(c); cnt_o, off_o = oc.reservoir()
+        assert np.array_equal(cnt_g, cnt_o)
+        np.testing.assert_allclose(off_g, off_o, atol=1e-12)
+        cnt, com, off, e = g.sync_to_host(c); c2, com2, off2 = oc.state()
+        assert np.array_equal(cnt, c2)
+        np.testing.assert_allclose(off, off2, atol=1e-12)
+        assert rel_err(e, oc.energy()) < TOL
+    r2 = g.run_batch(300, seed=5, records=True)       # Philox stream
+    oc = orc.Oracle(s); oc.system_energy(); oc.run(n, tape=tapes[1])
+    compare_records(r2[1], oc.run(300, seed=5, chain=1, step0=n))
+    g.close()

@@ -233,3 +233,46 @@ def test_swap_move_identities():
     s0 = two_species(); s0.p_swap = 0.0
     o0 = orc.Oracle(s0); o0.system_energy()
     assert not (o0.run(300, seed=5)["kind"] == 5).any()
+
+
+def with_reservoir(name="h2o_ads", n_pool=12, seed=3):
+    """fixture system + a reservoir box of n_pool randomly oriented copies of the active molecule"""
+    from maniac_mc_b200 import builders
+    s = load_system(name, init_sk=1, deletion_mode=1)
+    rng = np.random.default_rng(seed)
+    cnt = np.zeros(s.nres, dtype=np.int32); offs = []
+    mo, ao = s.mol_offsets()
+    for r in range(s.nres):
+        if s.is_active[r]:
+            na = int(s.natoms[r]); tmpl = s.offsets[ao[r]:ao[r] + na]
+            cnt[r] = n_pool
+            offs.append(np.einsum("nij,aj->nai", builders.random_rotations(rng, n_pool), tmpl).reshape(-1, 3))
+    s.reservoir_count, s.reservoir_offsets = cnt, np.concatenate(offs)
+    return s
+
+
+def test_reservoir_insertion_geometry_and_bookkeeping():
+    """has_reservoir (create_molecule.f90:185-193, :118-130, delete_molecule.f90:148-166): inserted molecules take a pool
+    geometry (no rotation draws), pool + box molecule count is conserved, tracked energies stay consistent."""
+    s = with_reservoir()
+    o = orc.Oracle(s); o.system_energy()
+    c0, off0 = o.reservoir()
+    assert c0.tolist() == [12] and off0.shape == (48, 3)
+    ref = o.run(500, tape=np.random.default_rng(4).random(8000))
+    acc_c = int(((ref["kind"] == MMC_CREATION) & (ref["accepted"] == 1)).sum())
+    acc_d = int(((ref["kind"] == MMC_DELETION) & (ref["accepted"] == 1)).sum())
+    assert acc_c > 0 and acc_d > 0
+    c1, off1 = o.reservoir()
+    cnt, com, off = o.state()
+    assert c1[0] == 12 - acc_c + acc_d and cnt[0] + c1[0] == int(s.count[0]) + 12
+    # every pool geometry is a rigid copy of the template: same pair distances
+    d_ref = np.linalg.norm(off0[:4, None] - off0[None, :4], axis=2)
+    for i in range(c1[0]):
+        g = off1[4 * i:4 * i + 4]
+        np.testing.assert_allclose(np.linalg.norm(g[:, None] - g[None], axis=2), d_ref, atol=1e-9)
+    s2 = s.copy(); s2.count, s2.com, s2.offsets = cnt, com, off
+    assert rel_err(o.energy(), orc.Oracle(s2).system_energy()) < 1e-10
+    # creation with a reservoir draws 3 (position) + 1 (pool pick) + 1 (accept) uniforms; without: 3 + 2 + 1
+    a = orc.Oracle(s); a.system_energy()
+    rec = a.single_move(MMC_CREATION, 0, int(s.count[0]), np.array([0.1, 0.2, 0.3, 0.5, 0.999999]))
+    assert rec["kind"] == MMC_CREATION
