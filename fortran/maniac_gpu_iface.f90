@@ -9,7 +9,7 @@ module maniac_gpu_iface
     public :: mmc_desc, mmc_init, mmc_destroy, mmc_last_error, mmc_system_energy, mmc_trial_energy, &
               mmc_trial_commit, mmc_sync_to_host, mmc_run_batch, mmc_ewald_setup, mmc_check, &
               mmc_set_chain_params, mmc_run_batch_async, mmc_synchronize, mmc_download_chains, mmc_upload_chains, &
-              mmc_shard_step_begin, mmc_shard_step_end, mmc_shard_trial_begin, mmc_shard_trial_end, mmc_trial_energy_swap
+              mmc_shard_step_begin, mmc_shard_step_end, mmc_shard_trial_begin, mmc_shard_trial_end, mmc_trial_energy_swap, mmc_adjust_step_sizes
 
     integer(c_int), parameter, public :: MMC_CREATION = 1, MMC_DELETION = 2, MMC_TRANSLATION = 3, MMC_ROTATION = 4, MMC_SWAP = 5
     integer(c_int), parameter, public :: MMC_NE = 6
@@ -98,6 +98,11 @@ module maniac_gpu_iface
             integer(c_int), value :: chain
             real(c_double), intent(in) :: fugacity(*)
             real(c_double), value :: temperature
+        end function
+        !> AdjustMoveStepSizes for every chain from its own counters (once per block, batched mode)
+        integer(c_int) function mmc_adjust_step_sizes(handle) bind(C, name="mmc_adjust_step_sizes")
+            import :: c_int, c_ptr
+            type(c_ptr), value :: handle
         end function
         integer(c_int) function mmc_run_batch_async(handle, n_steps, seed) bind(C, name="mmc_run_batch_async")
             import :: c_int, c_ptr, c_int64_t

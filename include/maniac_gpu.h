@@ -153,6 +153,10 @@ int mmc_get_chain_state(mmc_t* handle, int chain, int* count, double* com, doubl
  * trajectory no longer depends on which GPU or which slot it was dealt to. */
 int mmc_set_chain_id(mmc_t* handle, int chain, uint32_t id);
 int mmc_set_step_sizes(mmc_t* handle, int chain, double translation_step, double rotation_step);
+/* AdjustMoveStepSizes (monte_carlo_utils.f90:99-129) for every chain from its own counters, enqueued on the library's
+ * stream; call once per block when input%recalibrate_moves is set (monte_carlo.f90:78).  Literal, quirks included. */
+int mmc_adjust_step_sizes(mmc_t* handle);
+int mmc_get_step_sizes(mmc_t* handle, int chain, double* translation_step, double* rotation_step);
 
 /* ---- single-point energy ----------------------------------------------------------------- */
 

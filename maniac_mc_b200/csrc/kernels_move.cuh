@@ -353,6 +353,26 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
     t.kind = -t.kind;
 }
 
+// AdjustMoveStepSizes monte_carlo_utils.f90:99-129, once per block for every chain (batched mode).  Literal: the
+// acceptance ratios are formed in single precision (real(counter)), `else if (acc - target < tol)` also fires inside the
+// tolerance band, and the rotation branch is min(angle * 1.95, MIN_ROTATION_ANGLE) (quirks Q6).
+__global__ void k_adjust_step_sizes(DevConst dc, ChainState cs) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= dc.n_chains) return;
+    const mmc_counters& k = cs.counters[c];
+    const double target = 0.40, tol = 0.05;          // parameters.f90:24-25
+    if (k.trial_translations > 500) {                 // MIN_TRIALS_FOR_RECALIBRATION parameters.f90:30
+        const double acc = (double)((float)k.translations / (float)k.trial_translations);
+        if (acc - target > tol) cs.tstep[c] = fmin(cs.tstep[c] * 1.05, 3.0);         // MAX_TRANSLATION_STEP
+        else if (acc - target < tol) cs.tstep[c] = fmax(cs.tstep[c] * 0.95, 1.0e-3);  // MIN_TRANSLATION_STEP
+    }
+    if (k.trial_rotations > 500) {
+        const double acc = (double)((float)k.rotations / (float)k.trial_rotations);
+        if (acc - target > tol) cs.rstep[c] = fmin(cs.rstep[c] * 1.05, 0.78);         // MAX_ROTATION_ANGLE
+        else if (acc - target < tol) cs.rstep[c] = fmin(cs.rstep[c] * 1.95, 1.0e-3);  // as written in the reference
+    }
+}
+
 struct BatchCtl { RngSrc rng; mmc_move_record* recs; long long rec_stride; long long rec_base; };
 
 // strict mode: sums the per-CTA partials of k_sweep in a fixed order -> Trial.old_e/new_e ; the host decides

@@ -583,6 +583,22 @@ extern "C" int mmc_set_chain_params(mmc_t* h, int c, const double* fugacity, dou
     return 0;
 }
 
+extern "C" int mmc_adjust_step_sizes(mmc_t* h) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    k_adjust_step_sizes<<<(h->dc.n_chains + 127) / 128, 128, 0, h->stream>>>(h->dc, h->cs);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+extern "C" int mmc_get_step_sizes(mmc_t* h, int c, double* tstep, double* rstep) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (tstep) CK(cudaMemcpy(tstep, h->cs.tstep + c, sizeof(double), cudaMemcpyDeviceToHost));
+    if (rstep) CK(cudaMemcpy(rstep, h->cs.rstep + c, sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
 extern "C" int mmc_set_chain_id(mmc_t* h, int c, uint32_t id) {
     CHECK_CHAIN(h, c);
     CK(cudaSetDevice(h->device));

@@ -42,7 +42,7 @@ def build(force=False, verbose=False):
 # every symbol declared in include/maniac_gpu.h
 ABI_SYMBOLS = [
     "mmc_ewald_setup", "mmc_init", "mmc_destroy", "mmc_last_error", "mmc_num_kvectors", "mmc_get_kvectors",
-    "mmc_set_chain_params", "mmc_set_chain_id", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
+    "mmc_set_chain_params", "mmc_set_chain_id", "mmc_adjust_step_sizes", "mmc_get_step_sizes", "mmc_set_chain_state", "mmc_get_chain_state", "mmc_set_step_sizes",
     "mmc_system_energy", "mmc_trial_energy", "mmc_trial_energy_swap", "mmc_trial_commit", "mmc_sync_to_host", "mmc_get_sk", "mmc_get_reservoir",
     "mmc_run_batch", "mmc_run_batch_async", "mmc_synchronize", "mmc_tape_used",
     "mmc_dbg_pair_singlemol", "mmc_dbg_self_singlemol", "mmc_dbg_intra_singlemol", "mmc_dbg_table_lookup",
@@ -72,6 +72,8 @@ def load():
     L.mmc_set_chain_params.argtypes = [vp, C.c_int, dp, C.c_double]
     L.mmc_set_chain_state.argtypes = [vp, C.c_int, ip, dp, dp]
     L.mmc_set_chain_id.argtypes = [vp, C.c_int, C.c_uint32]
+    L.mmc_adjust_step_sizes.argtypes = [vp]
+    L.mmc_get_step_sizes.argtypes = [vp, C.c_int, dp, dp]
     L.mmc_get_chain_state.argtypes = [vp, C.c_int, ip, dp, dp]
     L.mmc_set_step_sizes.argtypes = [vp, C.c_int, C.c_double, C.c_double]
     L.mmc_system_energy.argtypes = [vp, C.c_int, dp]
@@ -177,6 +179,15 @@ class ManiacGPU:
 
     def set_chain_id(self, chain, stream_id):
         _ck(load().mmc_set_chain_id(self.h, chain, int(stream_id)))
+
+    def adjust_step_sizes(self):
+        """AdjustMoveStepSizes for every chain (once per block)"""
+        _ck(load().mmc_adjust_step_sizes(self.h))
+
+    def step_sizes(self, chain=0):
+        a, b = C.c_double(), C.c_double()
+        _ck(load().mmc_get_step_sizes(self.h, chain, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def set_step_sizes(self, chain, tstep, rstep):
         _ck(load().mmc_set_step_sizes(self.h, chain, float(tstep), float(rstep)))

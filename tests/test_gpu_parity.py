@@ -604,3 +604,22 @@ def test_reservoir_strict_and_batched():
     oc = orc.Oracle(s); oc.system_energy(); oc.run(n, tape=tapes[1])
     compare_records(r2[1], oc.run(300, seed=5, chain=1, step0=n))
     g.close()
+
+
+def test_adjust_step_sizes_per_block():
+    """MonteCarloLoop's per-block AdjustMoveStepSizes (monte_carlo_utils.f90:99-129) in batched mode: blocks of 700 steps with
+    recalibration after each == the oracle doing the same; the step sizes follow the reference's literal rule."""
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1, p_translation=0.45, p_rotation=0.45)
+    g = ManiacGPU(s, n_chains=2)
+    for c in range(2):
+        g.system_energy(c)
+    o = orc.Oracle(s); o.system_energy(); o.set_recalibrate(1)
+    for b in range(4):
+        recs = g.run_batch(700, seed=31, records=True)
+        g.adjust_step_sizes()
+        ref = o.run(700, seed=31, chain=1, step0=700 * b); o.adjust_step_sizes()
+        compare_records(recs[1], ref)
+        t, r = g.step_sizes(1); t2, r2 = o.step_sizes()
+        assert t == t2 and r == r2
+    assert (t, r) != (s.translation_step, s.rotation_step)
+    g.close()
