@@ -100,3 +100,22 @@ def test_fortran_interface_matches_header():
     assert len(names) >= 15
     for n in names:
         assert hasattr(L, n), f"{n} bound in the Fortran interface but not exported"
+
+
+def test_fortran_glue_uses_declared_names_only():
+    """fortran/maniac_gpu_glue.f90 (compile-untested): every mmc_* it calls is declared in the interface module and
+    exported, every mmc_desc component it sets is a header field, and it sets all of them."""
+    glue = open(os.path.join(ROOT, "fortran", "maniac_gpu_glue.f90")).read()
+    code = "\n".join(l.split("!")[0] for l in glue.splitlines())
+    f90 = open(os.path.join(ROOT, "fortran", "maniac_gpu_iface.f90")).read()
+    declared = set(re.findall(r'bind\(C, name="(\w+)"\)', f90)) | {"mmc_check", "mmc_desc"}
+    used = set(re.findall(r"\b(mmc_\w+)", code))
+    assert used and used <= declared, used - declared
+    L = lib.load()
+    for n in used - {"mmc_check", "mmc_desc"}:
+        assert hasattr(L, n)
+    hdr = open(os.path.join(ROOT, "include", "maniac_gpu.h")).read()
+    body = re.sub(r"/\*.*?\*/", "", re.search(r"typedef struct mmc_desc \{(.*?)\} mmc_desc;", hdr, re.S).group(1), flags=re.S)
+    fields = set(re.findall(r"(\w+)(?:\[\d+\])?\s*;", body))
+    set_in_glue = set(re.findall(r"\bd%(\w+)", code))
+    assert set_in_glue == fields, (set_in_glue ^ fields)
