@@ -124,6 +124,20 @@ module maniac_gpu_iface
             type(c_ptr), value :: handle, count, com, offsets, energies, counters
         end function
         !> k-sharded mode: dev_sums is a DEVICE buffer (6 doubles per chain) all-reduced by the caller between begin and end
+        !> per-block snapshot behind the queued work (slot 0 or 1); returns at once
+        integer(c_int) function mmc_snapshot_begin(handle, slot) bind(C, name="mmc_snapshot_begin")
+            import :: c_ptr, c_int
+            type(c_ptr), value :: handle
+            integer(c_int), value :: slot
+        end function
+        !> waits for that snapshot only; the five c_ptr results point into pinned host memory (c_f_pointer them)
+        integer(c_int) function mmc_snapshot_wait(handle, slot, count, com, offsets, energies, counters) &
+                bind(C, name="mmc_snapshot_wait")
+            import :: c_ptr, c_int
+            type(c_ptr), value :: handle
+            integer(c_int), value :: slot
+            type(c_ptr), intent(out) :: count, com, offsets, energies, counters
+        end function
         integer(c_int) function mmc_shard_step_begin(handle, seed, dev_sums) bind(C, name="mmc_shard_step_begin")
             import :: c_int, c_ptr, c_int64_t
             type(c_ptr), value :: handle, dev_sums

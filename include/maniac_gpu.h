@@ -210,6 +210,16 @@ int mmc_chain_capacity(const mmc_t* handle, int* g_mols, int* g_atoms);
 int mmc_upload_chains(mmc_t* handle, const int* count, const double* com, const double* offsets);
 int mmc_download_chains(mmc_t* handle, int* count, double* com, double* offsets, double* energies,
                         mmc_counters* counters);
+/* Per-block output without stalling the chains (UpdateFiles / PrintStatus, monte_carlo.f90:82-84, run between blocks;
+ * the reference's writers are write_utils.f90:13-188).  mmc_snapshot_begin queues, behind the work already on the
+ * handle's stream, a device-side copy of every chain's counts, coordinates, energies and counters, and copies it to
+ * library-owned pinned host memory on a second stream: the next mmc_run_batch_async may be issued immediately.
+ * slot = 0 or 1 (two snapshots may be in flight).  mmc_snapshot_wait blocks until THAT copy has landed (not until the
+ * handle's stream drains) and returns pointers laid out like mmc_download_chains' arguments (count [n_chains][nres]);
+ * they stay valid until the next mmc_snapshot_begin on the same slot or mmc_destroy. */
+int mmc_snapshot_begin(mmc_t* handle, int slot);
+int mmc_snapshot_wait(mmc_t* handle, int slot, const int** count, const double** com, const double** offsets,
+                      const double** energies, const mmc_counters** counters);
 /* tracked A(k) as (re,im) pairs, 2*K doubles (ewald%recip_amplitude) */
 /* reservoir pool of one chain (batched mode): count[nres], offsets packed like mmc_desc.reservoir_offsets
  * (capacity reservoir_count + capacity molecules per type) */

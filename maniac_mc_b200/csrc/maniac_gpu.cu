@@ -59,6 +59,12 @@ struct mmc_handle {
     int64_t launches = 0;
     unsigned long long steps_done = 0;     // Philox step counter across batches
     int pending_chain = -1;
+    // per-block snapshots (mmc_snapshot_begin / _wait): device blob + pinned mirror per slot, copied out on copy_stream
+    struct Snap { char* dev = nullptr; char* host = nullptr; cudaEvent_t taken = nullptr, landed = nullptr; bool pending = false; };
+    Snap snap[2];
+    size_t snap_off[5] = {0, 0, 0, 0, 0}, snap_bytes = 0;
+    std::vector<int> snap_count[2];        // compacted [C][nres] counts handed to the caller
+    cudaStream_t copy_stream = nullptr;
 };
 
 template <typename T>
@@ -108,6 +114,13 @@ extern "C" void mmc_destroy(mmc_t* h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_tape_pos) cudaFreeHost(h->h_tape_pos);
+    for (auto& s : h->snap) {
+        if (s.dev) cudaFree(s.dev);
+        if (s.host) cudaFreeHost(s.host);
+        if (s.taken) cudaEventDestroy(s.taken);
+        if (s.landed) cudaEventDestroy(s.landed);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -706,6 +719,64 @@ extern "C" int mmc_download_chains(mmc_t* h, int* count, double* com, double* of
     if (count)  // inactive residues: the host already knows them
         for (size_t c = 0; c < C; c++)
             for (int r = 0; r < dc.nres; r++) if (!dc.is_active[r]) count[c * dc.nres + r] = dc.cap[r];
+    return 0;
+}
+
+// Per-block snapshot without stalling the chains (write_utils.f90:13-188 runs between blocks in the reference):
+// device-to-device copy of the small per-chain state on the handle's stream (the next batch may be queued right behind
+// it), then ONE device-to-host copy of the blob into pinned memory on a second stream.
+extern "C" int mmc_snapshot_begin(mmc_t* h, int slot) {
+    if (!h) return fail("null handle");
+    if (slot < 0 || slot > 1) return fail("mmc_snapshot_begin: slot must be 0 or 1");
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; const size_t C = dc.n_chains;
+    if (!h->snap_bytes) {
+        const size_t sz[5] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
+                              C * MMC_NE * sizeof(double), C * sizeof(mmc_counters)};
+        size_t o = 0;
+        for (int i = 0; i < 5; i++) { h->snap_off[i] = o; o += (sz[i] + 255) & ~(size_t)255; }
+        h->snap_bytes = o;
+        CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    }
+    mmc_handle::Snap& s = h->snap[slot];
+    if (!s.dev) {
+        CK(cudaMalloc((void**)&s.dev, h->snap_bytes));
+        CK(cudaMallocHost((void**)&s.host, h->snap_bytes));
+        CK(cudaEventCreateWithFlags(&s.taken, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&s.landed, cudaEventDisableTiming));
+    }
+    if (s.pending) CK(cudaEventSynchronize(s.landed));   // the slot's previous copy-out still reads s.dev
+    const void* src[5] = {h->cs.count, h->cs.gcom, h->cs.goff, h->cs.energy, h->cs.counters};
+    const size_t sz[5] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
+                          C * MMC_NE * sizeof(double), C * sizeof(mmc_counters)};
+    for (int i = 0; i < 5; i++)
+        if (sz[i]) CK(cudaMemcpyAsync(s.dev + h->snap_off[i], src[i], sz[i], cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaEventRecord(s.taken, h->stream));
+    CK(cudaStreamWaitEvent(h->copy_stream, s.taken, 0));
+    CK(cudaMemcpyAsync(s.host, s.dev, h->snap_bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+    CK(cudaEventRecord(s.landed, h->copy_stream));
+    s.pending = true;
+    return 0;
+}
+
+extern "C" int mmc_snapshot_wait(mmc_t* h, int slot, const int** count, const double** com, const double** offsets,
+                                 const double** energies, const mmc_counters** counters) {
+    if (!h) return fail("null handle");
+    if (slot < 0 || slot > 1 || !h->snap[slot].pending) return fail("mmc_snapshot_wait: no snapshot pending on this slot");
+    CK(cudaSetDevice(h->device));
+    mmc_handle::Snap& s = h->snap[slot];
+    CK(cudaEventSynchronize(s.landed));                  // waits for the copy-out only, not for the handle's stream
+    const DevConst& dc = h->dc; const size_t C = dc.n_chains;
+    std::vector<int>& cnt = h->snap_count[slot];
+    cnt.resize(C * dc.nres);
+    const int* raw = (const int*)(s.host + h->snap_off[0]);
+    for (size_t c = 0; c < C; c++)
+        for (int r = 0; r < dc.nres; r++) cnt[c * dc.nres + r] = dc.is_active[r] ? raw[c * MMC_MAX_RES + r] : dc.cap[r];
+    if (count) *count = cnt.data();
+    if (com) *com = (const double*)(s.host + h->snap_off[1]);
+    if (offsets) *offsets = (const double*)(s.host + h->snap_off[2]);
+    if (energies) *energies = (const double*)(s.host + h->snap_off[3]);
+    if (counters) *counters = (const mmc_counters*)(s.host + h->snap_off[4]);
     return 0;
 }
 

@@ -153,6 +153,30 @@ class IsothermSweep:
         self.avg.add(self._cnt[:n, self.res], self._e[:n, 5], self._ctr[:n])
         self.step += n_steps
 
+    def run_blocks(self, n_blocks, n_steps, seed=0, output_root=None, trajectory=False, literal=True):
+        """`n_blocks` blocks with the per-block exchange off the critical path (`mmc_snapshot_begin/_wait`): block b+1 is
+        queued before the host reads block b's snapshot.  With `output_root` every chain also gets the reference's
+        per-block files (`energy.dat`, `number_<RES>.dat`, `moves.dat`, optionally `trajectory.lammpstrj`) in
+        `<output_root>/p<point>_r<replica>/` (`writers.py`)."""
+        from . import writers as W
+        ws = [None] * self.gpu.n_chains
+        if output_root is not None:
+            for c, cid in enumerate(self.ids):
+                ws[c] = W.ChainWriter(W.chain_directory(output_root, cid.point, cid.replica), self.sys, literal=literal,
+                                      nb_block=n_blocks, trajectory=trajectory)
+        n = len(self.ids)
+
+        def sample(block, snap):
+            cnt, _, _, e, ctr = snap
+            if block > 0:
+                self.avg.add(cnt[:n, self.res], e[:n, 5], ctr[:n])
+        pipe = W.BlockPipeline(self.gpu, ws, on_block=sample)
+        if output_root is not None and self.step == 0:
+            pipe.write_initial()
+        pipe.block = self.step // max(n_steps, 1)
+        pipe.run(n_blocks, n_steps, seed=seed)
+        self.step += n_blocks * n_steps
+
     def table(self):
         return gather_table(self.ids, self.avg.rows(), self.n_points, self.replicas, self.world)
 

@@ -49,6 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
+    "mmc_snapshot_begin", "mmc_snapshot_wait",
 ]
 
 _lib = None
@@ -104,6 +105,8 @@ def load():
     L.mmc_chain_capacity.argtypes = [vp, ip, ip]
     L.mmc_upload_chains.argtypes = [vp, vp, vp, vp]
     L.mmc_download_chains.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.mmc_snapshot_begin.argtypes = [vp, C.c_int]
+    L.mmc_snapshot_wait.argtypes = [vp, C.c_int] + [C.POINTER(vp)] * 5
     L.mmc_profile_kernels.argtypes = [vp, C.c_int, C.c_uint64, dp, C.POINTER(C.c_int64)]
     _lib = L
     return L
@@ -301,6 +304,28 @@ class ManiacGPU:
 
     def download_chains(self, count=None, com=None, offsets=None, energies=None, counters=None):
         _ck(load().mmc_download_chains(self.h, _addr(count), _addr(com), _addr(offsets), _addr(energies), _addr(counters)))
+
+    def snapshot_begin(self, slot=0):
+        """queue a per-block snapshot behind the work already on the stream; returns at once"""
+        _ck(load().mmc_snapshot_begin(self.h, slot))
+
+    def snapshot_wait(self, slot=0):
+        """(count [C, nres], com [C, g_mols, 3], offsets [C, g_atoms, 3], energies [C, 6], counters [C, N_COUNTERS]) of
+        the snapshot on `slot`, copied out of the library's pinned buffers; does not wait for later batches"""
+        from .system import N_COUNTERS
+        p = [C.c_void_p() for _ in range(5)]
+        _ck(load().mmc_snapshot_wait(self.h, slot, *[C.byref(x) for x in p]))
+        g_mols, g_atoms = self.chain_capacity()
+        n = self.n_chains
+
+        def view(ptr, ctype, shape):
+            size = int(np.prod(shape))
+            if size == 0:
+                return np.zeros(shape, dtype=ctype)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ctype)), shape=(size,)).reshape(shape).copy()
+        return (view(p[0], C.c_int, (n, self.sys.nres)), view(p[1], C.c_double, (n, g_mols, 3)),
+                view(p[2], C.c_double, (n, g_atoms, 3)), view(p[3], C.c_double, (n, 6)),
+                view(p[4], C.c_int64, (n, N_COUNTERS)))
 
     def profile_kernels(self, n_steps, seed=0):
         ms = (C.c_double * 3)(); n = (C.c_int64 * 3)()

@@ -1,6 +1,8 @@
 """GPU parity tests (B200): every result goes through the C ABI of libmaniacgpu.so and is compared with the CPU
 oracle on the same inputs.  FP64 tolerances: 1e-10 relative on energies (north star), 1e-12 where the sum order
 is the only difference; accept/reject sequences must be identical."""
+import os
+
 import numpy as np
 import pytest
 
@@ -8,7 +10,7 @@ from conftest import load_system, rel_err
 from maniac_mc_b200 import builders
 from maniac_mc_b200.driver import StrictDriver, TapeRng
 from maniac_mc_b200.lib import ManiacGPU, ManiacGpuError
-from maniac_mc_b200.system import (E_INTRA, E_RECIP, E_TOTAL, MMC_CREATION, MMC_DELETION, MMC_ROTATION,
+from maniac_mc_b200.system import (E_INTRA, E_RECIP, E_TOTAL, MMC_CREATION, MMC_DELETION, MMC_ROTATION, N_COUNTERS,
                                    MMC_TRANSLATION)
 from oracle import oracle as orc
 
@@ -623,3 +625,91 @@ def test_adjust_step_sizes_per_block():
         assert t == t2 and r == r2
     assert (t, r) != (s.translation_step, s.rotation_step)
     g.close()
+
+
+def test_snapshot_is_the_state_at_its_place_in_the_stream(tmp_path):
+    """mmc_snapshot_begin/_wait return exactly what mmc_download_chains would have returned at that point of
+    the stream, although two more batches were queued behind the snapshot before the host waited for it; both slots
+    can be in flight; and BlockPipeline writes the reference's per-block files from them, one directory per chain."""
+    from maniac_mc_b200 import writers as W
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    C = 6
+    g = ManiacGPU(s, n_chains=C)
+    for c in range(C):
+        g.system_energy(c)
+    g_mols, g_atoms = g.chain_capacity()
+
+    def download():
+        cnt = np.zeros((C, s.nres), dtype=np.int32); com = np.zeros((C, g_mols, 3)); off = np.zeros((C, g_atoms, 3))
+        e = np.zeros((C, 6)); ctr = np.zeros((C, N_COUNTERS), dtype=np.int64)
+        g.download_chains(cnt, com, off, e, ctr)
+        return cnt, com, off, e, ctr
+
+    # reference sequence with synchronous downloads
+    g.run_batch_async(300, seed=3); a = download()
+    g.run_batch_async(300, seed=3); b = download()
+    g.run_batch_async(300, seed=3); g.synchronize()
+    g.close()
+    # same sequence, snapshots queued and read late
+    g = ManiacGPU(s, n_chains=C)
+    for c in range(C):
+        g.system_energy(c)
+    g.run_batch_async(300, seed=3); g.snapshot_begin(0)
+    g.run_batch_async(300, seed=3); g.snapshot_begin(1)
+    g.run_batch_async(300, seed=3)
+    sa, sb = g.snapshot_wait(0), g.snapshot_wait(1)
+    for want, got in ((a, sa), (b, sb)):
+        for w, x in zip(want, got):
+            assert np.array_equal(w, x)
+    assert not np.array_equal(sa[4], sb[4])                         # the counters moved between the two
+    with pytest.raises(RuntimeError):
+        g.snapshot_begin(2)
+    g.close()
+    g = ManiacGPU(s, n_chains=C)
+    with pytest.raises(RuntimeError):
+        g.snapshot_wait(0)                                          # nothing pending
+    for c in range(C):
+        g.system_energy(c)
+    ws = [W.ChainWriter(W.chain_directory(str(tmp_path), c, 0), s, nb_block=3) if c != 4 else None for c in range(C)]
+    pipe = W.BlockPipeline(g, ws)
+    pipe.write_initial()
+    last = pipe.run(3, 300, seed=3)
+    g.synchronize()
+    assert np.array_equal(last[0], download()[0]) and np.array_equal(last[3], download()[3])
+    assert sorted(os.listdir(tmp_path)) == ["p000_r00", "p001_r00", "p002_r00", "p003_r00", "p005_r00"]
+    d = tmp_path / "p002_r00"
+    en = (d / "energy.dat").read_text().splitlines()
+    assert en[0] == W.ENERGY_HEADER and [l.split()[0] for l in en[1:]] == ["0", "1", "2", "3"]
+    assert en[-1] == W.energy_row(3, last[3][2])
+    mv = (d / "moves.dat").read_text().splitlines()
+    assert mv[-1] == W.moves_row(3, last[4][2]) and int(mv[-1].split()[1]) > 0
+    tr = (d / "trajectory.lammpstrj").read_text().splitlines()
+    assert tr.count("ITEM: TIMESTEP") == 4
+    n_last = int((last[0][2] * s.natoms).sum())
+    assert int(tr[-(n_last + 9) + 3]) == n_last                     # NUMBER OF ATOMS of the last frame
+    g.close()
+
+
+def test_isotherm_run_blocks_equals_blockwise_sync_and_writes_per_chain_files(tmp_path):
+    """The pipelined block loop (snapshots read one block late, files written under the next block) gives the same
+    averages table as the synchronous loop, and one directory of reference-format files per (point, replica)."""
+    from maniac_mc_b200 import isotherm as iso
+    from maniac_mc_b200 import writers as W
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    a = iso.IsothermSweep(s, n_points=4, replicas=2, lo_atm=1.0, hi_atm=1e5)
+    for b in range(4):
+        a.run_block(250, seed=11)
+    ta = a.table(); a.close()
+    b = iso.IsothermSweep(s, n_points=4, replicas=2, lo_atm=1.0, hi_atm=1e5)
+    b.run_blocks(4, 250, seed=11, output_root=str(tmp_path), trajectory=True, literal=False)
+    tb = b.table(); b.close()
+    assert np.array_equal(ta, tb)
+    assert sorted(os.listdir(tmp_path)) == [f"p{p:03d}_r{r:02d}" for p in range(4) for r in range(2)]
+    d = tmp_path / "p003_r01"
+    rows = (d / "energy.dat").read_text().splitlines()
+    assert len(rows) == 6 and rows[0] == W.ENERGY_HEADER
+    tr = (d / "trajectory.lammpstrj").read_text().splitlines()
+    assert [tr[i + 1].strip() for i, l in enumerate(tr) if l == "ITEM: TIMESTEP"] == ["0", "1", "2", "3", "4"]
+    num = (d / f"number_res{b.res + 1}.dat").read_text().splitlines()
+    if len(num) == 6:                                              # a row per block: the chain was never empty
+        assert abs(np.mean([int(l.split()[1]) for l in num[2:]]) - tb[1, 3, 0]) < 1e-12   # the rows ARE the table's samples
