@@ -90,7 +90,7 @@ contains
         d%com = c_loc(p_com); d%offsets = c_loc(p_off); d%fugacity = c_loc(p_fug)
         d%box_lo = primary%bounds(:, 1)
         do i = 1, 3
-            d%box_len(i) = primary%matrix(i, i)                   ! box%type 1, 2 only (orthorhombic)
+            d%box_len(i) = primary%matrix(i, i)                   ! lx, ly, lz (the diagonal, also for box%type 3)
         end do
         d%alpha = ewald%alpha; d%cutoff = input%real_space_cutoff; d%temperature = input%temp_K; d%kmax = ewald%kmax
         d%translation_step = input%translation_step; d%rotation_step = input%rotation_step_angle
@@ -99,7 +99,7 @@ contains
         d%device = device; d%coulomb_xcut = 0.0_c_double
         d%shard_rank = 0; d%shard_count = 1
         d%reservoir_count = c_null_ptr; d%reservoir_offsets = c_null_ptr   ! strict mode: the host keeps reservoir%
-        if (primary%type == 3) call mmc_check(1_c_int)            ! triclinic cells are not supported by the library
+        d%tilt = primary%tilt                                     ! xy, xz, yz; zero for box%type 1 and 2
         call mmc_check(mmc_init(gpu, d))
     end subroutine gpu_attach
 

@@ -29,6 +29,7 @@ module maniac_gpu_iface
         integer(c_int) :: shard_rank, shard_count
         real(c_double) :: p_swap
         type(c_ptr) :: reservoir_count, reservoir_offsets
+        real(c_double) :: tilt(3)
     end type mmc_desc
 
     interface

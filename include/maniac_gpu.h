@@ -100,6 +100,13 @@ typedef struct mmc_desc {
      * device; in strict mode the host owns the pool and these stay NULL.  NULL = no reservoir. */
     const int* reservoir_count;      /* [nres] reservoir%num_residues */
     const double* reservoir_offsets; /* [3 * sum(reservoir_count*natoms)] reservoir%site_offset, packed like offsets */
+    /* Triclinic cell (box%type 3): LAMMPS tilt factors xy, xz, yz (box%tilt, readers_utils.f90:238-240) of the cell
+     * a = (lx, 0, 0), b = (xy, ly, 0), c = (xz, yz, lz) with lx, ly, lz = box_len; all zero = orthorhombic.  The
+     * reference mixes row and column conventions for this cell (ApplyPBC does not even return a point
+     * it need not wrap), so the library implements ONE consistent convention instead: fractional coordinates
+     * s = (a b c)^-1 (r - box_lo), k = 2 pi (a b c)^-T n, nearest lattice image (ComputeDistance's 27-image search,
+     * geometry_utils.f90:397-411, with a, b, c as the shifts), insertion at box_lo + (a b c) u. */
+    double tilt[3];
 } mmc_desc;
 
 /* One record per trial move of a batched run (optional output). */

@@ -39,6 +39,7 @@ class MmcDesc(C.Structure):
         ("shard_count", C.c_int),
         ("p_swap", C.c_double),
         ("reservoir_count", C.POINTER(C.c_int)), ("reservoir_offsets", C.POINTER(C.c_double)),
+        ("tilt", C.c_double * 3),
     ]
 
 
@@ -113,6 +114,7 @@ class System:
     reservoir_count: np.ndarray | None = None     # [nres] molecules in the reservoir box per type (None = no reservoir)
     reservoir_offsets: np.ndarray | None = None   # [sum(count*natoms), 3] their site offsets, packed like `offsets`
     ewald_tolerance: float = 1e-5
+    tilt: np.ndarray = field(default_factory=lambda: np.zeros(3))   # xy, xz, yz (box%tilt); zeros = orthorhombic
 
     # ---- helpers ----
     @property
@@ -178,6 +180,8 @@ class System:
         d.init_sk, d.deletion_mode, d.use_table, d.device = self.init_sk, self.deletion_mode, self.use_table, device
         d.coulomb_xcut = float(self.coulomb_xcut)
         d.shard_rank, d.shard_count = int(shard_rank), int(shard_count)
+        for k in range(3):
+            d.tilt[k] = float(self.tilt[k])
         if self.reservoir_count is not None:
             d.reservoir_count = arr("reservoir_count", self.reservoir_count, np.int32)
             ro = np.asarray(self.reservoir_offsets, dtype=np.float64)
@@ -195,6 +199,8 @@ class System:
         d = {k: getattr(self, k) for k in self._ARRS}
         d.update({k: np.array(getattr(self, k)) for k in self._SCAL})
         d["kmax"] = np.array(self.kmax, dtype=np.int32)
+        if np.any(np.asarray(self.tilt) != 0.0):
+            d["tilt"] = np.asarray(self.tilt, dtype=np.float64)
         np.savez_compressed(path, **d)
 
     @classmethod
@@ -207,6 +213,8 @@ class System:
             v = z[k].item()
             kw[k] = int(v) if k in ("init_sk", "deletion_mode", "use_table") else float(v)
         kw["kmax"] = [int(v) for v in z["kmax"]]
+        if "tilt" in z.files:
+            kw["tilt"] = z["tilt"]
         return cls(**kw)
 
     def copy(self):

@@ -58,6 +58,7 @@ typedef struct orc {
     double **com;  /* com[r][3*m + d]                      primary%mol_com(d,r,m)        */
     double **off;  /* off[r][(m*natoms[r] + a)*3 + d]      primary%site_offset(d,r,m,a)  */
     double lo[3], L[3], volume;
+    double tilt[3]; int tri; double half_min2;   /* xy, xz, yz; any non-zero; (min(L)/2)^2 */
     double alpha, rc, T; double* fugacity;
     double translation_step, rotation_step, p_translation, p_rotation, p_swap;
     int kmax[3], nk; int *kx, *ky, *kz; double *ksq_mag, *form, *W;
@@ -154,6 +155,12 @@ static void precompute_kvectors(orc_t* o) {
                     if (pass == 1) {
                         double v[3] = {(double)kx * (TWOPI * (1.0 / o->L[0])), (double)ky * (TWOPI * (1.0 / o->L[1])),
                                        (double)kz * (TWOPI * (1.0 / o->L[2]))};
+                        if (o->tri) { /* k = 2 pi (a b c)^-T n for a = (lx,0,0), b = (xy,ly,0), c = (xz,yz,lz) */
+                            const double gx = (double)kx * (1.0 / o->L[0]);
+                            const double gy = ((double)ky - o->tilt[0] * gx) * (1.0 / o->L[1]);
+                            const double gz = ((double)kz - o->tilt[1] * gx - o->tilt[2] * gy) * (1.0 / o->L[2]);
+                            v[0] = TWOPI * gx; v[1] = TWOPI * gy; v[2] = TWOPI * gz;
+                        }
                         o->kx[n] = kx; o->ky[n] = ky; o->kz[n] = kz;
                         o->ksq_mag[n] = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
                         o->form[n] = (kx == 0) ? 1.0 : 2.0;
@@ -231,6 +238,9 @@ orc_t* orc_create(const mmc_desc* d) {
     o->epsilon = malloc(nt2 * sizeof(double)); memcpy(o->epsilon, d->epsilon, nt2 * sizeof(double));
     for (int k = 0; k < 3; k++) { o->lo[k] = d->box_lo[k]; o->L[k] = d->box_len[k]; o->kmax[k] = d->kmax[k]; }
     o->volume = o->L[0] * o->L[1] * o->L[2];
+    for (int k = 0; k < 3; k++) o->tilt[k] = d->tilt[k];
+    o->tri = o->tilt[0] != 0.0 || o->tilt[1] != 0.0 || o->tilt[2] != 0.0;
+    { double m = fmin(o->L[0], fmin(o->L[1], o->L[2])); o->half_min2 = 0.25 * m * m; }
     o->alpha = d->alpha; o->rc = d->cutoff; o->T = d->temperature;
     o->translation_step = d->translation_step; o->rotation_step = d->rotation_step;
     o->p_translation = d->p_translation; o->p_rotation = d->p_rotation; o->p_swap = d->p_swap;
@@ -331,11 +341,54 @@ void orc_get_counters(orc_t* o, mmc_counters* c) { *c = o->cnt; }
 
 /* ---------------- geometry ---------------------------------------------------------------------- */
 
-/* ComputeDistance geometry_utils.f90:359-394 (orthorhombic branch; triclinic is out of scope, Q8) */
+/* Triclinic nearest image of a separation (ComputeDistance's triclinic branch, geometry_utils.f90:397-411, with the
+ * lattice vectors a = (lx,0,0), b = (xy,ly,0), c = (xz,yz,lz) as the shifts - the reference's own shifts are the columns
+ * of a matrix whose ROWS are a, b, c: Q8).  The cascade z -> y -> x lands in the brick [-l/2, l/2]^3, a fundamental
+ * domain of the lattice; a brick point shorter than half the shortest edge is the nearest image, any other one gets
+ * the reference's 27-image search around it.  Same arithmetic as min_image_tri in csrc/common.cuh. */
+static void min_image_tri(const orc_t* o, double* d) {
+    const double big = 6755399441055744.0; /* 1.5 * 2^52: fma(x, 1/l, big) - big = x/l rounded to an integer */
+    double n = fma(d[2], 1.0 / o->L[2], big) - big;
+    d[2] = fma(-n, o->L[2], d[2]); d[1] = fma(-n, o->tilt[2], d[1]); d[0] = fma(-n, o->tilt[1], d[0]);
+    n = fma(d[1], 1.0 / o->L[1], big) - big;
+    d[1] = fma(-n, o->L[1], d[1]); d[0] = fma(-n, o->tilt[0], d[0]);
+    n = fma(d[0], 1.0 / o->L[0], big) - big;
+    d[0] = fma(-n, o->L[0], d[0]);
+    double best = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+    if (best < o->half_min2) return;
+    const double x0 = d[0], y0 = d[1], z0 = d[2];
+    for (int sa = -1; sa <= 1; sa++)
+        for (int sb = -1; sb <= 1; sb++)
+            for (int sc = -1; sc <= 1; sc++) {
+                const double x = x0 + sa * o->L[0] + sb * o->tilt[0] + sc * o->tilt[1];
+                const double y = y0 + sb * o->L[1] + sc * o->tilt[2];
+                const double z = z0 + sc * o->L[2];
+                const double r2 = x * x + y * y + z * z;
+                if (r2 < best) { best = r2; d[0] = x; d[1] = y; d[2] = z; }
+            }
+}
+/* fractional coordinates s = (a b c)^-1 p of a triclinic cell (back substitution) */
+static void frac_tri(const orc_t* o, const double* p, double* s) {
+    s[2] = (1.0 / o->L[2]) * p[2];
+    s[1] = (1.0 / o->L[1]) * (p[1] - o->tilt[2] * s[2]);
+    s[0] = (1.0 / o->L[0]) * (p[0] - o->tilt[0] * s[1] - o->tilt[1] * s[2]);
+}
+static void cart_tri(const orc_t* o, const double* s, double* p) {
+    p[0] = o->L[0] * s[0] + o->tilt[0] * s[1] + o->tilt[1] * s[2];
+    p[1] = o->L[1] * s[1] + o->tilt[2] * s[2];
+    p[2] = o->L[2] * s[2];
+}
+
+/* ComputeDistance geometry_utils.f90:359-411 */
 static double compute_distance(const orc_t* o, int r1, int m1, int a1, int r2, int m2, int a2) {
     double delta[3], s = 0.0;
     const double* c1 = o->com[r1] + 3 * m1; const double* o1 = o->off[r1] + ((size_t)m1 * o->natoms[r1] + a1) * 3;
     const double* c2 = o->com[r2] + 3 * m2; const double* o2 = o->off[r2] + ((size_t)m2 * o->natoms[r2] + a2) * 3;
+    if (o->tri) {
+        for (int d = 0; d < 3; d++) delta[d] = (c2[d] + o2[d]) - (c1[d] + o1[d]);
+        min_image_tri(o, delta);
+        return sqrt(delta[0] * delta[0] + delta[1] * delta[1] + delta[2] * delta[2]);
+    }
     for (int d = 0; d < 3; d++) {
         delta[d] = (c2[d] + o2[d]) - (c1[d] + o1[d]);
         delta[d] = f_modulo(delta[d] + 0.5 * o->L[d], o->L[d]) - 0.5 * o->L[d];
@@ -344,8 +397,16 @@ static double compute_distance(const orc_t* o, int r1, int m1, int a1, int r2, i
     return sqrt(s);
 }
 
-/* ApplyPBC geometry_utils.f90:167-196 (non-triclinic branch) */
+/* ApplyPBC geometry_utils.f90:167-219; triclinic: s = (a b c)^-1 (r - r0), s mod 1, r = r0 + (a b c) s */
 static void apply_pbc(const orc_t* o, double* pos) {
+    if (o->tri) {
+        double rel[3] = {pos[0] - o->lo[0], pos[1] - o->lo[1], pos[2] - o->lo[2]}, s[3];
+        frac_tri(o, rel, s);
+        for (int d = 0; d < 3; d++) { s[d] -= floor(s[d]); if (s[d] >= 1.0) s[d] = 0.0; }
+        cart_tri(o, s, rel);
+        for (int d = 0; d < 3; d++) pos[d] = o->lo[d] + rel[d];
+        return;
+    }
     for (int d = 0; d < 3; d++) pos[d] = o->lo[d] + f_modulo(pos[d] - o->lo[d], o->L[d]);
 }
 
@@ -466,6 +527,7 @@ void orc_single_mol_fourier(orc_t* o, int r, int m) {
             pos[d] = o->com[r][3 * m + d] + o->off[r][((size_t)m * o->natoms[r] + a) * 3 + d];
             th[d] = TWOPI * ((1.0 / o->L[d]) * pos[d]);
         }
+        if (o->tri) { double s[3]; frac_tri(o, pos, s); for (int d = 0; d < 3; d++) th[d] = TWOPI * s[d]; }
         phase_factors_1d(&PH(o, px, 0, r, m, a, 0), th[0], o->kmax[0]);
         phase_factors_1d(&PH(o, py, 1, r, m, a, 0), th[1], o->kmax[1]);
         phase_factors_1d(&PH(o, pz, 2, r, m, a, 0), th[2], o->kmax[2]);
@@ -715,7 +777,10 @@ static int create_molecule(orc_t* o, int r, int m, mmc_move_record* rec) {
     orc_compute_old_energy(o, r, m, old, 1, 0);
     o->count[r]++;
     orc_save_fourier(o, r, m);
-    for (int d = 0; d < 3; d++) { double t = rand_uniform(o); o->com[r][3 * m + d] = o->lo[d] + o->L[d] * t; } /* :180-182 (diagonal matrix) */
+    { double u[3], p[3];                                               /* :180-182: bounds(:,1) + matmul(matrix, u) */
+      for (int d = 0; d < 3; d++) u[d] = rand_uniform(o);
+      if (o->tri) { cart_tri(o, u, p); for (int d = 0; d < 3; d++) o->com[r][3 * m + d] = o->lo[d] + p[d]; }
+      else for (int d = 0; d < 3; d++) o->com[r][3 * m + d] = o->lo[d] + o->L[d] * u[d]; }
     int rsv = -1;
     if (o->has_reservoir) { /* :185-193: geometry of a randomly drawn reservoir molecule, no rotation */
         rsv = (int)(rand_uniform(o) * o->rsv_count[r]);
