@@ -42,6 +42,9 @@ struct DevConst {
     int type[MMC_MAX_RES][MMC_MAX_MOL_ATOMS];  // 0-based atom types
     double self_e[MMC_MAX_RES];                // ComputeEwaldSelfInteractionSingleMol per residue (K)
     double lo[3], L[3], invL[3], volume;
+    // triclinic cell a = (L0,0,0), b = (xy,L1,0), c = (xz,yz,L2): tilt = {xy, xz, yz}; tri = any tilt non-zero;
+    // half_min2 = (min(L)/2)^2: a brick image shorter than that is the nearest image
+    double tilt[3], half_min2; int tri;
     double alpha, rc, coul_const, recip_const;  // coul_const = EPS0_INV_eVA/KB_eVK ; recip_const = coul_const*2pi/V
     double p_translation, p_rotation, p_swap;
     // pointers
@@ -225,6 +228,57 @@ __device__ __forceinline__ double min_image_fast(double d, double L, double invL
     const double big = 6755399441055744.0;
     const double n = fma(d, invL, big) - big;
     return fma(-n, L, d);
+}
+
+// Triclinic nearest image of a separation (ComputeDistance's triclinic branch, geometry_utils.f90:397-411, with the lattice
+// vectors a, b, c as the shifts).  The cascade z -> y -> x lands in the brick [-l/2, l/2]^3, a fundamental domain of the
+// lattice; a brick point shorter than half the shortest edge IS the nearest image, any other one gets the reference's
+// 27-image search around it.
+__device__ __forceinline__ void min_image_tri_brick(const DevConst& dc, double& dx, double& dy, double& dz) {
+    const double big = 6755399441055744.0;
+    double n = fma(dz, dc.invL[2], big) - big;
+    dz = fma(-n, dc.L[2], dz); dy = fma(-n, dc.tilt[2], dy); dx = fma(-n, dc.tilt[1], dx);
+    n = fma(dy, dc.invL[1], big) - big;
+    dy = fma(-n, dc.L[1], dy); dx = fma(-n, dc.tilt[0], dx);
+    n = fma(dx, dc.invL[0], big) - big;
+    dx = fma(-n, dc.L[0], dx);
+}
+// out of line and fed plain values: a reference to the kernel-parameter DevConst here would force a local copy of it
+__device__ __noinline__ double3 min_image_tri_search(double lx, double ly, double lz, double xy, double xz, double yz,
+                                                     double x0, double y0, double z0) {
+    double3 b = make_double3(x0, y0, z0);
+    double best = x0 * x0 + y0 * y0 + z0 * z0;
+    for (int sa = -1; sa <= 1; sa++)
+        for (int sb = -1; sb <= 1; sb++)
+            for (int sc = -1; sc <= 1; sc++) {
+                const double x = x0 + sa * lx + sb * xy + sc * xz;
+                const double y = y0 + sb * ly + sc * yz;
+                const double z = z0 + sc * lz;
+                const double r2 = x * x + y * y + z * z;
+                if (r2 < best) { best = r2; b = make_double3(x, y, z); }
+            }
+    return b;
+}
+__device__ __forceinline__ void min_image_tri(const DevConst& dc, double& dx, double& dy, double& dz) {
+    min_image_tri_brick(dc, dx, dy, dz);
+    if (dx * dx + dy * dy + dz * dz >= dc.half_min2) {
+        const double3 b = min_image_tri_search(dc.L[0], dc.L[1], dc.L[2], dc.tilt[0], dc.tilt[1], dc.tilt[2], dx, dy, dz);
+        dx = b.x; dy = b.y; dz = b.z;
+    }
+}
+// separation under the cell's periodicity, exact form (ComputeDistance geometry_utils.f90:385-411)
+__device__ __forceinline__ void min_image3(const DevConst& dc, double& dx, double& dy, double& dz) {
+    if (dc.tri) { min_image_tri(dc, dx, dy, dz); return; }
+    dx = min_image(dx, dc.L[0], dc.invL[0]); dy = min_image(dy, dc.L[1], dc.invL[1]); dz = min_image(dz, dc.L[2], dc.invL[2]);
+}
+// coordinate `ax` of (a b c)^-1 p: the argument of ComputeAtomPhase (ewald_phase.f90:41-63) is 2 pi times this
+__device__ __forceinline__ double frac_coord(const DevConst& dc, const double* p, int ax) {
+    if (!dc.tri) return dc.invL[ax] * p[ax];
+    const double sz = dc.invL[2] * p[2];
+    if (ax == 2) return sz;
+    const double sy = dc.invL[1] * (p[1] - dc.tilt[2] * sz);
+    if (ax == 1) return sy;
+    return dc.invL[0] * (p[0] - dc.tilt[0] * sy - dc.tilt[1] * sz);
 }
 
 // LookupTabulated tabulated_utils.f90:87-113

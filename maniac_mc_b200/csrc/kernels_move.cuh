@@ -149,6 +149,14 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             const double* com = g_com(dc, cs, c, r, m);
             const double step = cs.tstep[c];
             double u[3]; for (int d = 0; d < 3; d++) u[d] = rng.next() - 0.5;
+            if (dc.tri) {   // ApplyPBC, triclinic branch (geometry_utils.f90:198-217): s = (a b c)^-1 (r - r0), s mod 1, back
+                double rel[3], sf[3];
+                for (int d = 0; d < 3; d++) rel[d] = (com[d] + u[d] * step) - dc.lo[d];
+                for (int d = 2; d >= 0; d--) { sf[d] = frac_coord(dc, rel, d); sf[d] -= floor(sf[d]); if (sf[d] >= 1.0) sf[d] = 0.0; }
+                com_new[0] = dc.lo[0] + (dc.L[0] * sf[0] + dc.tilt[0] * sf[1] + dc.tilt[1] * sf[2]);
+                com_new[1] = dc.lo[1] + (dc.L[1] * sf[1] + dc.tilt[2] * sf[2]);
+                com_new[2] = dc.lo[2] + dc.L[2] * sf[2];
+            } else
             for (int d = 0; d < 3; d++) {
                 double x = com[d] + u[d] * step;
                 com_new[d] = dc.lo[d] + f_modulo(x - dc.lo[d], dc.L[d], dc.invL[d]);  // ApplyPBC
@@ -199,6 +207,12 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             if (m >= dc.cap[r]) { t.error = 1; }  // CheckMoleculeIndex -> AbortRun in the reference
             else {
                 ctr.trial_creations++;
+                if (dc.tri) {   // bounds(:,1) + matmul(matrix, u) with the cell vectors as columns (create_molecule.f90:180-182)
+                    double uu[3]; for (int d = 0; d < 3; d++) uu[d] = rng.next();
+                    com_new[0] = dc.lo[0] + (dc.L[0] * uu[0] + dc.tilt[0] * uu[1] + dc.tilt[1] * uu[2]);
+                    com_new[1] = dc.lo[1] + (dc.L[1] * uu[1] + dc.tilt[2] * uu[2]);
+                    com_new[2] = dc.lo[2] + dc.L[2] * uu[2];
+                } else
                 for (int d = 0; d < 3; d++) com_new[d] = dc.lo[d] + dc.L[d] * rng.next();
                 int rsv = -1;
                 if (dc.has_reservoir) {  // InsertAndOrientMolecule create_molecule.f90:185-193: a random reservoir molecule's geometry, no rotation
@@ -231,9 +245,8 @@ __device__ inline double intra_energy(const DevConst& dc, int nat, const double*
     double e = 0.0;
     for (int a1 = 0; a1 < nat - 1; a1++)
         for (int a2 = a1 + 1; a2 < nat; a2++) {
-            const double dx = min_image(p[a2][0] - p[a1][0], dc.L[0], dc.invL[0]);
-            const double dy = min_image(p[a2][1] - p[a1][1], dc.L[1], dc.invL[1]);
-            const double dz = min_image(p[a2][2] - p[a1][2], dc.L[2], dc.invL[2]);
+            double dx = p[a2][0] - p[a1][0], dy = p[a2][1] - p[a1][1], dz = p[a2][2] - p[a1][2];
+            min_image3(dc, dx, dy, dz);
             const double r = sqrt(dx * dx + dy * dy + dz * dz);
             if (r > MMC_ERR) e += q[a1] * q[a2] * (erfc(dc.alpha * r) - 1.0) / r;
         }

@@ -170,8 +170,7 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
         if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
         else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
         else { j -= s.nx + s.ny; ax = 2; k = j; dst = s.Z + j * s.zs + term; }
-        const double pos = plus ? t.p_plus[a][ax] : t.p_old[a][ax];
-        const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
+        const double theta = MMC_TWOPI * frac_coord(dc, plus ? t.p_plus[a] : t.p_old[a], ax);
         double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
         if (k < 0) sn = -sn;
         if (ax == 2) { const double q = plus ? t.q2[a] : -t.q[a]; co *= q; sn *= q; }
@@ -185,13 +184,16 @@ struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, s
 
 // one (moved atom, other atom) pair at one geometry; SHIFT: the other atom was already moved to the periodic
 // image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
-template <bool SHIFT>
-__device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gtab, double dx, double dy, double dz,
+template <bool SHIFT, bool TRI>
+__device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc, const double* s_gtab, double dx, double dy, double dz,
                                          double qq, bool charged, double2 lj, double& e_lj, double& e_c, unsigned& n_in) {
     if (!SHIFT) {
-        dx = min_image_fast(dx, pc.Lx, pc.iLx);
-        dy = min_image_fast(dy, pc.Ly, pc.iLy);
-        dz = min_image_fast(dz, pc.Lz, pc.iLz);
+        if (TRI) min_image_tri(dc, dx, dy, dz);
+        else {
+            dx = min_image_fast(dx, pc.Lx, pc.iLx);
+            dy = min_image_fast(dy, pc.Ly, pc.iLy);
+            dz = min_image_fast(dz, pc.Lz, pc.iLz);
+        }
     }
     const double r2 = fma(dx, dx, fma(dy, dy, dz * dz));
     if (r2 < pc.reach2) {
@@ -211,18 +213,25 @@ __device__ __forceinline__ void pair_one(const PairConst& pc, const double* s_gt
 }
 
 // one "other" atom against every atom of the moved molecule, old and/or new geometry
-template <bool OLD, bool NEW, bool SHIFT>
-__device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
+// TRI: tilted cell; the OLD / NEW sets are then also masked at run time (one instantiation serves every move type)
+template <bool OLD, bool NEW, bool SHIFT, bool TRI>
+__device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
                                           double qj, int tj, double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
     if (SHIFT) {
         double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
-        const double big = 6755399441055744.0;
-        const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
-        xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
-        dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
+        if (TRI) {   // the image inside the brick around the molecule's centre: exact for every pair within reach (shift_ok)
+            min_image_tri_brick(dc, dx, dy, dz);
+            xj = m.cc[0] + dx; yj = m.cc[1] + dy; zj = m.cc[2] + dz;
+        } else {
+            const double big = 6755399441055744.0;
+            const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
+            xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
+            dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
+        }
         if (fma(dx, dx, fma(dy, dy, dz * dz)) > m.cc[3]) return;  // beyond reach of every atom of the molecule
     }
+    const bool use_old = OLD && (!TRI || m.do_old), use_new = NEW && (!TRI || m.do_new);
     const bool qj_ok = fabs(qj) >= MMC_ERR;
     const int nat = m.nat;
 #pragma unroll 2
@@ -233,9 +242,9 @@ __device__ __forceinline__ void pair_atom(const PairConst& pc, const SweepCtx& s
         const double2 lj = s.lj[a * ntypes + tj];
         if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
-        cnt[0] += (OLD ? 1u : 0u) + (NEW ? 1u : 0u);
-        if (OLD) pair_one<SHIFT>(pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt[1]);
-        if (NEW) pair_one<SHIFT>(pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt[1]);
+        cnt[0] += (use_old ? 1u : 0u) + (use_new ? 1u : 0u);
+        if (use_old) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt[1]);
+        if (use_new) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt[1]);
     }
 }
 
@@ -244,6 +253,20 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
     const double* b = dc.tbox + t; const size_t nt = (size_t)dc.n_tiles;
     const double bx = b[0], by = b[nt], bz = b[2 * nt], hx = b[3 * nt], hy = b[4 * nt], hz = b[5 * nt];
     bool hit = false;
+    if (dc.tri) {
+        // tilted cell: the z image fixes the y shift and the y image the x shift, so the per-axis bound holds only while
+        // the image along each axis is unambiguous (R + h < l/2); otherwise the tile is kept
+        for (int g = 0; g < 2; g++) {
+            if (g == 0 ? !use_old : !use_new) continue;
+            const double R = m.cen[g][3];
+            if (R + hx >= 0.5 * dc.L[0] || R + hy >= 0.5 * dc.L[1] || R + hz >= 0.5 * dc.L[2]) return true;
+            double dx = m.cen[g][0] - bx, dy = m.cen[g][1] - by, dz = m.cen[g][2] - bz;
+            min_image_tri_brick(dc, dx, dy, dz);
+            dx = fmax(0.0, fabs(dx) - hx); dy = fmax(0.0, fabs(dy) - hy); dz = fmax(0.0, fabs(dz) - hz);
+            hit = hit || (dx * dx + dy * dy + dz * dz <= R * R);
+        }
+        return hit;
+    }
 #pragma unroll
     for (int g = 0; g < 2; g++) {
         if (g == 0 ? !use_old : !use_new) continue;
@@ -260,7 +283,7 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
 // Real-space phase of one trial.  Work items = framework tiles in reach (ordered compaction of the cull
 // result, so the item -> warp assignment and hence the summation order is deterministic) followed by tiles
 // of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
-template <int NT, bool OLD, bool NEW, bool SHIFT>
+template <int NT, bool OLD, bool NEW, bool SHIFT, bool TRI>
 __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                     double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
@@ -274,7 +297,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
         const int nwords = (n + 31) >> 5;
         for (int i0 = warp * 32; i0 < n; i0 += NT) {
             const int i = i0 + lane;
-            const bool hit = i < n && (!cull || tile_in_reach(dc, m, base + i, OLD, NEW));
+            const bool hit = i < n && (!cull || tile_in_reach(dc, m, base + i, OLD && (!TRI || m.do_old), NEW && (!TRI || m.do_new)));
             const unsigned b = __ballot_sync(0xffffffffu, hit);
             if (lane == 0) s.mask[i0 >> 5] = b;
         }
@@ -301,7 +324,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
         const int nlist = m.nlist;
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
             const int j = (base + (int)s.list[it]) * TILE + lane;
-            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc, cnt);
+            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc, cnt);
         }
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
@@ -317,7 +340,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
             if (i < n_at) {
                 const int mol = i / na, a = i - mol * na;
                 if (!(m.excl && r == m.res && mol == m.mol))
-                    pair_atom<OLD, NEW, SHIFT>(pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
+                    pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
                                         dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc, cnt);
             }
         }
@@ -331,9 +354,14 @@ __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int 
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
     const bool sh = m.shift_ok && dc.reach2 < 1e300;
-    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
-    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
-    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, false, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    if (dc.tri) {   // tilted cell: one instantiation per shift mode, OLD / NEW masked at run time
+        if (sh) pair_phase_t<NT, true, true, true, true>(dc, cs, c, s, part, n_parts, acc, cnt);
+        else pair_phase_t<NT, true, true, false, true>(dc, cs, c, s, part, n_parts, acc, cnt);
+        return;
+    }
+    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, false, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, false, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -371,7 +399,7 @@ __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& 
         const bool two = kz != 0;
         const double2 ap = A[kpl];
         const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
-        const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz
+        const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz in an orthorhombic cell
         const double2* pt = xy + (ix * ny + iy - ra) * zs;
         const double2* zt = s.Z + kz * zs;
         // sum_t P_t Z_t and sum_t P_t conj(Z_t) from the four real product sums
@@ -397,8 +425,9 @@ __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& 
         if (two) {
             const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
             An[kmi] = bm;
-            acc[0] = fma(w, fma(am.x, am.x, am.y * am.y), acc[0]);
-            acc[1] = fma(w, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
+            const double wm = dc.tri ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
+            acc[0] = fma(wm, fma(am.x, am.x, am.y * am.y), acc[0]);
+            acc[1] = fma(wm, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
         }
     }
 }
@@ -460,10 +489,11 @@ __device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int
     {
         double pa[4] = {0, 0, 0, 0};
         unsigned cnt[2] = {0u, 0u};
-        if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
-        if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
-            __syncthreads();
-            stage_molecule(dc, cs, c, s, 2);
+        // a swap sweeps twice: the removed molecule, then the inserted one (different atom set, removed slot still excluded).
+        // ONE call site: a second one makes the compiler call pair_phase_t out of line, with a local copy of DevConst
+#pragma unroll 1
+        for (int pass = 0; pass < (swap ? 2 : 1); pass++) {
+            if (pass) { __syncthreads(); stage_molecule(dc, cs, c, s, 2); }
             if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
         }
         const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt[0]), w1 = __reduce_add_sync(0xffffffffu, cnt[1]);

@@ -84,9 +84,8 @@ __global__ void __launch_bounds__(SYS_THREADS) k_sys_pair(DevConst dc, SysScratc
         for (int jj = 0; jj < SYS_THREADS; jj++) {
             const int j = bj * SYS_THREADS + jj;
             if (j <= i || smol[jj] < 0 || smol[jj] == mi) continue;
-            const double dx = min_image(sx[jj] - xi, dc.L[0], dc.invL[0]);
-            const double dy = min_image(sy[jj] - yi, dc.L[1], dc.invL[1]);
-            const double dz = min_image(sz[jj] - zi, dc.L[2], dc.invL[2]);
+            double dx = sx[jj] - xi, dy = sy[jj] - yi, dz = sz[jj] - zi;
+            min_image3(dc, dx, dy, dz);
             const double r = sqrt(dx * dx + dy * dy + dz * dz);
             sys_pair_eval(dc, r, dc.lj[ti * dc.ntypes + st[jj]], qi, sq[jj], acc[0], acc[1]);
         }
@@ -124,8 +123,8 @@ __global__ void __launch_bounds__(RECIP_THREADS) k_sys_sk(DevConst dc, SysScratc
             const int j = ch * chunk + a;
             double2 v = make_double2(0.0, 0.0);
             if (j < ss.n && k <= dc.kmax[ax] && ss.mol[j] >= 0) {
-                const double pos = ax == 0 ? ss.x[j] : ax == 1 ? ss.y[j] : ss.z[j];
-                const double theta = MMC_TWOPI * (dc.invL[ax] * pos);
+                const double pos[3] = {ss.x[j], ss.y[j], ss.z[j]};
+                const double theta = MMC_TWOPI * frac_coord(dc, pos, ax);
                 double s, co; sincos((double)k * theta, &s, &co);
                 v = make_double2(co, s);
             }
@@ -186,9 +185,8 @@ __global__ void __launch_bounds__(SYS_THREADS) k_sys_self_intra(DevConst dc, Cha
             double e = 0.0;
             for (int a1 = 0; a1 < nat - 1; a1++)
                 for (int a2 = a1 + 1; a2 < nat; a2++) {
-                    const double dx = min_image(p[a2][0] - p[a1][0], dc.L[0], dc.invL[0]);
-                    const double dy = min_image(p[a2][1] - p[a1][1], dc.L[1], dc.invL[1]);
-                    const double dz = min_image(p[a2][2] - p[a1][2], dc.L[2], dc.invL[2]);
+                    double dx = p[a2][0] - p[a1][0], dy = p[a2][1] - p[a1][1], dz = p[a2][2] - p[a1][2];
+                    min_image3(dc, dx, dy, dz);
                     const double rr = sqrt(dx * dx + dy * dy + dz * dz);
                     if (rr > MMC_ERR) e += dc.q[r][a1] * dc.q[r][a2] * (erfc(dc.alpha * rr) - 1.0) / rr;
                 }
@@ -209,8 +207,14 @@ __global__ void k_init_weights(DevConst dc, double* fw, double* w_only) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= dc.nk) return;
     const int4 kv = dc.kvec[i];
-    const double vx = (double)kv.x * (MMC_TWOPI * dc.invL[0]), vy = (double)kv.y * (MMC_TWOPI * dc.invL[1]),
-                 vz = (double)kv.z * (MMC_TWOPI * dc.invL[2]);
+    double vx = (double)kv.x * (MMC_TWOPI * dc.invL[0]), vy = (double)kv.y * (MMC_TWOPI * dc.invL[1]),
+           vz = (double)kv.z * (MMC_TWOPI * dc.invL[2]);
+    if (dc.tri) {   // k = 2 pi (a b c)^-T n
+        const double gx = (double)kv.x * dc.invL[0];
+        const double gy = ((double)kv.y - dc.tilt[0] * gx) * dc.invL[1];
+        const double gz = ((double)kv.z - dc.tilt[1] * gx - dc.tilt[2] * gy) * dc.invL[2];
+        vx = MMC_TWOPI * gx; vy = MMC_TWOPI * gy; vz = MMC_TWOPI * gz;
+    }
     const double k2 = vx * vx + vy * vy + vz * vz;
     const double w = exp(-k2 / (4.0 * (dc.alpha * dc.alpha))) / k2;
     w_only[i] = w;

@@ -239,10 +239,13 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     const uint32_t ncell = 1u << bits;
     std::vector<double> wx(n), wy(n), wz(n);  // wrapped into [lo, lo + L)
     std::vector<uint32_t> code(n); std::vector<int> order(n);
-    auto wrap = [&](double x, int ax) { double u = (x - dc.lo[ax]) / dc.L[ax]; u -= std::floor(u); if (u >= 1.0) u = 0.0; return u; };
+    auto unit = [&](double u) { u -= std::floor(u); if (u >= 1.0) u = 0.0; return u; };
     for (size_t j = 0; j < n; j++) {
-        const double ux = wrap(fx[j], 0), uy = wrap(fy[j], 1), uz = wrap(fz[j], 2);
-        wx[j] = dc.lo[0] + ux * dc.L[0]; wy[j] = dc.lo[1] + uy * dc.L[1]; wz[j] = dc.lo[2] + uz * dc.L[2];
+        // fractional coordinates of the (possibly tilted) cell, wrapped into [0, 1), and the lattice-equivalent point
+        const double rz = fz[j] - dc.lo[2], ry = fy[j] - dc.lo[1], rx = fx[j] - dc.lo[0];
+        const double fz_ = rz / dc.L[2], fy_ = (ry - dc.tilt[2] * fz_) / dc.L[1], fx_ = (rx - dc.tilt[0] * fy_ - dc.tilt[1] * fz_) / dc.L[0];
+        const double ux = unit(fx_), uy = unit(fy_), uz = unit(fz_);
+        wx[j] = dc.lo[0] + ux * dc.L[0] + uy * dc.tilt[0] + uz * dc.tilt[1]; wy[j] = dc.lo[1] + uy * dc.L[1] + uz * dc.tilt[2]; wz[j] = dc.lo[2] + uz * dc.L[2];
         auto cell = [&](double u) { uint32_t c = (uint32_t)(u * ncell); return c >= ncell ? ncell - 1 : c; };
         code[j] = morton3(cell(ux), cell(uy), cell(uz));
     }
@@ -392,6 +395,9 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
         if (d->kmax[k] > kmaxmax) kmaxmax = d->kmax[k];
     }
     dc.kstride = kmaxmax + 1;
+    for (int k = 0; k < 3; k++) dc.tilt[k] = d->tilt[k];
+    dc.tri = d->tilt[0] != 0.0 || d->tilt[1] != 0.0 || d->tilt[2] != 0.0;
+    { const double m = std::fmin(dc.L[0], std::fmin(dc.L[1], dc.L[2])); dc.half_min2 = 0.25 * m * m; }
 #define BAIL(...) do { fail(__VA_ARGS__); std::string keep_ = g_err; mmc_destroy(h); g_err = keep_; return 1; } while (0)
 #define CKB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) BAIL("%s failed: %s", #call, cudaGetErrorString(e_)); } while (0)
     // residues

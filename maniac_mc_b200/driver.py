@@ -140,15 +140,36 @@ class StrictDriver:
         rec["old_e"], rec["new_e"] = old, new
         return rec
 
+    # tilted cell a = (lx,0,0), b = (xy,ly,0), c = (xz,yz,lz): same arithmetic as the library and the CPU restatement
+    @property
+    def tri(self):
+        return bool(np.any(np.asarray(self.sys.tilt) != 0.0))
+
+    def frac(self, p):
+        L, (xy, xz, yz) = self.sys.box_len, self.sys.tilt
+        sz = (1.0 / L[2]) * p[2]
+        sy = (1.0 / L[1]) * (p[1] - yz * sz)
+        sx = (1.0 / L[0]) * (p[0] - xy * sy - xz * sz)
+        return [sx, sy, sz]
+
+    def cart(self, s):
+        L, (xy, xz, yz) = self.sys.box_len, self.sys.tilt
+        return np.array([L[0] * s[0] + xy * s[1] + xz * s[2], L[1] * s[1] + yz * s[2], L[2] * s[2]])
+
     def Translation(self, rng, r, m):
         if m < 0:
             return None
         self.counter["trial_translations"] += 1
         u = [rng() - 0.5 for _ in range(3)]
         com = self.com[r][m].copy()
-        for d in range(3):
-            x = com[d] + u[d] * self.translation_step
-            com[d] = self.sys.box_lo[d] + f_modulo(x - self.sys.box_lo[d], self.sys.box_len[d])  # ApplyPBC
+        if self.tri:      # ApplyPBC, triclinic branch: s = (a b c)^-1 (r - r0), s mod 1, r = r0 + (a b c) s
+            s = self.frac(np.array([com[d] + u[d] * self.translation_step for d in range(3)]) - self.sys.box_lo)
+            s = [v - math.floor(v) for v in s]
+            com = self.sys.box_lo + self.cart([0.0 if v >= 1.0 else v for v in s])
+        else:
+            for d in range(3):
+                x = com[d] + u[d] * self.translation_step
+                com[d] = self.sys.box_lo[d] + f_modulo(x - self.sys.box_lo[d], self.sys.box_len[d])  # ApplyPBC
         old, new = self.gpu.trial_energy(MMC_TRANSLATION, r, m, com, self.off[r][m], chain=self.chain)
         p = self.mc_acceptance_probability(old, new, r, MMC_TRANSLATION)
         acc = rng() <= p
@@ -175,7 +196,10 @@ class StrictDriver:
             raise RuntimeError("molecule index exceeds NB_MAX_MOLECULE")  # CheckMoleculeIndex
         self.counter["trial_creations"] += 1
         self.count[r] += 1
-        com = np.array([self.sys.box_lo[d] + self.sys.box_len[d] * rng() for d in range(3)])
+        if self.tri:      # bounds(:,1) + matmul(matrix, u), cell vectors as columns
+            com = self.sys.box_lo + self.cart([rng() for _ in range(3)])
+        else:
+            com = np.array([self.sys.box_lo[d] + self.sys.box_len[d] * rng() for d in range(3)])
         rsv = -1
         if self.has_reservoir:   # InsertAndOrientMolecule create_molecule.f90:185-193
             rsv = int(rng() * len(self.rsv[r])); off = self.rsv[r][rsv].copy()

@@ -713,3 +713,79 @@ def test_isotherm_run_blocks_equals_blockwise_sync_and_writes_per_chain_files(tm
     num = (d / f"number_res{b.res + 1}.dat").read_text().splitlines()
     if len(num) == 6:                                              # a row per block: the chain was never empty
         assert abs(np.mean([int(l.split()[1]) for l in num[2:]]) - tb[1, 3, 0]) < 1e-12   # the rows ARE the table's samples
+
+
+# ---- triclinic cells (the CPU restatement is pinned physically in tests/test_triclinic_oracle.py) ----
+def tilted_dipoles(**over):
+    from test_triclinic_oracle import dipole_cell
+    s = dipole_cell((3.0, -2.0, 4.5), kmax=(8, 8, 8), alpha=0.42, n_mol=10)
+    for k, v in over.items():
+        setattr(s, k, v)
+    return s
+
+
+def tilted_framework(n_fw=6000, box=60.0, tilt=(9.0, -7.0, 12.0)):
+    """a framework big enough for the tile cull and the single-shift path (reach + molecule < L/2) in a tilted cell"""
+    s = builders.synthetic_framework(n_framework=n_fw, n_guests=40, box=box, cutoff=12.0, tol=1e-5, capacity=128)
+    s.tilt = np.array(tilt); s.init_sk = 1; s.deletion_mode = 1
+    return s
+
+
+def test_triclinic_single_point_energies():
+    for s in (tilted_dipoles(), tilted_framework()):
+        g = ManiacGPU(s); e = g.system_energy()
+        assert rel_err(e, orc.Oracle(s).system_energy()) < 1e-11
+        kv_g, kv_o = g.kvectors(), orc.Oracle(s).kvectors()
+        for a, b in zip(kv_g, kv_o):
+            np.testing.assert_allclose(a, b, rtol=1e-13)
+        g.close()
+
+
+@pytest.mark.parametrize("which", ["dipoles", "framework"])
+def test_triclinic_strict_mode_trajectory(which):
+    s = tilted_dipoles() if which == "dipoles" else tilted_framework()
+    n = 400 if which == "dipoles" else 150
+    tape = np.random.default_rng(8).random(16 * n)
+    o = orc.Oracle(s); o.system_energy(); ref = o.run(n, tape=tape)
+    g = ManiacGPU(s); drv = StrictDriver(s, g); drv.ComputeSystemEnergy()
+    rng = TapeRng(tape); got = drv.MonteCarloLoop(rng, 1, n)
+    compare_records(got, ref)
+    assert rng.pos == o.tape_used and ref["accepted"].sum() > n // 10
+    cnt, com, off, e = g.sync_to_host()
+    c2, com2, off2 = o.state()
+    assert np.array_equal(cnt, c2)
+    np.testing.assert_allclose(com, com2, atol=1e-11); np.testing.assert_allclose(off, off2, atol=1e-12)
+    assert rel_err(e, o.energy()) < TOL and rel_err(e, g.system_energy()) < 1e-9
+    np.testing.assert_allclose(g.sk(), o.sk(), atol=1e-9)
+    g.close()
+
+
+@pytest.mark.parametrize("which", ["dipoles", "framework"])
+def test_triclinic_batched_matches_oracle(which):
+    """device proposals (fractional insertion, fractional ApplyPBC) + fused chain kernel in a tilted cell"""
+    s = tilted_dipoles() if which == "dipoles" else tilted_framework()
+    n = 300 if which == "dipoles" else 120
+    g = ManiacGPU(s, n_chains=3)
+    for c in range(3):
+        g.system_energy(c)
+    recs = g.run_batch(n, seed=17, records=True)
+    for c in range(3):
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(recs[c], o.run(n, seed=17, chain=c))
+        _, _, _, tracked = g.sync_to_host(c)
+        assert rel_err(tracked, o.energy()) < TOL
+    g.close()
+
+
+def test_triclinic_cull_equals_every_pair():
+    """the tile cull + single-shift path in a tilted cell against the every-pair sweep of the same library"""
+    s = tilted_framework()
+    a = ManiacGPU(s, n_chains=2); s2 = s.copy(); s2.coulomb_xcut = -1.0; b = ManiacGPU(s2, n_chains=2)
+    for c in range(2):
+        a.system_energy(c); b.system_energy(c)
+    ra, rb = a.run_batch(150, seed=4, records=True), b.run_batch(150, seed=4, records=True)
+    for c in range(2):
+        compare_records(ra[c], rb[c], tol=1e-12)
+    wa, wb = a.pair_work(), b.pair_work()
+    assert wa[0] < 0.5 * wb[0]                     # the cull really dropped most of the framework
+    a.close(); b.close()
