@@ -16,7 +16,7 @@
 
 // phases: bit 0 = real-space sweep, bit 1 = reciprocal sweep (both for production; single-phase variants
 // exist only so bench.py can time each sweep alone on the same trials -- they do not commit)
-template <int NT, int MINB>
+template <int NT, int MINB, bool TRI>
 __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState cs, const BatchCtl* ctl, int chain0, int n_steps,
                                                         int phases) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
         }
         __syncthreads();
-        sweep_trial<NT>(dc, cs, c, s, 0, 1, phases);
+        sweep_trial<NT, TRI>(dc, cs, c, s, 0, 1, phases);
         if (threadIdx.x == 0) {
             Trial& t = cs.trial[c];
             const int kind = t.kind;

@@ -246,7 +246,10 @@ __device__ inline double intra_energy(const DevConst& dc, int nat, const double*
     for (int a1 = 0; a1 < nat - 1; a1++)
         for (int a2 = a1 + 1; a2 < nat; a2++) {
             double dx = p[a2][0] - p[a1][0], dy = p[a2][1] - p[a1][1], dz = p[a2][2] - p[a1][2];
-            min_image3(dc, dx, dy, dz);
+            if (dc.tri) min_image_tri_brick(dc, dx, dy, dz);   // sites of one molecule are closer than half the shortest cell edge:
+            else {                                             // the brick image is the nearest one, no 27-image search (and no call here)
+                dx = min_image(dx, dc.L[0], dc.invL[0]); dy = min_image(dy, dc.L[1], dc.invL[1]); dz = min_image(dz, dc.L[2], dc.invL[2]);
+            }
             const double r = sqrt(dx * dx + dy * dy + dz * dz);
             if (r > MMC_ERR) e += q[a1] * q[a2] * (erfc(dc.alpha * r) - 1.0) / r;
         }

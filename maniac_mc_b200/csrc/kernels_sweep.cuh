@@ -144,6 +144,7 @@ __device__ inline void stage_molecule(const DevConst& dc, const ChainState& cs, 
 // ComputePhaseFactors1D, ewald_phase.f90:41-109: direct cos/sin(k theta)), one row per term with the charge and the
 // sign folded into Z.  Added atoms come from the NEW set (p_plus, q2), removed atoms from the OLD set (p_old, q).
 // All threads; ends with a barrier.
+template <bool TRI>
 __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
     const Trial& t = cs.trial[c];
     MolS& m = *s.mol;
@@ -170,7 +171,8 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
         if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
         else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
         else { j -= s.nx + s.ny; ax = 2; k = j; dst = s.Z + j * s.zs + term; }
-        const double theta = MMC_TWOPI * frac_coord(dc, plus ? t.p_plus[a] : t.p_old[a], ax);
+        const double* pp = plus ? t.p_plus[a] : t.p_old[a];
+        const double theta = MMC_TWOPI * (TRI ? frac_coord(dc, pp, ax) : dc.invL[ax] * pp[ax]);
         double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
         if (k < 0) sn = -sn;
         if (ax == 2) { const double q = plus ? t.q2[a] : -t.q[a]; co *= q; sn *= q; }
@@ -249,11 +251,12 @@ __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& p
 }
 
 // can tile `t` hold an atom within reach of the moved molecule?  periodic point-to-box distance per axis
+template <bool TRI>
 __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m, int t, bool use_old, bool use_new) {
     const double* b = dc.tbox + t; const size_t nt = (size_t)dc.n_tiles;
     const double bx = b[0], by = b[nt], bz = b[2 * nt], hx = b[3 * nt], hy = b[4 * nt], hz = b[5 * nt];
     bool hit = false;
-    if (dc.tri) {
+    if (TRI) {
         // tilted cell: the z image fixes the y shift and the y image the x shift, so the per-axis bound holds only while
         // the image along each axis is unambiguous (R + h < l/2); otherwise the tile is kept
         for (int g = 0; g < 2; g++) {
@@ -297,7 +300,7 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
         const int nwords = (n + 31) >> 5;
         for (int i0 = warp * 32; i0 < n; i0 += NT) {
             const int i = i0 + lane;
-            const bool hit = i < n && (!cull || tile_in_reach(dc, m, base + i, OLD && (!TRI || m.do_old), NEW && (!TRI || m.do_new)));
+            const bool hit = i < n && (!cull || tile_in_reach<TRI>(dc, m, base + i, OLD && (!TRI || m.do_old), NEW && (!TRI || m.do_new)));
             const unsigned b = __ballot_sync(0xffffffffu, hit);
             if (lane == 0) s.mask[i0 >> 5] = b;
         }
@@ -348,13 +351,13 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
     }
 }
 
-template <int NT>
+template <int NT, bool TRI>
 __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                   double (&acc)[4], unsigned (&cnt)[2]) {
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
     const bool sh = m.shift_ok && dc.reach2 < 1e300;
-    if (dc.tri) {   // tilted cell: one instantiation per shift mode, OLD / NEW masked at run time
+    if (TRI) {   // tilted cell (kernels compiled for it): one instantiation per shift mode, OLD / NEW masked at run time
         if (sh) pair_phase_t<NT, true, true, true, true>(dc, cs, c, s, part, n_parts, acc, cnt);
         else pair_phase_t<NT, true, true, false, true>(dc, cs, c, s, part, n_parts, acc, cnt);
         return;
@@ -385,7 +388,7 @@ __device__ __forceinline__ void recip_stage_rows(const SweepCtx& s, int nterm, i
 
 // the items [i0, i1) of one staged chunk of rows.  NTERM > 0: term count known at compile time (the shared loads get
 // immediate offsets and the loop disappears); NTERM == 0: generic loop over nterm.
-template <int NT, int NTERM>
+template <int NT, int NTERM, bool TRI>
 __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& s, const double2* __restrict__ A, double2* __restrict__ An,
                                             const double2* xy, int ra, int i0, int i1, int nterm, double (&acc)[2]) {
     const int ny = s.ny, zs = s.zs;
@@ -425,14 +428,14 @@ __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& 
         if (two) {
             const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
             An[kmi] = bm;
-            const double wm = dc.tri ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
+            const double wm = TRI ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
             acc[0] = fma(wm, fma(am.x, am.x, am.y * am.y), acc[0]);
             acc[1] = fma(wm, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
         }
     }
 }
 
-template <int NT>
+template <int NT, bool TRI>
 __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                    double (&acc)[2]) {
     constexpr int RMAX = NT / 4;
@@ -463,13 +466,13 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
         const double2* xy = s.XY + buf * bufsz;
         const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
         switch (nterm) {   // 3 / 6 = rigid water insertion-deletion / move; the others cover 1..4 charged sites
-            case 1: recip_items<NT, 1>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            case 2: recip_items<NT, 2>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            case 3: recip_items<NT, 3>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            case 4: recip_items<NT, 4>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            case 6: recip_items<NT, 6>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            case 8: recip_items<NT, 8>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
-            default: recip_items<NT, 0>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 1: recip_items<NT, 1, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 2: recip_items<NT, 2, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 3: recip_items<NT, 3, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 4: recip_items<NT, 4, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 6: recip_items<NT, 6, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            case 8: recip_items<NT, 8, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            default: recip_items<NT, 0, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
         }
         __syncthreads();
         buf ^= 1;
@@ -481,20 +484,20 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
 // Result: s.mol->sums = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} of this CTA (block sums in a
 // fixed order), valid after the trailing barrier.  The real-space sums are reduced and parked in shared memory BEFORE
 // the reciprocal sweep so that its item loop does not carry them in registers (64 registers per thread at 4 CTAs/SM).
-template <int NT>
+// TRI: compiled for tilted cells (dc.tri); the orthorhombic kernels carry none of that code
+template <int NT, bool TRI>
 __device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts, int phases) {
     const bool swap = cs.trial[c].kind == MMC_SWAP;
-    stage_terms(dc, cs, c, s);
+    stage_terms<TRI>(dc, cs, c, s);
     stage_molecule(dc, cs, c, s, swap ? 1 : 0);
     {
         double pa[4] = {0, 0, 0, 0};
         unsigned cnt[2] = {0u, 0u};
-        // a swap sweeps twice: the removed molecule, then the inserted one (different atom set, removed slot still excluded).
-        // ONE call site: a second one makes the compiler call pair_phase_t out of line, with a local copy of DevConst
-#pragma unroll 1
-        for (int pass = 0; pass < (swap ? 2 : 1); pass++) {
-            if (pass) { __syncthreads(); stage_molecule(dc, cs, c, s, 2); }
-            if (phases & 1) pair_phase<NT>(dc, cs, c, s, part, n_parts, pa, cnt);
+        if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
+        if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
+            __syncthreads();
+            stage_molecule(dc, cs, c, s, 2);
+            if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
         }
         const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt[0]), w1 = __reduce_add_sync(0xffffffffu, cnt[1]);
         if ((threadIdx.x & 31) == 0 && (w0 | w1)) { atomicAdd(&s.mol->work[0], w0); atomicAdd(&s.mol->work[1], w1); }
@@ -503,7 +506,7 @@ __device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int
     }
     {
         double ra[2] = {0, 0};
-        if (phases & 2) recip_phase<NT>(dc, cs, c, s, part, n_parts, ra);
+        if (phases & 2) recip_phase<NT, TRI>(dc, cs, c, s, part, n_parts, ra);
         block_sum<2, NT>(ra, s.red);
         if (threadIdx.x == 0) { s.mol->sums[4] = ra[0]; s.mol->sums[5] = ra[1]; }
     }
@@ -534,7 +537,8 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
     sweep_load_tables(dc, s);
     pair_count_init(s);
-    sweep_trial<SWEEP_THREADS>(dc, cs, c, s, part, n_parts, 3);
+    if (dc.tri) sweep_trial<SWEEP_THREADS, true>(dc, cs, c, s, part, n_parts, 3);
+    else sweep_trial<SWEEP_THREADS, false>(dc, cs, c, s, part, n_parts, 3);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
         for (int i = 0; i < 6; i++) out[i] = s.mol->sums[i];

@@ -353,9 +353,15 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
                                                  dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
     CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
-    CK(cudaFuncSetAttribute(k_chain_run<256, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-    CK(cudaFuncSetAttribute(k_chain_run<512, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-    CK(cudaFuncSetAttribute(k_chain_run<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    if (h->dc.tri) {
+        CK(cudaFuncSetAttribute(k_chain_run<256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+        CK(cudaFuncSetAttribute(k_chain_run<512, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+        CK(cudaFuncSetAttribute(k_chain_run<1024, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    } else {
+        CK(cudaFuncSetAttribute(k_chain_run<256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+        CK(cudaFuncSetAttribute(k_chain_run<512, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+        CK(cudaFuncSetAttribute(k_chain_run<1024, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
+    }
     CK(dalloc(h, &h->cs.part, (size_t)dc.n_chains * dc.sweep_parts * 6));
     return 0;
 }
@@ -969,9 +975,14 @@ extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
 // one launch of the chain-per-CTA kernel: every chain advances n steps
 static void launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases) {
     const int C = h->dc.n_chains;
-    if (h->chain_threads == 256) k_chain_run<256, 4><<<C, 256, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
-    else if (h->chain_threads == 512) k_chain_run<512, 2><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
-    else k_chain_run<1024, 1><<<C, 1024, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    if (h->dc.tri) {   // the tilted-cell build of the same kernel
+        if (h->chain_threads == 256) k_chain_run<256, 4, true><<<C, 256, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+        else if (h->chain_threads == 512) k_chain_run<512, 2, true><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+        else k_chain_run<1024, 1, true><<<C, 1024, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    }
+    else if (h->chain_threads == 256) k_chain_run<256, 4, false><<<C, 256, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    else if (h->chain_threads == 512) k_chain_run<512, 2, false><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
+    else k_chain_run<1024, 1, false><<<C, 1024, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
     h->launches++;
 }
 static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
