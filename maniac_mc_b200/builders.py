@@ -19,6 +19,8 @@ def from_files(maniac_path, data_path, inc_path, capacity=None) -> System:
     ntypes = max(dat["ntypes"], int(atoms[:, 2].max()))
     lo, hi = dat["box_lo"], dat["box_hi"]
     L = hi - lo
+    tilt = np.asarray(dat.get("tilt", np.zeros(3)), dtype=np.float64)
+    tri = bool(np.any(tilt != 0.0))
     nres = len(inp.residues)
     max_atoms = max(r.natoms for r in inp.residues)
     natoms = np.array([r.natoms for r in inp.residues], dtype=np.int32)
@@ -43,7 +45,8 @@ def from_files(maniac_path, data_path, inc_path, capacity=None) -> System:
         if res.active:
             # RepairMolecule readers_utils.f90:258: chain of nearest-image bonds
             for k in range(1, res.natoms):
-                xyz[:, k] = xyz[:, k - 1] + readers.wrap_nearest(xyz[:, k] - xyz[:, k - 1], L)
+                dk = xyz[:, k] - xyz[:, k - 1]
+                xyz[:, k] = xyz[:, k - 1] + (readers.nearest_image_tri(dk, L, tilt) if tri else readers.wrap_nearest(dk, L))
         # TransformCoordinate data_parser.f90:1386: the mass vector is overwritten by a scalar
         # (:1421), so the "COM" is the unweighted centroid
         com0 = xyz.mean(axis=1) if res.natoms > 1 else xyz[:, 0].copy()
@@ -53,14 +56,16 @@ def from_files(maniac_path, data_path, inc_path, capacity=None) -> System:
                 com0 = com0 + 1.0 * xyz[:, k]
             com0 = com0 / float(res.natoms)
         off = xyz - com0[:, None, :]
-        com = lo + np.mod(com0 - lo, L)  # ApplyPBC geometry_utils.f90:167
+        com = readers.wrap_tri(com0, lo, L, tilt) if tri else lo + np.mod(com0 - lo, L)  # ApplyPBC geometry_utils.f90:167
         coms.append(com); offs.append(off.reshape(-1, 3))
     sigma, eps = readers.read_pair_coeffs(inc_path, ntypes)
     sigma, eps = readers.lorentz_berthelot(sigma, eps)
     cutoff = inp.real_space_cutoff
-    if (cutoff > L).any():  # AdjustRealSpaceCutoff prepare_utils.f90:141-150
-        cutoff = float(L.min()) / 2.0
-    alpha, kmax = ewald_setup(cutoff, inp.ewald_tolerance, L)
+    # box%metrics(1:3), geometry_utils.f90:124: column norms of the matrix whose rows are a, b, c (= L when not tilted)
+    metrics = np.array([math.sqrt(L[0] ** 2 + tilt[0] ** 2 + tilt[1] ** 2), math.sqrt(L[1] ** 2 + tilt[2] ** 2), L[2]]) if tri else L
+    if (cutoff > metrics).any():  # AdjustRealSpaceCutoff prepare_utils.f90:141-150
+        cutoff = float(metrics.min()) / 2.0
+    alpha, kmax = ewald_setup(cutoff, inp.ewald_tolerance, metrics)
     # ConvertFugacity prepare_utils.f90:48-75
     fug = np.array([(r.fugacity_atm * readers.ATM_TO_PA * readers.A3_TO_M3 / (readers.KB_JK * inp.temperature))
                     if r.active else r.fugacity_atm for r in inp.residues])
@@ -75,7 +80,7 @@ def from_files(maniac_path, data_path, inc_path, capacity=None) -> System:
                   fugacity=fug, kmax=kmax, translation_step=inp.translation_step,
                   rotation_step=inp.rotation_step_angle, p_translation=inp.p_translation,
                   p_rotation=inp.p_rotation, p_swap=inp.p_swap, names=[r.name for r in inp.residues],
-                  ewald_tolerance=inp.ewald_tolerance)
+                  ewald_tolerance=inp.ewald_tolerance, tilt=tilt)
 
 
 # ---- TIP4P/2005-like water of mc-topology/molecule-reservoir/tip4p-water (values restated) ----

@@ -127,8 +127,9 @@ def read_maniac_input(path) -> ManiacInput:
 
 
 def read_lammps_data(path):
-    """Returns dict(box_lo, box_hi, masses{type:mass}, atoms=array[id, mol, type, q, x, y, z])."""
+    """Returns dict(box_lo, box_hi, tilt (xy, xz, yz), masses{type:mass}, atoms=array[id, mol, type, q, x, y, z])."""
     lo, hi = [0.0] * 3, [0.0] * 3
+    tilt = [0.0, 0.0, 0.0]
     masses, atoms = {}, []
     natoms = ntypes = 0
     section = None
@@ -145,9 +146,8 @@ def read_lammps_data(path):
             ntypes = int(tok[0]); continue
         if len(tok) == 4 and tok[2] in ("xlo", "ylo", "zlo"):
             d = "xyz".index(tok[2][0]); lo[d], hi[d] = float(tok[0]), float(tok[1]); continue
-        if len(tok) >= 6 and tok[3] == "xy":
-            if any(abs(float(t)) > 0 for t in tok[:3]):
-                raise ValueError("triclinic boxes are out of scope (SURVEY Q8)")
+        if len(tok) >= 6 and tok[3] == "xy":      # "xy xz yz" tilt factors (ParseLAMMPSBox readers_utils.f90:205-214)
+            tilt = [float(v) for v in tok[:3]]
             continue
         if tok[0][0].isalpha():
             section = " ".join(tok); continue
@@ -163,7 +163,7 @@ def read_lammps_data(path):
     if not masses or len(masses) < ntypes:
         raise ValueError(f"{path}: missing or incomplete Masses section")
     a = np.array(sorted(atoms, key=lambda t: t[0]), dtype=np.float64)
-    return dict(box_lo=np.array(lo), box_hi=np.array(hi), masses=masses, atoms=a, ntypes=ntypes)
+    return dict(box_lo=np.array(lo), box_hi=np.array(hi), tilt=np.array(tilt), masses=masses, atoms=a, ntypes=ntypes)
 
 
 def read_pair_coeffs(path, ntypes):
@@ -200,3 +200,31 @@ def lorentz_berthelot(sigma, eps):
 
 def wrap_nearest(x, L):
     return np.mod(x + 0.5 * L, L) - 0.5 * L
+
+
+def nearest_image_tri(d, L, tilt):
+    """Nearest lattice image of separations d [..., 3] in the cell a = (lx,0,0), b = (xy,ly,0), c = (xz,yz,lz):
+    cascade z -> y -> x into the brick, then the 27 neighbouring images (same definition as the library's)."""
+    d = np.array(d, dtype=np.float64)
+    xy, xz, yz = tilt
+    n = np.rint(d[..., 2] / L[2]); d[..., 2] -= n * L[2]; d[..., 1] -= n * yz; d[..., 0] -= n * xz
+    n = np.rint(d[..., 1] / L[1]); d[..., 1] -= n * L[1]; d[..., 0] -= n * xy
+    n = np.rint(d[..., 0] / L[0]); d[..., 0] -= n * L[0]
+    best = d.copy(); best2 = (d ** 2).sum(-1)
+    for sa in (-1, 0, 1):
+        for sb in (-1, 0, 1):
+            for sc in (-1, 0, 1):
+                t = d + np.array([sa * L[0] + sb * xy + sc * xz, sb * L[1] + sc * yz, sc * L[2]])
+                r2 = (t ** 2).sum(-1)
+                m = r2 < best2
+                best[m] = t[m]; best2[m] = r2[m]
+    return best
+
+
+def wrap_tri(p, lo, L, tilt):
+    """ApplyPBC for a tilted cell: s = (a b c)^-1 (p - lo), s mod 1, back to Cartesian"""
+    xy, xz, yz = tilt
+    r = np.asarray(p, dtype=np.float64) - lo
+    sz = r[..., 2] / L[2]; sy = (r[..., 1] - yz * sz) / L[1]; sx = (r[..., 0] - xy * sy - xz * sz) / L[0]
+    sx, sy, sz = sx - np.floor(sx), sy - np.floor(sy), sz - np.floor(sz)
+    return lo + np.stack([L[0] * sx + xy * sy + xz * sz, L[1] * sy + yz * sz, L[2] * sz], axis=-1)

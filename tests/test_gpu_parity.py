@@ -731,8 +731,13 @@ def tilted_framework(n_fw=6000, box=60.0, tilt=(9.0, -7.0, 12.0)):
     return s
 
 
+def reference_dipoles():
+    """the reference's own tilted example (testcase-energy/DIPOLE-orthorhombic, tilt -20 -20 20)"""
+    return load_system("dipole_tri", init_sk=1, deletion_mode=1)
+
+
 def test_triclinic_single_point_energies():
-    for s in (tilted_dipoles(), tilted_framework()):
+    for s in (tilted_dipoles(), tilted_framework(), reference_dipoles()):
         g = ManiacGPU(s); e = g.system_energy()
         assert rel_err(e, orc.Oracle(s).system_energy()) < 1e-11
         kv_g, kv_o = g.kvectors(), orc.Oracle(s).kvectors()
@@ -741,10 +746,10 @@ def test_triclinic_single_point_energies():
         g.close()
 
 
-@pytest.mark.parametrize("which", ["dipoles", "framework"])
+@pytest.mark.parametrize("which", ["dipoles", "framework", "reference"])
 def test_triclinic_strict_mode_trajectory(which):
-    s = tilted_dipoles() if which == "dipoles" else tilted_framework()
-    n = 400 if which == "dipoles" else 150
+    s = tilted_dipoles() if which == "dipoles" else tilted_framework() if which == "framework" else reference_dipoles()
+    n = 150 if which == "framework" else 400
     tape = np.random.default_rng(8).random(16 * n)
     o = orc.Oracle(s); o.system_energy(); ref = o.run(n, tape=tape)
     g = ManiacGPU(s); drv = StrictDriver(s, g); drv.ComputeSystemEnergy()
@@ -760,11 +765,11 @@ def test_triclinic_strict_mode_trajectory(which):
     g.close()
 
 
-@pytest.mark.parametrize("which", ["dipoles", "framework"])
+@pytest.mark.parametrize("which", ["dipoles", "framework", "reference"])
 def test_triclinic_batched_matches_oracle(which):
     """device proposals (fractional insertion, fractional ApplyPBC) + fused chain kernel in a tilted cell"""
-    s = tilted_dipoles() if which == "dipoles" else tilted_framework()
-    n = 300 if which == "dipoles" else 120
+    s = tilted_dipoles() if which == "dipoles" else tilted_framework() if which == "framework" else reference_dipoles()
+    n = 120 if which == "framework" else 300
     g = ManiacGPU(s, n_chains=3)
     for c in range(3):
         g.system_energy(c)

@@ -97,3 +97,23 @@ def test_zero_tilt_is_the_orthorhombic_path_bit_for_bit():
     a.system_energy(); b.system_energy()
     ra, rb = a.run(200, seed=5), b.run(200, seed=5)
     assert np.array_equal(ra, rb)
+
+
+def test_reference_tilted_example_loads_and_runs():
+    """`mc-topology/testcase-energy/DIPOLE-orthorhombic` is, its name notwithstanding, a 40 A cell with tilt factors
+    (-20, -20, 20): 71 two-site dipoles (bond length 2, `bond_coeff 1 0 2`).  The fixture was read from the reference's
+    files by tools/make_golden.py; molecules repaired across the tilted boundaries have their bond length back."""
+    from conftest import load_system
+    s = load_system("dipole_tri", init_sk=1, deletion_mode=1)
+    assert np.array_equal(s.tilt, [-20.0, -20.0, 20.0]) and s.count.tolist() == [71] and s.kmax == [8, 7, 6]
+    bond = np.linalg.norm(s.offsets[0::2] - s.offsets[1::2], axis=1)
+    assert np.allclose(bond, 2.0, atol=0.3)                      # a thermal snapshot of a harmonic bond with r0 = 2
+    H = np.array([[40.0, -20.0, -20.0], [0.0, 40.0, 20.0], [0.0, 0.0, 40.0]])
+    frac = np.linalg.solve(H, (s.com - s.box_lo).T).T
+    assert frac.min() >= 0 and frac.max() < 1
+    o = orc.Oracle(s); e0 = o.system_energy()
+    assert np.all(np.isfinite(e0)) and abs(e0[1]) > 0 and abs(e0[2]) > 0
+    o.run(500, seed=2, records=False)
+    cnt, com, off = o.state()
+    t = s.copy(); t.count = cnt.copy(); t.com = com; t.offsets = off
+    assert np.allclose(o.energy(), orc.Oracle(t).system_energy(), rtol=1e-9, atol=1e-7)

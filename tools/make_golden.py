@@ -26,6 +26,8 @@ CASES = {
     # slit pore: 1912-atom wall + single-site fluid (no rotation moves, box origin at -20)
     "slit": ("testcase-adsorption/SLIT", "input.maniac", "topology.data", "parameters.inc", 256),
     "zif8_ch4o_h2o": ("testcase-adsorption/ZIF8-CH4O-H2O", "input.maniac", "topology.data", "parameters.inc", 256),
+    # the reference's only tilted cell: 71 two-site dipoles, 40 A box with xy xz yz = -20 -20 20 (despite the directory name)
+    "dipole_tri": ("testcase-energy/DIPOLE-orthorhombic", "dipole.maniac", "dipole.data", "dipole.inc", 256),
 }
 
 # Known answers held by the reference's own tests (kcal/mol):
