@@ -199,13 +199,18 @@ class BlockPipeline:
         self.gpu.snapshot_begin(0)
         self._drain(0, 0)
 
-    def run(self, n_blocks, n_steps, seed=0):
+    def run(self, n_blocks, n_steps, seed=0, pipelined=True):
+        """`pipelined=False` waits for every snapshot and writes its files before the next block is queued (what the
+        reference's loop does); only there to measure what the overlap buys"""
         pending = None
         for _ in range(n_blocks):
             self.block += 1
             self.gpu.run_batch_async(n_steps, seed=seed)
             slot = self.block & 1
             self.gpu.snapshot_begin(slot)
+            if not pipelined:
+                self._drain(slot, self.block)
+                continue
             if pending is not None:
                 self._drain(*pending)                            # files of the previous block, GPU busy with this one
             pending = (slot, self.block)

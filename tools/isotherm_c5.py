@@ -30,6 +30,9 @@ def main():
     p.add_argument("--blocks", type=int, default=20)
     p.add_argument("--steps", type=int, default=500)
     p.add_argument("--system", default=os.path.join(ROOT, "tests", "golden", "zif8_h2o.npz"))
+    p.add_argument("--files", default=None, help="directory: also time the block loop with the reference's per-block files "
+                   "written per chain, synchronously and pipelined behind the next block (wall clock, rank 0 prints)")
+    p.add_argument("--trajectory", action="store_true", help="with --files: also write trajectory.lammpstrj frames")
     a = p.parse_args()
     rank, world, lr = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(lr)
@@ -63,6 +66,25 @@ def main():
         f = iso.fugacity_points(a.points, 1e-2, 1e4)
         for i in range(0, a.points, max(1, a.points // 16)):
             print(f"  f = {f[i]:10.3e} atm   <N> = {curve[i, 0]:8.3f} +- {curve[i, 1]:.3f}")
+    if a.files:
+        import time
+        from maniac_mc_b200 import writers as W
+        out = {}
+        for mode in ("no_files", "files_sync", "files_pipelined"):
+            ws = [None] * sw.gpu.n_chains
+            if mode != "no_files":
+                for c, cid in enumerate(sw.ids):
+                    ws[c] = W.ChainWriter(W.chain_directory(os.path.join(a.files, mode, f"rank{rank}"), cid.point, cid.replica), s,
+                                          nb_block=a.blocks, trajectory=a.trajectory)
+            pipe = W.BlockPipeline(sw.gpu, ws)
+            sw.gpu.synchronize()
+            t0 = time.perf_counter()
+            pipe.run(a.blocks, a.steps, seed=1, pipelined=(mode != "files_sync"))
+            sw.gpu.synchronize()
+            out[mode] = time.perf_counter() - t0
+        if rank == 0:
+            print(json.dumps({"per_block_files": {k: round(v, 4) for k, v in out.items()}, "unit": "s wall per %d blocks" % a.blocks,
+                              "chains_on_rank0": len(sw.ids), "trajectory": a.trajectory}))
     sw.close()
     if world > 1:
         dist.barrier()
