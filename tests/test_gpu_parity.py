@@ -363,9 +363,10 @@ def test_c4_large_k_full_size_identities():
 
 
 # ---- k-sharded mode (SURVEY 8e optional mode): two emulated ranks on one GPU, the all-reduce replaced by a sum -----
-def test_k_sharded_steps_match_oracle_and_unsharded():
+@pytest.mark.parametrize("which", ["zif8_h2o", "tilted_framework"])
+def test_k_sharded_steps_match_oracle_and_unsharded(which):
     from maniac_mc_b200.sharded import emulate_ranks
-    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    s = load_system("zif8_h2o", init_sk=1, deletion_mode=1) if which == "zif8_h2o" else tilted_framework(n_fw=3000, box=48.0, tilt=(7.0, -5.0, 9.0))
     n, seed, C = 80, 4321, 2
     shards, step, _, _ = emulate_ranks(s, world=2, n_chains=C)
     recs = np.stack([step(seed, records=True) for _ in range(n)], axis=1)
