@@ -970,7 +970,9 @@ extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
 }
 
 // ---- batched mode -------------------------------------------------------------------------------
+#ifndef GRAPH_CHUNK
 #define GRAPH_CHUNK 128
+#endif
 
 // one launch of the chain-per-CTA kernel: every chain advances n steps
 static void launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases) {
