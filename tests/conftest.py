@@ -22,6 +22,19 @@ def load_system(name, **over):
     return s
 
 
+def ideal_mixture(ratio=2.0):
+    """The reference's two-species example with every interaction switched off and swap moves only: N_A + N_B is fixed
+    and detailed balance of mc_acceptance_probability_swap (monte_carlo_utils.f90:228-268) with a uniformly picked type
+    makes N_A binomial with p = phi_A / (phi_A + phi_B).  Returns (system, indices of the two active types, p_A)."""
+    import numpy as np
+    s = load_system("zif8_ch4o_h2o", init_sk=1, deletion_mode=1)
+    s.charges[:] = 0.0; s.epsilon[:] = 0.0
+    s.p_translation, s.p_rotation, s.p_swap = 0.0, 0.0, 1.0
+    act = np.flatnonzero(s.is_active == 1)
+    s.fugacity[act[0]] = ratio * 1e-3; s.fugacity[act[1]] = 1e-3
+    return s, act, ratio / (ratio + 1.0)
+
+
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN

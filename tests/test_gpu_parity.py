@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import load_system, rel_err
+from conftest import ideal_mixture, load_system, rel_err
 from maniac_mc_b200 import builders
 from maniac_mc_b200.driver import StrictDriver, TapeRng
 from maniac_mc_b200.lib import ManiacGPU, ManiacGpuError
@@ -475,6 +475,33 @@ def test_swap_batched_modes():
     assert (rs["kind"] == 5).sum() > 20
     for sh in shards:
         sh.close()
+    g.close()
+
+
+def test_swap_detailed_balance_ideal_mixture():
+    """SURVEY 8f.1 asks for a detailed-balance check of the swap move (there is no reference trajectory): swap moves only
+    in a non-interacting two-species mixture keep N_A + N_B and make N_A binomial(N, phi_A / (phi_A + phi_B)) on every
+    chain of the batched loop.  Same system and expectation as tests/test_oracle_golden.py's CPU check."""
+    s, act, pA = ideal_mixture(2.0)
+    n_tot = int(s.count[act].sum())
+    C = 64
+    g = ManiacGPU(s, n_chains=C)
+    for c in range(C):
+        g.set_chain_id(c, 500 + c); g.system_energy(c)
+    g.run_batch(400, seed=23)
+    cnt = np.zeros((C, s.nres), dtype=np.int32)
+    samples = []
+    for b in range(150):
+        g.run_batch_async(20, seed=23)
+        g.download_chains(cnt, None, None, None, None)
+        assert np.all(cnt[:, act].sum(axis=1) == n_tot)
+        samples.append(cnt[:, act[0]].copy())
+    n = np.array(samples, dtype=np.float64)
+    mean, var = n.mean(), n.var()
+    assert abs(mean - n_tot * pA) < 0.02 * n_tot * pA, (mean, n_tot * pA)          # 9600 samples, ~1 per 20 moves independent
+    assert abs(var - n_tot * pA * (1 - pA)) < 0.1 * n_tot * pA * (1 - pA), (var, n_tot * pA * (1 - pA))
+    e = np.zeros((C, 6)); g.download_chains(None, None, None, e, None)
+    assert np.all(np.abs(e[:, :3]) < 1e-9)
     g.close()
 
 

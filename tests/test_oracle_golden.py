@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN, load_system, rel_err
+from conftest import GOLDEN, ideal_mixture, load_system, rel_err
 from maniac_mc_b200.system import (E_COUL, E_INTRA, E_NONCOUL, E_RECIP, E_SELF, E_TOTAL, MMC_CREATION, MMC_DELETION,
                                    MMC_ROTATION, MMC_TRANSLATION, ewald_setup)
 from oracle import oracle as orc
@@ -205,6 +205,27 @@ def test_two_species_fixture_and_reader():
     s = load_system("zif8_ch4o_h2o")
     assert s.natoms.tolist() == [2208, 6, 4] and s.is_active.tolist() == [0, 1, 1] and s.count.tolist() == [1, 5, 5]
     assert s.num_kvectors == 297 and abs(s.p_swap - 0.2 / 1.2) < 1e-12     # probabilities renormalised (input_parser.f90:98-111)
+
+
+def test_swap_detailed_balance_ideal_mixture():
+    """the swap move has no reference trajectory, so it is validated by detailed balance.  Swap moves only in a
+    non-interacting two-species mixture: N_A + N_B is conserved and N_A is binomial(N, phi_A / (phi_A + phi_B))."""
+    s, act, pA = ideal_mixture(2.0)
+    o = orc.Oracle(s); o.system_energy()
+    n_tot = int(s.count[act].sum())
+    o.run(300, seed=3, chain=0, step0=0, records=False)
+    ns = []
+    for b in range(500):
+        o.run(10, seed=3, chain=0, step0=300 + b * 10, records=False)
+        ns.append(o.state()[0][act].copy())
+    ns = np.array(ns, dtype=np.float64)
+    assert np.all(ns.sum(axis=1) == n_tot)
+    mean, var = ns[:, 0].mean(), ns[:, 0].var()
+    assert abs(mean - n_tot * pA) < 0.4, (mean, n_tot * pA)               # s.e. ~ 0.09 for ~250 independent samples
+    assert abs(var - n_tot * pA * (1 - pA)) < 0.6, (var, n_tot * pA * (1 - pA))
+    c = o.counters()
+    assert c["trial_swaps"] > 4000 and 0 < c["swaps"] < c["trial_swaps"]
+    assert np.all(np.abs(o.energy()[:3]) < 1e-9)
 
 
 def test_swap_move_identities():
