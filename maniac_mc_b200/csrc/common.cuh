@@ -198,6 +198,11 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
 // variable t in [-1, 1)), built at mmc_init for this system's alpha in long double (build_coulomb_table,
 // maniac_gpu.cu).  Absolute error <= 5e-16 (it is at the rounding floor of the coefficients), i.e. a few
 // 1e-16 relative where the terms matter (alpha r < 1.5) -- no sqrt, no exp, no division per pair.
+// Reciprocal update of a translation as S_mol(k) (e^{i k d} - 1) (kernels_sweep.cuh, stage_terms): n + 1 product terms
+// instead of 2 n.  On by default (A/B on one box: +1.5 %); -DMMC_NO_FACTORED_TRANSLATION restores the 2 n terms.
+#ifndef MMC_NO_FACTORED_TRANSLATION
+#define MMC_FACTORED_TRANSLATION 1
+#endif
 #define MMC_GTAB_DEG 9
 #define MMC_GTAB_MBITS 3
 #define MMC_GTAB_MAXSEG 128   // also the row stride: layout [degree][segment]

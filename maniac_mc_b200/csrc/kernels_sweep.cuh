@@ -25,6 +25,7 @@ struct MolS {
     int shift_ok;       // reach + radius < L/2 on every axis: one periodic shift per other atom is exact
     int type[MMC_MAX_MOL_ATOMS];
     int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
+    int fact;           // MMC_FACTORED_TRANSLATION: terms = +q phi(old) of the charged atoms, last term = e^{i k d}
     signed char term[2 * MMC_MAX_MOL_ATOMS];  // reciprocal terms: +(a+1) = atom a added, -(a+1) = atom a removed
     double sums[6];        // block sums of this trial: parked here between the phases so they hold no registers
     unsigned int work[2];  // executed real-space work of this CTA (distances formed, pairs inside reach)
@@ -152,6 +153,16 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
     if (tid == 0) {
         // atoms with q == 0 add exactly zero to A(k) (ewald_energy.f90:241-256 multiplies by the charge): no term
         int n = 0;
+        m.fact = 0;
+#ifdef MMC_FACTORED_TRANSLATION
+        // a translation moves every atom by the same d: sum q phi(new) - sum q phi(old) = S_mol(k) (e^{i k d} - 1) with
+        // S_mol = sum q phi(old): n + 1 product terms instead of 2 n
+        if (!TRI && t.kind == MMC_TRANSLATION) {
+            for (int a = 0; a < t.nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(-(a + 1));
+            if (n > 1) { m.term[n++] = 127; m.fact = 1; } else n = 0;
+        }
+        if (!m.fact)
+#endif
         if (t.kind > 0) {
             if (t.r_plus) for (int a = 0; a < t.nat2; a++) if (t.q2[a] != 0.0) m.term[n++] = (signed char)(a + 1);
             if (t.r_minus) for (int a = 0; a < t.nat; a++) if (t.q[a] != 0.0) m.term[n++] = (signed char)(-(a + 1));
@@ -166,16 +177,25 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
         const int term = i / per; int j = i % per;
         const int ta = m.term[term];
         const bool plus = ta > 0;
-        const int a = (plus ? ta : -ta) - 1;
+        const int a = ta == 127 ? 0 : (plus ? ta : -ta) - 1;
         int ax, k; double2* dst;
         if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
         else if (j < s.nx + s.ny) { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
         else { j -= s.nx + s.ny; ax = 2; k = j; dst = s.Z + j * s.zs + term; }
         const double* pp = plus ? t.p_plus[a] : t.p_old[a];
-        const double theta = MMC_TWOPI * (TRI ? frac_coord(dc, pp, ax) : dc.invL[ax] * pp[ax]);
+        double theta = MMC_TWOPI * (TRI ? frac_coord(dc, pp, ax) : dc.invL[ax] * pp[ax]);
+#ifdef MMC_FACTORED_TRANSLATION
+        if (ta == 127) theta = MMC_TWOPI * dc.invL[ax] * (t.p_plus[0][ax] - t.p_old[0][ax]);
+#endif
         double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
         if (k < 0) sn = -sn;
-        if (ax == 2) { const double q = plus ? t.q2[a] : -t.q[a]; co *= q; sn *= q; }
+        if (ax == 2) {
+            double q = plus ? t.q2[a] : -t.q[a];
+#ifdef MMC_FACTORED_TRANSLATION
+            if (m.fact) q = ta == 127 ? 1.0 : t.q[a];
+#endif
+            co *= q; sn *= q;
+        }
         *dst = make_double2(co, sn);
     }
     __syncthreads();
@@ -388,7 +408,7 @@ __device__ __forceinline__ void recip_stage_rows(const SweepCtx& s, int nterm, i
 
 // the items [i0, i1) of one staged chunk of rows.  NTERM > 0: term count known at compile time (the shared loads get
 // immediate offsets and the loop disappears); NTERM == 0: generic loop over nterm.
-template <int NT, int NTERM, bool TRI>
+template <int NT, int NTERM, bool TRI, bool FACT = false>
 __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& s, const double2* __restrict__ A, double2* __restrict__ An,
                                             const double2* xy, int ra, int i0, int i1, int nterm, double (&acc)[2]) {
     const int ny = s.ny, zs = s.zs;
@@ -409,24 +429,33 @@ __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& 
         double s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0;
         if (NTERM > 0) {
 #pragma unroll
-            for (int t = 0; t < NTERM; t++) {
+            for (int t = 0; t < (FACT ? NTERM - 1 : NTERM); t++) {
                 const double2 P = pt[t], Z = zt[t];
                 s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
                 s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
             }
         } else {
-            for (int t = 0; t < nterm; t++) {
+            for (int t = 0; t < (FACT ? nterm - 1 : nterm); t++) {
                 const double2 P = pt[t], Z = zt[t];
                 s1 = fma(P.x, Z.x, s1); s2 = fma(P.y, Z.y, s2);
                 s3 = fma(P.x, Z.y, s3); s4 = fma(P.y, Z.x, s4);
             }
         }
-        const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
+        double dpx = s1 - s2, dpy = s3 + s4, dmx = s1 + s2, dmy = s4 - s3;   // sum_t P_t Z_t and sum_t P_t conj(Z_t)
+        if (FACT) {   // times (e^{i k d} - 1), the last term's product, for k(+kz) and k(-kz)
+            const double2 P = pt[(NTERM > 0 ? NTERM : nterm) - 1], Z = zt[(NTERM > 0 ? NTERM : nterm) - 1];
+            const double d1 = P.x * Z.x, d2 = P.y * Z.y, d3 = P.x * Z.y, d4 = P.y * Z.x;
+            const double epx = (d1 - d2) - 1.0, epy = d3 + d4, emx = (d1 + d2) - 1.0, emy = d4 - d3;
+            const double tpx = fma(dpx, epx, -dpy * epy), tmx = fma(dmx, emx, -dmy * emy);
+            dpy = fma(dpx, epy, dpy * epx); dmy = fma(dmx, emy, dmy * emx);
+            dpx = tpx; dmx = tmx;
+        }
+        const double2 bp = make_double2(ap.x + dpx, ap.y + dpy);
         An[kpl] = bp;
         acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
         acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
         if (two) {
-            const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
+            const double2 bm = make_double2(am.x + dmx, am.y + dmy);
             An[kmi] = bm;
             const double wm = TRI ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
             acc[0] = fma(wm, fma(am.x, am.x, am.y * am.y), acc[0]);
@@ -465,6 +494,16 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
         }
         const double2* xy = s.XY + buf * bufsz;
         const int i0 = dc.item_row_start[ra], i1 = dc.item_row_start[rb];
+#ifdef MMC_FACTORED_TRANSLATION
+        if (m.fact) {
+            switch (nterm) {   // charged atoms + 1
+                case 3: recip_items<NT, 3, TRI, true>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+                case 4: recip_items<NT, 4, TRI, true>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+                case 5: recip_items<NT, 5, TRI, true>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+                default: recip_items<NT, 0, TRI, true>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
+            }
+        } else
+#endif
         switch (nterm) {   // 3 / 6 = rigid water insertion-deletion / move; the others cover 1..4 charged sites
             case 1: recip_items<NT, 1, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
             case 2: recip_items<NT, 2, TRI>(dc, s, A, An, xy, ra, i0, i1, nterm, acc); break;
