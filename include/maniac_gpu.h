@@ -71,7 +71,7 @@ typedef struct mmc_desc {
     const double* com;     /* [3 * sum(count)] */
     const double* offsets; /* [3 * sum(count*natoms)] */
     double box_lo[3];      /* primary%bounds(:,1) */
-    double box_len[3];     /* primary%matrix(d,d); orthorhombic boxes only (box%type 1,2) */
+    double box_len[3];     /* primary%matrix(d,d): cell edge lengths lx, ly, lz (box%type 1,2; type 3 adds `tilt` below) */
     double alpha;          /* ewald%alpha */
     double cutoff;         /* input%real_space_cutoff */
     double temperature;    /* input%temp_K */
@@ -235,8 +235,8 @@ int mmc_get_sk(mmc_t* handle, int chain, double* sk);
 
 /* ---- batched mode: the inner `do current_step` loop of MonteCarloLoop on the device ------- */
 
-/* Runs n_steps Monte Carlo steps (monte_carlo.f90:42-76) on EVERY chain, all chains advancing
- * one step per launch group, the step sequence captured in a CUDA graph.
+/* Runs n_steps Monte Carlo steps (monte_carlo.f90:42-76) on EVERY chain: one CTA (or one thread-block cluster) owns a
+ * chain and loops over the steps inside the kernel, 128 steps per launch, the launches replayed from a CUDA graph.
  * Random numbers: if tape != NULL chain c reads its uniforms sequentially from
  * tape[c*tape_stride ...] (strict replay of a recorded stream, draw order of SURVEY 3.8);
  * otherwise Philox4x32-10 keyed by seed with counter (step, chain, draw).
@@ -282,6 +282,8 @@ int mmc_dbg_intra_singlemol(mmc_t* handle, int chain, int res, int mol, double* 
 int mmc_dbg_table_lookup(mmc_t* handle, int which, const double* r, int n, double* out);
 /* device erfc used by the pair sweep, for accuracy tests */
 int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
+/* test support: overwrite a chain's tracked energies (6 doubles) and / or tracked A(k) (2*K doubles); NULL = keep */
+int mmc_dbg_set_tracked(mmc_t* handle, int chain, const double* energies, const double* sk);
 /* timing of the last pair / recip sweeps in a batched run is taken by the caller with
  * CUDA events on this stream */
 void* mmc_stream(mmc_t* handle);

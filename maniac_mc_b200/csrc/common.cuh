@@ -27,6 +27,9 @@
 #define MMC_KB_eVK 8.6173852e-5
 #define MMC_ERR 1.0e-10
 #define MMC_PROB_CREATE_DELETE 0.5  // parameters.f90:21
+// bits of ChainState.error_flag: sticky on the device until a host entry point reads (and clears) them
+#define MMC_ERRF_CAPACITY 1   // a creation / swap hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604); the move was skipped
+#define MMC_ERRF_TAPE 2       // a chain consumed more uniforms than its tape holds
 
 struct DevConst {
     int nres, ntypes, n_chains, n_active;
@@ -124,7 +127,7 @@ struct ChainState {
     double* roff;         // [C][r_atoms][3] their site offsets (reservoir%site_offset)
     unsigned int* chain_id;  // [C] Philox stream of each chain (default: the chain index); global ids make a sweep independent of how chains are dealt to GPUs
     unsigned long long* pair_count;  // [2] executed real-space work since mmc_init: distances formed, pairs inside reach
-    int* error_flag;      // [1] set when a creation hit the slot capacity (CheckMoleculeIndex, output_utils.f90:604)
+    int* error_flag;      // [1] MMC_ERRF_* bits, sticky until read by the host
 };
 
 struct RngSrc {

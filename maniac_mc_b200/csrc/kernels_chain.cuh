@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             RngSrc rs = ctl->rng;
             rs.step += (unsigned long long)st;
             propose_move(dc, cs, rs, c);
-            if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
+            if (cs.trial[c].error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
         }
         __syncthreads();
         sweep_trial<NT, TRI>(dc, cs, c, s, 0, 1, phases);

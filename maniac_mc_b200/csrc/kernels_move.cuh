@@ -16,7 +16,13 @@ __device__ __forceinline__ size_t g_atom(const DevConst& dc, int c, int r, int m
 struct Rng {
     const RngSrc* src; ChainState cs; int c; int draw;
     __device__ double next() {
-        if (src->tape) { long long p = cs.tape_pos[c]++; return src->tape[(size_t)c * src->tape_stride + p]; }
+        if (src->tape) {
+            // a tape shorter than the draws consumed must not run into the next chain's tape (a host-side replay aborts on
+            // exhaustion): flag it (MMC_ERR_TAPE, reported by the host entry point) and return a harmless uniform
+            const long long p = cs.tape_pos[c]++;
+            if (p >= src->tape_stride) { atomicOr(cs.error_flag, MMC_ERRF_TAPE); return 0.5; }
+            return src->tape[(size_t)c * src->tape_stride + p];
+        }
         return philox_uniform(src->seed, cs.chain_id[c], src->step, (uint32_t)draw++);
     }
 };
@@ -425,7 +431,7 @@ __global__ void k_propose_all(DevConst dc, ChainState cs, const BatchCtl* ctl, i
     const int c = c0 + blockIdx.x;
     RngSrc rs = ctl->rng;
     propose_move(dc, cs, rs, c);
-    if (cs.trial[c].error) atomicExch(cs.error_flag, 1);
+    if (cs.trial[c].error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
 }
 __global__ void __launch_bounds__(TAIL_THREADS) k_part_sum(DevConst dc, ChainState cs, int c0, double* sums /* [chains][6] */) {
     __shared__ double red[6 * TAIL_THREADS / 32];

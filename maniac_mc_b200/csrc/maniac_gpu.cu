@@ -62,7 +62,7 @@ struct mmc_handle {
     // per-block snapshots (mmc_snapshot_begin / _wait): device blob + pinned mirror per slot, copied out on copy_stream
     struct Snap { char* dev = nullptr; char* host = nullptr; cudaEvent_t taken = nullptr, landed = nullptr; bool pending = false; };
     Snap snap[2];
-    size_t snap_off[5] = {0, 0, 0, 0, 0}, snap_bytes = 0;
+    size_t snap_off[6] = {0, 0, 0, 0, 0, 0}, snap_bytes = 0;   // count, com, offsets, energies, counters, error flag
     std::vector<int> snap_count[2];        // compacted [C][nres] counts handed to the caller
     cudaStream_t copy_stream = nullptr;
 };
@@ -77,6 +77,17 @@ static cudaError_t dalloc(mmc_handle* h, T** p, size_t n) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(0);   // set-up only: the zero fill is complete before any stream touches q
     *p = (T*)q;
     return e;
+}
+
+// The device raises MMC_ERRF_* bits in cs.error_flag and leaves them set; every host entry point that hands chain data
+// back (mmc_synchronize, mmc_run_batch, mmc_download_chains, mmc_snapshot_wait) reports them through this function, so an
+// overflow can never pass silently (the reference aborts there: CheckMoleculeIndex -> AbortRun, output_utils.f90:604).
+// `clear`: the flag was read from the live device word (not from a snapshot blob) and is reset for the next report.
+static int report_error_flag(mmc_handle* h, int flag, bool clear) {
+    if (!flag) return 0;
+    if (clear) cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), h->stream);
+    if (flag & MMC_ERRF_TAPE) return fail("a chain consumed more uniforms than its tape holds (tape_stride too short for n_steps); the extra draws were 0.5");
+    return fail("a creation move exceeded the slot capacity (molecule index exceeds the maximum allowed, NB_MAX_MOLECULE analogue); that move was skipped");
 }
 
 extern "C" const char* mmc_last_error(void) { return g_err.c_str(); }
@@ -371,8 +382,15 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     *out = nullptr;
     if (d->nres < 1 || d->nres > MMC_MAX_RES) return fail("mmc_init: nres=%d outside [1,%d]", d->nres, MMC_MAX_RES);
     if (d->n_chains < 1) return fail("mmc_init: n_chains must be >= 1");
+    if (d->ntypes < 1) return fail("mmc_init: ntypes must be >= 1");
+    if (!d->natoms || !d->is_active || !d->count || !d->charges || !d->types || !d->sigma || !d->epsilon) return fail("mmc_init: null array in mmc_desc");
+    for (int r = 0; r < d->nres; r++) {
+        if (d->natoms[r] < 1) return fail("mmc_init: residue %d has %d atoms", r, d->natoms[r]);
+        if (d->natoms[r] > d->max_atoms) return fail("mmc_init: residue %d has %d atoms but max_atoms (leading dimension of charges/types) is %d", r, d->natoms[r], d->max_atoms);
+        if (d->count[r] < 0) return fail("mmc_init: residue %d has a negative molecule count", r);
+    }
     for (int k = 0; k < 3; k++) {
-        if (!(d->box_len[k] > 0.0)) return fail("mmc_init: box_len[%d] must be positive (orthorhombic boxes only)", k);
+        if (!(d->box_len[k] > 0.0)) return fail("mmc_init: box_len[%d] must be positive (cell edge lengths lx, ly, lz; tilt factors go in mmc_desc.tilt)", k);
         if (d->kmax[k] < 1) return fail("mmc_init: kmax[%d] must be >= 1", k);
     }
     if (!(d->alpha > 0.0) || !(d->cutoff > 0.0) || !(d->temperature > 0.0)) return fail("mmc_init: alpha, cutoff and temperature must be positive");
@@ -727,11 +745,13 @@ extern "C" int mmc_download_chains(mmc_t* h, int* count, double* com, double* of
     if (offsets) CK(cudaMemcpyAsync(offsets, h->cs.goff, C * dc.g_atoms * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
     if (energies) CK(cudaMemcpyAsync(energies, h->cs.energy, C * MMC_NE * sizeof(double), cudaMemcpyDeviceToHost, st));
     if (counters) CK(cudaMemcpyAsync(counters, h->cs.counters, C * sizeof(mmc_counters), cudaMemcpyDeviceToHost, st));
+    int* h_flag = (int*)(h->h_out + 15);   // pinned; the last of the 16 result doubles is not used by any energy read-back
+    CK(cudaMemcpyAsync(h_flag, h->cs.error_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (count)  // inactive residues: the host already knows them
         for (size_t c = 0; c < C; c++)
             for (int r = 0; r < dc.nres; r++) if (!dc.is_active[r]) count[c * dc.nres + r] = dc.cap[r];
-    return 0;
+    return report_error_flag(h, *h_flag, true);   // the arrays are filled either way
 }
 
 // Per-block snapshot without stalling the chains (write_utils.f90:13-188 runs between blocks in the reference):
@@ -743,10 +763,10 @@ extern "C" int mmc_snapshot_begin(mmc_t* h, int slot) {
     CK(cudaSetDevice(h->device));
     const DevConst& dc = h->dc; const size_t C = dc.n_chains;
     if (!h->snap_bytes) {
-        const size_t sz[5] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
-                              C * MMC_NE * sizeof(double), C * sizeof(mmc_counters)};
+        const size_t sz[6] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
+                              C * MMC_NE * sizeof(double), C * sizeof(mmc_counters), sizeof(int)};
         size_t o = 0;
-        for (int i = 0; i < 5; i++) { h->snap_off[i] = o; o += (sz[i] + 255) & ~(size_t)255; }
+        for (int i = 0; i < 6; i++) { h->snap_off[i] = o; o += (sz[i] + 255) & ~(size_t)255; }
         h->snap_bytes = o;
         CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     }
@@ -758,10 +778,10 @@ extern "C" int mmc_snapshot_begin(mmc_t* h, int slot) {
         CK(cudaEventCreateWithFlags(&s.landed, cudaEventDisableTiming));
     }
     if (s.pending) CK(cudaEventSynchronize(s.landed));   // the slot's previous copy-out still reads s.dev
-    const void* src[5] = {h->cs.count, h->cs.gcom, h->cs.goff, h->cs.energy, h->cs.counters};
-    const size_t sz[5] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
-                          C * MMC_NE * sizeof(double), C * sizeof(mmc_counters)};
-    for (int i = 0; i < 5; i++)
+    const void* src[6] = {h->cs.count, h->cs.gcom, h->cs.goff, h->cs.energy, h->cs.counters, h->cs.error_flag};
+    const size_t sz[6] = {C * MMC_MAX_RES * sizeof(int), C * dc.g_mols * 3 * sizeof(double), C * dc.g_atoms * 3 * sizeof(double),
+                          C * MMC_NE * sizeof(double), C * sizeof(mmc_counters), sizeof(int)};
+    for (int i = 0; i < 6; i++)
         if (sz[i]) CK(cudaMemcpyAsync(s.dev + h->snap_off[i], src[i], sz[i], cudaMemcpyDeviceToDevice, h->stream));
     CK(cudaEventRecord(s.taken, h->stream));
     CK(cudaStreamWaitEvent(h->copy_stream, s.taken, 0));
@@ -789,7 +809,8 @@ extern "C" int mmc_snapshot_wait(mmc_t* h, int slot, const int** count, const do
     if (offsets) *offsets = (const double*)(s.host + h->snap_off[2]);
     if (energies) *energies = (const double*)(s.host + h->snap_off[3]);
     if (counters) *counters = (const mmc_counters*)(s.host + h->snap_off[4]);
-    return 0;
+    // the error word as it stood when the snapshot was taken (sticky on the device: a later mmc_synchronize reports it again)
+    return report_error_flag(h, *(const int*)(s.host + h->snap_off[5]), false);
 }
 
 extern "C" int mmc_get_reservoir(mmc_t* h, int c, int* count, double* offsets) {
@@ -1003,7 +1024,7 @@ static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const do
     ctl.recs = d_recs; ctl.rec_stride = n_steps; ctl.rec_base = 0;
     CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, st));  // pageable source: copied before return
     CK(cudaMemsetAsync(h->cs.tape_pos, 0, h->dc.n_chains * sizeof(long long), st));
-    CK(cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), st));
+    // cs.error_flag is NOT cleared here: it stays set until a host entry point reports it (report_error_flag)
     int64_t done = 0;
     if (n_steps >= GRAPH_CHUNK) {
         if (!h->graph) {
@@ -1034,8 +1055,7 @@ static int refresh_counts(mmc_handle* h) {
     CK(cudaMemcpy(h->h_count.data(), h->cs.count, h->h_count.size() * sizeof(int), cudaMemcpyDeviceToHost));
     int flag = 0;
     CK(cudaMemcpy(&flag, h->cs.error_flag, sizeof(int), cudaMemcpyDeviceToHost));
-    if (flag) return fail("a creation move exceeded the slot capacity (NB_MAX_MOLECULE analogue); that move was skipped");
-    return 0;
+    return report_error_flag(h, flag, true);
 }
 
 extern "C" int mmc_run_batch_async(mmc_t* h, int64_t n_steps, uint64_t seed) {
@@ -1054,7 +1074,6 @@ extern "C" int mmc_profile_kernels(mmc_t* h, int n_steps, uint64_t seed, double 
     ctl.rng.tape = nullptr; ctl.rng.tape_stride = 0; ctl.rng.seed = seed; ctl.rng.step = h->steps_done;
     ctl.recs = nullptr; ctl.rec_stride = n_steps; ctl.rec_base = 0;
     CK(cudaMemcpyAsync(h->d_ctl, &ctl, sizeof ctl, cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(h->cs.error_flag, 0, sizeof(int), st));
     cudaEvent_t ev[4];
     for (auto& e : ev) CK(cudaEventCreate(&e));
     // the same n_steps proposals three times: real-space phase only, reciprocal phase only (neither commits,
@@ -1205,6 +1224,20 @@ extern "C" int mmc_dbg_intra_singlemol(mmc_t* h, int c, int res, int mol, double
     if (mmc_trial_energy(h, c, MMC_DELETION, res, mol, nullptr, nullptr, o, n)) return 1;
     if (mmc_trial_commit(h, c, 0)) return 1;
     if (e_intra) *e_intra = o[MMC_E_INTRA];
+    return 0;
+}
+// test support: overwrite a chain's tracked energies and / or its tracked A(k) (resynchronising a long parity run with
+// its CPU checker after an accept/reject flip; the reference has no counterpart)
+extern "C" int mmc_dbg_set_tracked(mmc_t* h, int c, const double* energies, const double* sk) {
+    CHECK_CHAIN(h, c);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (energies) CK(cudaMemcpy(h->cs.energy + (size_t)c * MMC_NE, energies, MMC_NE * sizeof(double), cudaMemcpyHostToDevice));
+    if (sk) {
+        int cur = 0;
+        CK(cudaMemcpy(&cur, h->cs.cur + c, sizeof(int), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(h->cs.A + ((size_t)c * 2 + cur) * h->dc.nk, sk, (size_t)h->dc.nk * sizeof(double2), cudaMemcpyHostToDevice));
+    }
     return 0;
 }
 static int run_elementwise(mmc_handle* h, int which, const double* in, int n, double* out) {

@@ -123,10 +123,12 @@ class IsothermSweep:
     """One rank's share of an isotherm sweep on one GPU."""
 
     def __init__(self, system, n_points=64, replicas=1, lo_atm=1.0e-2, hi_atm=1.0e4, world=1, rank=0, device=0,
-                 active_residue=None):
+                 active_residue=None, recalibrate=None):
         from . import builders
         from .lib import ManiacGPU   # raises if the CUDA library is missing: no CPU fallback
         self.sys, self.n_points, self.replicas, self.world, self.rank = system, n_points, replicas, world, rank
+        # input%recalibrate_moves (monte_carlo.f90:78): AdjustMoveStepSizes after every block; default = what the input says
+        self.recalibrate = bool(getattr(system, "recalibrate_moves", False)) if recalibrate is None else bool(recalibrate)
         self.ids = deal_chains(n_points, replicas, world, rank)
         self.f_atm = fugacity_points(n_points, lo_atm, hi_atm)
         self.res = int(np.flatnonzero(system.is_active)[0]) if active_residue is None else active_residue
@@ -148,6 +150,9 @@ class IsothermSweep:
         """one block of `n_steps` MC steps on every local chain, then one sample of N, E and the counters
         (`monte_carlo.f90:42-84`: inner step loop, then the per-block output)."""
         self.gpu.run_batch_async(n_steps, seed=seed)
+        if self.recalibrate:
+            self.gpu.adjust_step_sizes()
+        # raises ManiacGpuError if a creation hit the slot capacity during the block (the reference aborts there)
         self.gpu.download_chains(self._cnt, None, None, self._e, self._ctr)
         n = len(self.ids)
         self.avg.add(self._cnt[:n, self.res], self._e[:n, 5], self._ctr[:n])
@@ -170,7 +175,7 @@ class IsothermSweep:
             cnt, _, _, e, ctr = snap
             if block > 0:
                 self.avg.add(cnt[:n, self.res], e[:n, 5], ctr[:n])
-        pipe = W.BlockPipeline(self.gpu, ws, on_block=sample)
+        pipe = W.BlockPipeline(self.gpu, ws, on_block=sample, recalibrate=self.recalibrate)
         if output_root is not None and self.step == 0:
             pipe.write_initial()
         pipe.block = self.step // max(n_steps, 1)

@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked",
 ]
 
 _lib = None
@@ -93,6 +93,7 @@ def load():
     L.mmc_dbg_intra_singlemol.argtypes = [vp, C.c_int, C.c_int, C.c_int, dp]
     L.mmc_dbg_table_lookup.argtypes = [vp, C.c_int, dp, C.c_int, dp]
     L.mmc_dbg_erfc.argtypes = [vp, dp, C.c_int, dp]
+    L.mmc_dbg_set_tracked.argtypes = [vp, C.c_int, dp, dp]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
     L.mmc_pair_work.argtypes = [vp, C.POINTER(C.c_int64)]
@@ -351,6 +352,14 @@ class ManiacGPU:
     def dbg_erfc(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64); out = np.zeros_like(x)
         _ck(load().mmc_dbg_erfc(self.h, _dp(x), len(x), _dp(out))); return out
+
+    def dbg_set_tracked(self, energies=None, sk=None, chain=0):
+        """overwrite tracked energies [6] and / or tracked A(k) (complex [K]) of one chain (test support)"""
+        e = None if energies is None else np.ascontiguousarray(energies, dtype=np.float64)
+        a = None
+        if sk is not None:
+            a = np.empty(2 * self.nk); a[0::2] = np.real(sk); a[1::2] = np.imag(sk)
+        _ck(load().mmc_dbg_set_tracked(self.h, chain, _dp(e), _dp(a)))
 
     def stream(self):
         return load().mmc_stream(self.h)

@@ -72,12 +72,22 @@ def number_row(block, n):
     return _fint(block, 10) + " " + _fint(n, 10)
 
 
+# field order of `mmc_counters` (include/maniac_gpu.h), the Counters ctypes class and the snapshot rows
+COUNTER_FIELDS = ("translations", "rotations", "creations", "deletions", "trial_translations", "trial_rotations",
+                  "trial_creations", "trial_deletions", "swaps", "trial_swaps")
+
+
 def moves_row(block, ctr, literal=True):
-    """ctr in `mmc_counters` order: translations, trial_translations, rotations, trial_rotations, creations,
-    trial_creations, deletions, trial_deletions, (swaps, trial_swaps)"""
-    last = ctr[6] if literal else ctr[2]
-    cols = [block, ctr[1], ctr[0], ctr[5], ctr[4], ctr[7], ctr[6], ctr[3], last]
-    return " ".join(_fint(c, 12) for c in cols)
+    """One `moves.dat` row (`write_utils.f90:178-186`).  `ctr` is one chain's counters in `mmc_counters` STRUCT order
+    (COUNTER_FIELDS: the four accepted counts, then the four trial counts, then swaps, trial_swaps) or a mapping by
+    field name.  Columns: block, trial_translations, translations, trial_creations, creations, trial_deletions,
+    deletions, trial_rotations and -- literally as the reference writes it (:186) -- deletions again in the
+    Rotate_Moves column; `literal=False` puts the accepted rotations there."""
+    c = ctr if isinstance(ctr, dict) else dict(zip(COUNTER_FIELDS, ctr))
+    last = c["deletions"] if literal else c["rotations"]
+    cols = [block, c["trial_translations"], c["translations"], c["trial_creations"], c["creations"],
+            c["trial_deletions"], c["deletions"], c["trial_rotations"], last]
+    return " ".join(_fint(int(v), 12) for v in cols)
 
 
 def lammpstrj_frame(timestep, box_len, types, is_active, natoms, count, com, offsets):
@@ -178,8 +188,10 @@ class BlockPipeline:
     `gpu` is a `ManiacGPU`; `writers[c]` a `ChainWriter` (or None to skip the chain); `on_block(block, snapshot)` is
     called with every snapshot (count, com, offsets, energies, counters) after its files are written."""
 
-    def __init__(self, gpu, writers, on_block=None):
-        self.gpu, self.writers, self.on_block = gpu, writers, on_block
+    def __init__(self, gpu, writers, on_block=None, recalibrate=False):
+        # recalibrate: AdjustMoveStepSizes after every block (monte_carlo.f90:78, input%recalibrate_moves); the call is
+        # stream-ordered on the device, so it does not stall the pipeline
+        self.gpu, self.writers, self.on_block, self.recalibrate = gpu, writers, on_block, recalibrate
         self.block = 0
         self.last = None
 
@@ -206,6 +218,8 @@ class BlockPipeline:
         for _ in range(n_blocks):
             self.block += 1
             self.gpu.run_batch_async(n_steps, seed=seed)
+            if self.recalibrate:
+                self.gpu.adjust_step_sizes()
             slot = self.block & 1
             self.gpu.snapshot_begin(slot)
             if not pipelined:

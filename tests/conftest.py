@@ -43,3 +43,38 @@ def golden_dir():
 def rel_err(a, b, floor=1.0):
     a = np.asarray(a, dtype=float); b = np.asarray(b, dtype=float)
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor)))
+
+
+# ---- move-record comparison (GPU vs oracle, oracle vs fixture) ----------------------------------------------------
+REL_TOL = 1e-10    # BASELINE.json north_star: energies within 1e-10 relative in FP64
+FLOOR_FRAC = 1e-3  # a component smaller than 1e-3 |E_total| of its own record is measured against that floor
+
+
+def record_errors(a, b):
+    """Per-component relative errors of the old/new energy vectors of two record arrays (b = the reference side).
+    err_i = |a_i - b_i| / max(|b_i|, FLOOR_FRAC * |b_total|, 1e-6 K): every component (LJ, real Coulomb, reciprocal,
+    self, intra, total) is held to the tolerance on its OWN magnitude, not on the largest one of the record; the floor only
+    keeps components that are (near) zero next to the record's total from dividing by nothing.
+    Returns (max error over old_e, max over new_e, max relative error of prob)."""
+    out = []
+    for key in ("old_e", "new_e"):
+        x, y = np.asarray(a[key], dtype=float), np.asarray(b[key], dtype=float)
+        if x.size == 0:
+            out.append(0.0); continue
+        scale = np.maximum(np.maximum(np.abs(y), FLOOR_FRAC * np.abs(y[..., 5:6])), 1e-6)
+        out.append(float(np.max(np.abs(x - y) / scale)))
+    pa, pb = np.asarray(a["prob"], dtype=float), np.asarray(b["prob"], dtype=float)
+    out.append(float(np.max(np.abs(pa - pb) / np.maximum(pb, 1e-3))) if pa.size else 0.0)
+    return tuple(out)
+
+
+def compare_records(a, b, tol=REL_TOL):
+    """identical move sequence and accept/reject decisions; energies per component within `tol`; returns the errors"""
+    assert np.array_equal(a["kind"], b["kind"])
+    assert np.array_equal(a["res"], b["res"]) and np.array_equal(a["mol"], b["mol"])
+    assert np.array_equal(a["accepted"], b["accepted"]), "accept/reject sequence differs"
+    e_old, e_new, e_p = record_errors(a, b)
+    assert e_old < tol, f"old_e per-component relative error {e_old:.3e} >= {tol:g}"
+    assert e_new < tol, f"new_e per-component relative error {e_new:.3e} >= {tol:g}"
+    assert e_p < 1e-9, f"acceptance probability relative error {e_p:.3e}"
+    return e_old, e_new, e_p

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import ideal_mixture, load_system, rel_err
+from conftest import compare_records, ideal_mixture, load_system, rel_err
 from maniac_mc_b200 import builders
 from maniac_mc_b200.driver import StrictDriver, TapeRng
 from maniac_mc_b200.lib import ManiacGPU, ManiacGpuError
@@ -16,16 +16,6 @@ from oracle import oracle as orc
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-10   # BASELINE.json north_star: energies within 1e-10 relative in FP64
-
-
-def compare_records(a, b, tol=TOL):
-    assert np.array_equal(a["kind"], b["kind"])
-    assert np.array_equal(a["res"], b["res"]) and np.array_equal(a["mol"], b["mol"])
-    assert np.array_equal(a["accepted"], b["accepted"]), "accept/reject sequence differs"
-    scale = np.maximum(np.abs(b["new_e"]).max(axis=1, keepdims=True), 1.0)
-    assert np.max(np.abs(a["old_e"] - b["old_e"]) / scale) < tol
-    assert np.max(np.abs(a["new_e"] - b["new_e"]) / scale) < tol
-    assert np.max(np.abs(a["prob"] - b["prob"])) < 1e-8
 
 
 @pytest.mark.parametrize("name", ["lj_gas", "h2o_gas", "h2o_ads", "zif8_h2o", "mfi_co2", "slit", "zif8_ch4o_h2o"])

@@ -24,10 +24,17 @@ def test_rows_follow_write_energy_and_count():
     want = "%10d %16.6f %16.6f %16.6f %16.6f %16.6f %16.6f" % (3, -1025 * k, 50 * k, 100 * k, -200 * k, -1000 * k, 25 * k)
     assert row == want and len(row) == 10 + 6 * 17
     assert W.number_row(12, 345) == "        12        345"
-    ctr = [1, 2, 3, 4, 5, 6, 7, 8, 0, 0]   # translations, trial_t, rotations, trial_r, creations, trial_c, deletions, trial_d
+    # mmc_counters struct order: translations, rotations, creations, deletions, then the four trial counts, swaps, trial_swaps
+    ctr = [1, 3, 5, 7, 2, 4, 6, 8, 0, 0]
     lit = W.moves_row(9, ctr).split()
-    assert lit == ["9", "2", "1", "6", "5", "8", "7", "4", "7"]            # last column repeats the deletions (:186)
+    # write_utils.f90:182-186: trial_translations, translations, trial_creations, creations, trial_deletions, deletions,
+    # trial_rotations, deletions (the last column repeats the deletions)
+    assert lit == ["9", "2", "1", "6", "5", "8", "7", "4", "7"]
     assert W.moves_row(9, ctr, literal=False).split()[-1] == "3"
+    by_name = dict(zip(W.COUNTER_FIELDS, ctr))
+    assert W.moves_row(9, by_name) == W.moves_row(9, ctr)
+    from maniac_mc_b200.system import Counters
+    assert tuple(f for f, _ in Counters._fields_) == W.COUNTER_FIELDS      # the row is indexed by the struct's own order
     assert len(W.moves_row(9, ctr)) == 9 * 12 + 8
     assert W.MOVES_HEADER.split()[1:] == ["Block", "Trial_Trans", "Trans_Moves", "Trial_Create", "Create_Moves", "Trial_Delete",
                                           "Delete_Moves", "Trial_Rotate", "Rotate_Moves", "Trial_BigMove", "Big_Moves"]

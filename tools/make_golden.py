@@ -34,10 +34,29 @@ CASES = {
 #   tests/integration/energy/LJ-gas/run-test.sh:18 parses TotEng from
 #   mc-topology/testcase-energy/LJ-gas/log.lammps:79-80  ("0 -38.589253 -0.40707303 49.708669 -87.890849")
 #   tests/integration/energy/H2O-gas/run-test.sh:15-16   (ref_energy=-32.822927, tolerance=0.01)
+#   mc-topology/testcase-adsorption/DIPOLE-orthorhombic/log.lammps:115: step 0 of LAMMPS' own GCMC run of the TILTED cell
+#   (triclinic box (-20 -20 -20) to (20 20 20) with tilt (-20 -20 20), 142 atoms = 71 dipoles, ewald 1e-5, kmax 6 6 6,
+#   gewald 0.1622) "0  -2.8812361  -1.2645192  40.097413  -41.71413  71"; its starting configuration is the 142-atom
+#   testcase-energy/DIPOLE-orthorhombic/dipole.data (fixture dipole_tri).  No reference script asserts it; the tolerance
+#   is the one the reference's energy tests use (run-test.sh: 0.01 kcal/mol)
+#   mc-topology/testcase-adsorption/H2O/number.dat:3-103: N(H2O) of LAMMPS fix gcmc at 0.5 atm, 300 K, 101 samples
 KAT = {
     "lj_gas": {"TotEng": -38.589253, "E_vdwl": -0.40707303, "E_coul": 49.708669, "E_long": -87.890849, "tolerance": 0.01},
     "h2o_gas": {"TotEng": -32.822927, "tolerance": 0.01},
+    "dipole_tri": {"TotEng": -2.8812361, "E_vdwl": -1.2645192, "E_coul": 40.097413, "E_long": -41.71413, "N": 71, "tolerance": 0.01},
 }
+
+
+def lammps_number_series(path):
+    """second column of a LAMMPS `fix ave/time`-style number.dat (comment lines skipped)"""
+    out = []
+    for ln in open(path):
+        f = ln.split()
+        if not f or f[0].startswith("#"):
+            continue
+        out.append(float(f[1]))
+    return out
+
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
@@ -46,5 +65,7 @@ if __name__ == "__main__":
         s.save(os.path.join(OUT, name + ".npz"))
         print(name, "counts", s.count.tolist(), "natoms", s.natoms.tolist(), "alpha %.6f" % s.alpha, "kmax", s.kmax,
               "K", s.num_kvectors, "L", s.box_len.tolist())
+    KAT["h2o_ads_gcmc"] = {"source": "mc-topology/testcase-adsorption/H2O/number.dat:3-103 (LAMMPS fix gcmc, 0.5 atm, 300 K)",
+                           "N": lammps_number_series(os.path.join(REF, "testcase-adsorption/H2O/number.dat"))}
     with open(os.path.join(OUT, "reference_kat.json"), "w") as fh:
         json.dump(KAT, fh, indent=1)
