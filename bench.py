@@ -163,6 +163,7 @@ class CpuSample:
         self.oracles = [Oracle(cpu) for _ in range(n_threads)]
         for i, o in enumerate(self.oracles):   # the isotherm's fugacity points of chains 0 .. n_threads-1, as the GPU arm's chains
             o.set_params(chain_fugacity(s, i), s.temperature)
+            o.prepare_fourier()                # every molecule's phase tables (ComputeAllFourierTerms) without the O(N K) sums
         self.step0 = 0
 
     def run(self, moves):

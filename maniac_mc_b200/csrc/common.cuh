@@ -65,8 +65,8 @@ struct DevConst {
     const int* stype;
     const double* tbox;            // [6][n_tiles]
     int n_tiles;
-    const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
-    int gtab_base;                 // segment index of s = gtab_smin
+    const double* gtab;            // [(MMC_GTAB_DEG+1)][gtab_stride] Coulomb kernel table for this alpha
+    int gtab_base, gtab_stride;    // segment index of s = gtab_smin; segments in use = row stride
     double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
     // reciprocal work items (build_sweep_layout): one per (kx, ky) row and kz >= 0, serving k(+kz) and k(-kz).
     // .x = kx | (ky+kmax_y)<<10 | kz<<21 | flag<<31, .y = index of k(+kz); index of k(-kz) = .y - 2 kz + flag
@@ -196,29 +196,45 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
 }
 
 // ---- real-space Coulomb kernel g(s) = erfc(alpha sqrt(s)) / sqrt(s), s = r^2 ----------------------------
-// Piecewise degree-9 polynomials on segments that follow the binary representation of s: 8 segments per
-// octave (exponent + top 3 mantissa bits select the segment, the remaining mantissa bits give the local
+// Piecewise degree-MMC_GTAB_DEG polynomials on segments that follow the binary representation of s: 2^MMC_GTAB_MBITS segments
+// per octave (exponent + top mantissa bits select the segment, the remaining mantissa bits give the local
 // variable t in [-1, 1)), built at mmc_init for this system's alpha in long double (build_coulomb_table,
 // maniac_gpu.cu).  Absolute error <= 5e-16 (it is at the rounding floor of the coefficients), i.e. a few
 // 1e-16 relative where the terms matter (alpha r < 1.5) -- no sqrt, no exp, no division per pair.
 // Reciprocal update of a translation as S_mol(k) (e^{i k d} - 1) (kernels_sweep.cuh, stage_terms): n + 1 product terms
 // instead of 2 n.  On by default (A/B on one box: +1.5 %); -DMMC_NO_FACTORED_TRANSLATION restores the 2 n terms.
-#ifndef MMC_NO_FACTORED_TRANSLATION
+// Reciprocal sweep implementation (kernels_sweep.cuh): default = rank-n_term update dS(row, kz) = sum_t P_t(row) Z_t(kz) on
+// the FP64 MMA unit (DMMA m8n8k4: the operands live in register fragments, so the per-term shared-memory loads of the
+// item loop disappear); -DMMC_RECIP_ITEMS builds the round-1 item loop (one (kx, ky, +-kz) item per thread, P and Z from
+// shared memory per term) for A/B runs.
+#ifndef MMC_RECIP_ITEMS
+#define MMC_RECIP_DMMA 1
+#endif
+#if !defined(MMC_NO_FACTORED_TRANSLATION) && !defined(MMC_RECIP_DMMA)
 #define MMC_FACTORED_TRANSLATION 1
 #endif
-#define MMC_GTAB_DEG 9
-#define MMC_GTAB_MBITS 3
-#define MMC_GTAB_MAXSEG 128   // also the row stride: layout [degree][segment]
+// Round 2: degree 8 on 16 segments per octave (was degree 9 on 8): measured against 40-digit values over r = 1.5 .. 37 A the
+// relative error for r < 10 A drops from 6.1e-16 rms / 3.3e-15 max to 9e-17 rms / 2.7e-16 max (the rounding floor; glibc's
+// erfc(x)/r, the CPU checker's kernel, sits at 3.2e-16 rms), with ONE coefficient load fewer per pair
+// (tools/coulomb_table_accuracy.py); -DMMC_GTAB_DEG=9 -DMMC_GTAB_MBITS=3 rebuilds the round-1 table.
+#ifndef MMC_GTAB_DEG
+#define MMC_GTAB_DEG 8
+#endif
+#ifndef MMC_GTAB_MBITS
+#define MMC_GTAB_MBITS 4
+#endif
+#define MMC_GTAB_MAXSEG (16 << MMC_GTAB_MBITS)   // 16 octaves; also the row stride: layout [degree][segment]
 __device__ __noinline__ double coul_kernel_slow(double s, double alpha) { const double r = sqrt(s); return erfc(alpha * r) / r; }
-__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base) {
+__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base, int stride) {
     const int hi = __double2hiint(s), lo = __double2loint(s);
     const int idx = (hi >> (20 - MMC_GTAB_MBITS)) - base;
     const double f = __hiloint2double(0x3FF00000 | ((hi & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
                                           (int)((unsigned)lo >> (32 - MMC_GTAB_MBITS)), lo << MMC_GTAB_MBITS);
     const double t = fma(2.0, f, -3.0);
-    double p = tab[MMC_GTAB_DEG * MMC_GTAB_MAXSEG + idx];
+    const double* c = tab + idx;
+    double p = c[MMC_GTAB_DEG * stride];
 #pragma unroll
-    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, tab[d * MMC_GTAB_MAXSEG + idx]);
+    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, c[d * stride]);
     return p;
 }
 // 1/a: MUFU.RCP64H seed + two Newton steps

@@ -35,8 +35,16 @@ struct SweepCtx {
     double* gtab;    // [MMC_GTAB_DEG+1][MMC_GTAB_MAXSEG] Coulomb kernel table
     double2* lj;     // [max_nat][ntypes] {sigma^2, 4 eps} rows of the moved molecule's atom types
     double2 *X, *Y;  // [2 max_nat][nx | ny] 1-D phase tables, one row per reciprocal term
+#ifdef MMC_RECIP_DMMA
+    // q_t Z_t(kz), kz >= 0 only, as two real planes [tpad][zS] (term-major): the A operand of the FP64 MMA of the
+    // reciprocal sweep.  tpad = terms padded to a multiple of 4, zS = row stride (kz padded to a multiple of 8, + 4: bank
+    // spread of the fragment load, recip_zstride); the pads that are read are zero.
+    double *ZR, *ZI;
+    int tpad, zS, nzb;    // nzb = blocks of 8 kz
+#else
     double2* Z;      // [kmax_z + 1][zs] q_t Z_t(kz), kz >= 0 only, term fastest; zs = 2 max_nat + 1 (odd: no bank conflicts)
     double2* XY;     // [2 buffers][threads / 4 rows][zs] products X_t(kx) Y_t(ky) of a chunk of (kx, ky) rows, term fastest
+#endif
     uint32_t* mask;  // [CULL_CHUNK / 32]
     int* prefix;     // [CULL_CHUNK / 32]
     uint16_t* list;  // [CULL_CHUNK]
@@ -45,40 +53,63 @@ struct SweepCtx {
     int nx, ny, nz, zs;   // nz = kmax_z + 1
 };
 
-__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[10]) {
+__host__ __device__ inline int recip_tpad(int max_nat) { return ((2 * max_nat + 3) / 4) * 4; }
+__host__ __device__ inline int recip_zstride(int kmax_z) {
+    // kz padded to a multiple of 8, plus 4: stride = 4 or 12 (mod 16) doubles, so that the 16 lanes of a half warp
+    // (4 terms x 4 kz, an 8-byte load is served per half warp) fall into 16 distinct 8-byte bank pairs
+    return ((kmax_z + 1 + 7) / 8) * 8 + 4;
+}
+__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int gtab_stride, int threads, size_t off[10]) {
     size_t o = 0;
     const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = kmax[2] + 1, zs = 2 * max_nat + 1;
-    off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
+    off[0] = o; o += ((size_t)(MMC_GTAB_DEG + 1) * gtab_stride * sizeof(double) + 15) / 16 * 16;
     off[1] = o; o += (size_t)max_nat * ntypes * sizeof(double2);
     off[2] = o; o += (size_t)2 * max_nat * nx * sizeof(double2);
     off[3] = o; o += (size_t)2 * max_nat * ny * sizeof(double2);
+#ifdef MMC_RECIP_DMMA
+    off[4] = o; o += (size_t)2 * recip_tpad(max_nat) * recip_zstride(kmax[2]) * sizeof(double);
+    (void)nz; (void)zs;
+#else
     off[4] = o; o += (size_t)nz * zs * sizeof(double2);
+#endif
     off[5] = o; o += (size_t)6 * (threads / 32) * sizeof(double);
     off[6] = o; o += (sizeof(MolS) + 15) / 16 * 16;
     off[7] = o; o += (CULL_CHUNK / 32) * sizeof(uint32_t) * 2;
     off[8] = o; o += CULL_CHUNK * sizeof(uint16_t);
     o = (o + 15) / 16 * 16;
+#ifdef MMC_RECIP_DMMA
+    off[9] = o; (void)threads;     // no staging buffer: the (kx, ky) products are formed in registers
+#else
     off[9] = o; o += (size_t)2 * (threads / 4) * zs * sizeof(double2);
+#endif
     return o;
 }
 
 __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned char* smem, int threads) {
     size_t off[10];
-    sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
+    sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, threads, off);
     SweepCtx s;
     s.gtab = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
-    s.X = (double2*)(smem + off[2]); s.Y = (double2*)(smem + off[3]); s.Z = (double2*)(smem + off[4]);
+    s.X = (double2*)(smem + off[2]); s.Y = (double2*)(smem + off[3]);
+#ifdef MMC_RECIP_DMMA
+    s.tpad = recip_tpad(dc.max_nat); s.zS = recip_zstride(dc.kmax[2]); s.nzb = (dc.kmax[2] + 8) >> 3;
+    s.ZR = (double*)(smem + off[4]); s.ZI = s.ZR + (size_t)s.tpad * s.zS;
+#else
+    s.Z = (double2*)(smem + off[4]);
+#endif
     s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]);
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
     s.list = (uint16_t*)(smem + off[8]);
+#ifndef MMC_RECIP_DMMA
     s.XY = (double2*)(smem + off[9]);
+#endif
     s.nx = dc.kmax[0] + 1; s.ny = 2 * dc.kmax[1] + 1; s.nz = dc.kmax[2] + 1; s.zs = 2 * dc.max_nat + 1;
     return s;
 }
 
 // once per kernel: the Coulomb kernel table
 __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const SweepCtx& s) {
-    for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG; i += blockDim.x) s.gtab[i] = dc.gtab[i];
+    for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * dc.gtab_stride; i += blockDim.x) s.gtab[i] = dc.gtab[i];
 }
 
 // Stages the moved molecule of the pending Trial of chain c for the real-space sweep: positions, charges, LJ rows,
@@ -87,7 +118,7 @@ __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const Swee
 //   pass 0: both sets in one sweep (every move but the swap)
 //   pass 1: swap, removed molecule only (old geometry)      pass 2: swap, inserted molecule only (new geometry)
 // All threads; ends with a barrier.
-__device__ inline void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int pass) {
+__device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int pass) {
     const Trial& t = cs.trial[c];
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
@@ -146,7 +177,7 @@ __device__ inline void stage_molecule(const DevConst& dc, const ChainState& cs, 
 // sign folded into Z.  Added atoms come from the NEW set (p_plus, q2), removed atoms from the OLD set (p_old, q).
 // All threads; ends with a barrier.
 template <bool TRI>
-__device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
+__device__ __forceinline__ void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
     const Trial& t = cs.trial[c];
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
@@ -172,6 +203,34 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
     __syncthreads();
     if (t.kind <= 0) return;
     const int nterm = m.nterm;
+#ifdef MMC_RECIP_DMMA
+    // X and Y rows of the nterm terms, then the two Z planes over the PADDED (term, kz) range the MMA fragments read:
+    // terms up to the next multiple of 4 and kz up to the next multiple of 8 are written as zeros
+    // (at least one K-block of 4 terms is always read, also when no charged atom moves: its pads must be zeros, not stale data)
+    const int nxy = s.nx + s.ny, kb4 = max(4, (nterm + 3) & ~3), nzp = s.nzb * 8;
+    for (int i = tid; i < nterm * nxy + kb4 * nzp; i += blockDim.x) {
+        int term, j, ax, k; double2* dst = nullptr; double *dr = nullptr, *di = nullptr;
+        if (i < nterm * nxy) {
+            term = i / nxy; j = i - term * nxy;
+            if (j < s.nx) { ax = 0; k = j; dst = s.X + term * s.nx + j; }
+            else { j -= s.nx; ax = 1; k = j - dc.kmax[1]; dst = s.Y + term * s.ny + j; }
+        } else {
+            const int u = i - nterm * nxy;
+            term = u / nzp; k = u - term * nzp; ax = 2;
+            dr = s.ZR + term * s.zS + k; di = s.ZI + term * s.zS + k;
+            if (term >= nterm || k >= s.nz) { *dr = 0.0; *di = 0.0; continue; }
+        }
+        const int ta = m.term[term];
+        const bool plus = ta > 0;
+        const int a = (plus ? ta : -ta) - 1;
+        const double* pp = plus ? t.p_plus[a] : t.p_old[a];
+        const double theta = MMC_TWOPI * (TRI ? frac_coord(dc, pp, ax) : dc.invL[ax] * pp[ax]);
+        double sn, co; sincos((double)(k < 0 ? -k : k) * theta, &sn, &co);
+        if (k < 0) sn = -sn;
+        if (ax == 2) { const double q = plus ? t.q2[a] : -t.q[a]; *dr = co * q; *di = sn * q; }
+        else *dst = make_double2(co, sn);
+    }
+#else
     const int per = s.nx + s.ny + s.nz;
     for (int i = tid; i < nterm * per; i += blockDim.x) {
         const int term = i / per; int j = i % per;
@@ -198,17 +257,18 @@ __device__ inline void stage_terms(const DevConst& dc, const ChainState& cs, int
         }
         *dst = make_double2(co, sn);
     }
+#endif
     __syncthreads();
 }
 
 // ----------------------------------------------------------------------------------------------
-struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase; };
+struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase, gstride; };
 
 // one (moved atom, other atom) pair at one geometry; SHIFT: the other atom was already moved to the periodic
 // image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
 template <bool SHIFT, bool TRI>
 __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc, const double* s_gtab, double dx, double dy, double dz,
-                                         double qq, bool charged, double2 lj, double& e_lj, double& e_c, unsigned& n_in) {
+                                         double qq, bool charged, double2 lj, double& e_lj, double& e_c, unsigned& work) {
     if (!SHIFT) {
         if (TRI) min_image_tri(dc, dx, dy, dz);
         else {
@@ -219,10 +279,10 @@ __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc
     }
     const double r2 = fma(dx, dx, fma(dy, dy, dz * dz));
     if (r2 < pc.reach2) {
-        n_in++;
+        work += 0x10000u;
         if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
             double g;
-            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase);
+            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase, pc.gstride);
             else g = coul_kernel_slow(r2, pc.alpha);
             e_c = fma(qq, g, e_c);
         }
@@ -238,7 +298,7 @@ __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc
 // TRI: tilted cell; the OLD / NEW sets are then also masked at run time (one instantiation serves every move type)
 template <bool OLD, bool NEW, bool SHIFT, bool TRI>
 __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
-                                          double qj, int tj, double (&acc)[4], unsigned (&cnt)[2]) {
+                                          double qj, int tj, double (&acc)[4], unsigned& cnt) {
     const MolS& m = *s.mol;
     if (SHIFT) {
         double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
@@ -264,9 +324,9 @@ __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& p
         const double2 lj = s.lj[a * ntypes + tj];
         if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
-        cnt[0] += (use_old ? 1u : 0u) + (use_new ? 1u : 0u);
-        if (use_old) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt[1]);
-        if (use_new) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt[1]);
+        cnt += (use_old ? 1u : 0u) + (use_new ? 1u : 0u);
+        if (use_old) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt);
+        if (use_new) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt);
     }
 }
 
@@ -307,12 +367,12 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
 // result, so the item -> warp assignment and hence the summation order is deterministic) followed by tiles
 // of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
 template <int NT, bool OLD, bool NEW, bool SHIFT, bool TRI>
-__device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                    double (&acc)[4], unsigned (&cnt)[2]) {
+__device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                    double (&acc)[4], unsigned& cnt) {
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
-    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base};
+    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base, dc.gtab_stride};
     const bool cull = dc.reach2 < 1e300;
     int item0 = 0;
     for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
@@ -372,8 +432,8 @@ __device__ inline void pair_phase_t(const DevConst& dc, const ChainState& cs, in
 }
 
 template <int NT, bool TRI>
-__device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                  double (&acc)[4], unsigned (&cnt)[2]) {
+__device__ __forceinline__ void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                  double (&acc)[4], unsigned& cnt) {
     const MolS& m = *s.mol;
     if (m.kind <= 0) return;
     const bool sh = m.shift_ok && dc.reach2 < 1e300;
@@ -388,6 +448,147 @@ __device__ inline void pair_phase(const DevConst& dc, const ChainState& cs, int 
 }
 
 // ----------------------------------------------------------------------------------------------
+#ifdef MMC_RECIP_DMMA
+// Reciprocal phase on the FP64 MMA unit.
+//
+// The k list is ordered (kx, ky, kz) with kz fastest, so all k of one (kx, ky) "row" are contiguous (kz = -m .. m; row (0, 0)
+// lacks kz = 0) and the update of a row is a rank-n_term product
+//     dS(row, kz) = sum_t P_t(row) Z_t(kz),   P_t = X_t(kx) Y_t(ky),   Z_t = q_t e^{i kz theta_z,t}.
+// With the real and imaginary parts spread over the MMA's rows and columns, ONE pair of DMMA m8n8k4 instructions per 4 terms
+// gives every lane the four real product sums of "its" (row, kz):
+//     A operand (8 x 4) = Zr or Zi for 8 consecutive kz (rows) x 4 terms        -> fragment = 1 double per lane
+//     B operand (4 x 8) = 4 terms x (4 rows x {Pr, Pi})                          -> fragment = 1 double per lane
+//     C (8 x 8): lane (g = lane / 4, t = lane % 4) holds C[g][2t], C[g][2t + 1]  = sum_t Z(kz_g) . (Pr, Pi)(row_t)
+//     with A = Zr: (s1, s4) = (sum Zr Pr, sum Zr Pi);   with A = Zi: (s3, s2) = (sum Zi Pr, sum Zi Pi)
+// and sum P Z = (s1 - s2, s3 + s4) updates k(+kz), sum P conj(Z) = (s1 + s2, s4 - s3) updates k(-kz) (Z(-kz) = conj Z(kz)).
+// The operands sit in register fragments: per 4 rows x 8 kz x (+-) = 64 k-vectors the warp issues four 8-byte shared loads
+// (the A fragments) instead of two 16-byte loads per TERM per 2 k-vectors in the round-1 item loop, whose P / Z loads were
+// 40 % of the kernel's shared-memory wavefronts (profiles/r1t_ncu_lines.txt).  The B fragments (the (kx, ky) products) are
+// formed in registers from the 1-D tables once per 4-row group; nothing is staged per chunk and the phase has NO barrier:
+// every warp walks its own row groups.  A is read and A' written exactly as before (A' goes to the other half of the
+// double buffer); acc[0] += f W |A|^2, acc[1] += f W |A'|^2.
+// The MMA is used as an operand-sharing device for a rank-4..8 update, not to reach tensor-core flops: the phase stays
+// HBM-bound (40 B per k-eval) and tcgen05 has no FP64 kind.
+__device__ __forceinline__ void dmma_884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// B fragment of K-block kb for the 4-row group starting at row rg: lane (g, t) supplies term 4 kb + t, row rg + g / 2,
+// component g % 2 of P = X(kx) Y(ky)
+__device__ __forceinline__ double recip_bfrag(const SweepCtx& s, int nterm, int term, bool row_ok, int ix, int iy, int comp) {
+    if (!row_ok || term >= nterm) return 0.0;
+    const double2 X = s.X[term * s.nx + ix], Y = s.Y[term * s.ny + iy];
+    return comp ? fma(X.x, Y.y, X.y * Y.x) : fma(X.x, Y.x, -X.y * Y.y);
+}
+
+// KB > 0: the B fragments of KB K-blocks stay in registers for the whole group (n_term <= 4 KB); KB == 0: generic, any n_term,
+// B fragments re-formed per kz block.  SPLIT: work unit = (group, kz block) instead of a whole group (few rows per CTA:
+// strict mode and the k-sharded / cluster sweeps), otherwise a unit = one group and the kz blocks are walked inside.
+template <int KB, bool TRI, bool SPLIT>
+__device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx& s, const double2* __restrict__ A, double2* __restrict__ An,
+                                             int r0, int r1, int unit0, int ustride, int nterm, double (&acc)[2]) {
+    const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int ngroups = (r1 - r0 + 3) >> 2, nzb = s.nzb;
+    const int nunits = SPLIT ? ngroups * nzb : ngroups;
+    const int kbn = (nterm + 3) >> 2;
+    for (int u = unit0; u < nunits; u += ustride) {
+        const int q = SPLIT ? u / nzb : u;
+        const int rg = r0 + 4 * q;
+        // the row this lane updates: k range [k0, k1) = kz -m .. m
+        const int r = rg + t;
+        int k0 = 0, n = 0;
+        if (r < r1) { k0 = dc.row_kstart[r]; n = dc.row_kstart[r + 1] - k0; }
+        const int m = n >> 1, has0 = n & 1;
+        const int mmax = __reduce_max_sync(0xffffffffu, n > 0 ? m : -1);
+        if (mmax < 0) continue;                                   // four empty rows (outside the k sphere)
+        const int jlo = SPLIT ? u - q * nzb : 0, jhi = SPLIT ? jlo + 1 : (mmax >> 3) + 1;
+        if (SPLIT && 8 * jlo > mmax) continue;
+        if (!SPLIT && lane == 0) {
+            // pull the group this warp takes next from HBM into L2 while this one is computed: one bulk prefetch (no LSU
+            // data wavefronts, unlike a prefetch per line)
+            const int rn = rg + 4 * ustride;
+            if (rn < r1) {
+                const int ka = dc.row_kstart[rn], kb = dc.row_kstart[min(r1, rn + 4)];
+                if (kb > ka) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + ka), "r"((kb - ka) * 16) : "memory");
+            }
+        }
+        // B fragments: row rg + g / 2, component g % 2
+        const int rb = rg + (g >> 1);
+        const bool rb_ok = rb < r1;
+        const int ix = rb_ok ? rb / s.ny : 0, iy = rb_ok ? rb - ix * s.ny : 0;
+        double bf[KB > 0 ? KB : 1];
+        if (KB > 0) {
+#pragma unroll
+            for (int kb = 0; kb < KB; kb++) bf[kb] = recip_bfrag(s, nterm, 4 * kb + t, rb_ok, ix, iy, g & 1);
+        }
+        const int base_p = k0 + m - (1 - has0);                   // k(+kz) = base_p + kz, k(-kz) = k0 + m - kz
+        for (int j = jlo; j < jhi; j++) {
+            const int kz = 8 * j + g;
+            double s1 = 0.0, s4 = 0.0, s3 = 0.0, s2 = 0.0;
+            const double* zr = s.ZR + t * s.zS + kz;
+            const double* zi = s.ZI + t * s.zS + kz;
+            if (KB > 0) {
+#pragma unroll
+                for (int kb = 0; kb < KB; kb++) {
+                    dmma_884(s1, s4, zr[4 * kb * s.zS], bf[kb]);
+                    dmma_884(s3, s2, zi[4 * kb * s.zS], bf[kb]);
+                }
+            } else {
+                for (int kb = 0; kb < kbn; kb++) {
+                    const double b = recip_bfrag(s, nterm, 4 * kb + t, rb_ok, ix, iy, g & 1);
+                    dmma_884(s1, s4, zr[4 * kb * s.zS], b);
+                    dmma_884(s3, s2, zi[4 * kb * s.zS], b);
+                }
+            }
+            if (kz <= m && (kz >= 1 || has0)) {
+                const int kpl = base_p + kz, kmi = k0 + m - kz;
+                const bool two = kz != 0;
+                const double2 ap = A[kpl];
+                const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
+                const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz in an orthorhombic cell
+                const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
+                An[kpl] = bp;
+                acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
+                acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
+                if (two) {
+                    const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
+                    An[kmi] = bm;
+                    const double wm = TRI ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
+                    acc[0] = fma(wm, fma(am.x, am.x, am.y * am.y), acc[0]);
+                    acc[1] = fma(wm, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
+                }
+            }
+        }
+    }
+}
+
+template <int NT, bool TRI>
+__device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+                                   double (&acc)[2]) {
+    const MolS& m = *s.mol;
+    if (m.kind <= 0) return;
+    const int nterm = m.nterm;
+    if (nterm == 0) {
+        // no charged atom moved: A' = A.  The energies are still summed and A copied (the reference re-sums it, ewald_energy.f90:259-272)
+    }
+    const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
+    double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
+    const int nrows = s.nx * s.ny;
+    const int rpp = (nrows + n_parts - 1) / n_parts;
+    const int r0 = min(nrows, part * rpp), r1 = min(nrows, r0 + rpp);
+    if (r0 >= r1) return;
+    const int warp = threadIdx.x >> 5;
+    if (n_parts > 1) {   // few rows per CTA: spread (group, kz block) units over the warps
+        if (nterm <= 4) recip_groups<1, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+        else if (nterm <= 8) recip_groups<2, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+        else recip_groups<0, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+    } else {
+        if (nterm <= 4) recip_groups<1, TRI, false>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+        else if (nterm <= 8) recip_groups<2, TRI, false>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+        else recip_groups<0, TRI, false>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
+    }
+}
+#else   // MMC_RECIP_ITEMS: the round-1 item loop
 // Reciprocal phase.  The k list is ordered (kx, ky, kz) with kz fastest, so all k of one (kx, ky) "row" are
 // contiguous and share the product X_t(kx) Y_t(ky).  The rows (flattened index kx*ny + ky+kmax_y) are walked in
 // chunks of NT/4: the chunk's products are staged in shared memory (double buffered: the next chunk is staged
@@ -465,7 +666,7 @@ __device__ __forceinline__ void recip_items(const DevConst& dc, const SweepCtx& 
 }
 
 template <int NT, bool TRI>
-__device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
+__device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
                                    double (&acc)[2]) {
     constexpr int RMAX = NT / 4;
     const MolS& m = *s.mol;
@@ -518,6 +719,8 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
     }
 }
 
+#endif  // MMC_RECIP_DMMA
+
 // One trial of chain c, all threads of the CTA: stage, real-space sweep(s), reciprocal sweep.  `part` of `n_parts`
 // CTAs share the trial (1 of 1 in batched mode).  phases: bit 0 real space, bit 1 reciprocal.
 // Result: s.mol->sums = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} of this CTA (block sums in a
@@ -525,20 +728,20 @@ __device__ inline void recip_phase(const DevConst& dc, const ChainState& cs, int
 // the reciprocal sweep so that its item loop does not carry them in registers (64 registers per thread at 4 CTAs/SM).
 // TRI: compiled for tilted cells (dc.tri); the orthorhombic kernels carry none of that code
 template <int NT, bool TRI>
-__device__ inline void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts, int phases) {
+__device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts, int phases) {
     const bool swap = cs.trial[c].kind == MMC_SWAP;
     stage_terms<TRI>(dc, cs, c, s);
     stage_molecule(dc, cs, c, s, swap ? 1 : 0);
     {
         double pa[4] = {0, 0, 0, 0};
-        unsigned cnt[2] = {0u, 0u};
+        unsigned cnt = 0u;   // executed work of this thread in this trial: low 16 bits = distances formed, high 16 = pairs inside reach
         if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
         if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
             __syncthreads();
             stage_molecule(dc, cs, c, s, 2);
             if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
         }
-        const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt[0]), w1 = __reduce_add_sync(0xffffffffu, cnt[1]);
+        const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt & 0xffffu), w1 = __reduce_add_sync(0xffffffffu, cnt >> 16);
         if ((threadIdx.x & 31) == 0 && (w0 | w1)) { atomicAdd(&s.mol->work[0], w0); atomicAdd(&s.mol->work[1], w1); }
         block_sum<4, NT>(pa, s.red);
         if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];

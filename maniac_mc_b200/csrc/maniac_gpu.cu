@@ -198,14 +198,15 @@ static uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) {
 // Coulomb kernel table (common.cuh coul_kernel_tab): g(s) = erfc(alpha sqrt(s))/sqrt(s) on segments
 // [2^e (1 + j/8), 2^e (1 + (j+1)/8)), degree-9 interpolation at Chebyshev nodes solved in long double.
 // Domain: s_min (0.25 A^2, raised if more than MMC_GTAB_MAXSEG segments would be needed) to (xmax/alpha)^2.
-static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out) {
+static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out, int* stride_out) {
     const int D = MMC_GTAB_DEG, M = MMC_GTAB_MBITS, NS = 1 << M;
     const double smax = (xmax / alpha) * (xmax / alpha);
     int e_hi = 0; std::frexp(smax, &e_hi);   // smax in [2^(e_hi-1), 2^e_hi)
-    int e_lo = -2;
+    int e_lo = 0;   // s >= 1 A^2: closer pairs (overlapping insertions only) take coul_kernel_slow
     while ((e_hi - e_lo) * NS > MMC_GTAB_MAXSEG) e_lo++;
     const int nseg = (e_hi - e_lo) * NS;
-    tab.assign((size_t)(D + 1) * MMC_GTAB_MAXSEG, 0.0);
+    tab.assign((size_t)(D + 1) * nseg, 0.0);   // layout [degree][segment], row stride = the segments in use
+    *stride_out = nseg;
     const long double pi = 3.14159265358979323846264338327950288L;
     long double nodes[D + 1];
     for (int k = 0; k <= D; k++) nodes[k] = cosl(pi * (2 * k + 1) / (2.0L * (D + 1)));
@@ -228,7 +229,7 @@ static void build_coulomb_table(double alpha, double xmax, std::vector<double>& 
                 for (int k = c; k <= D + 1; k++) V[r][k] -= f * V[c][k];
             }
         }
-        for (int c = 0; c <= D; c++) tab[(size_t)c * MMC_GTAB_MAXSEG + seg] = (double)(V[c][D + 1] / V[c][c]);
+        for (int c = 0; c <= D; c++) tab[(size_t)c * nseg + seg] = (double)(V[c][D + 1] / V[c][c]);
     }
     const double smin = std::ldexp(1.0, e_lo);
     union { double d; uint64_t u; } cv; cv.d = smin;
@@ -293,7 +294,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     dc.sx = px; dc.sy = py; dc.sz = pz; dc.sq = pq; dc.stype = pt; dc.tbox = pb; dc.n_tiles = n_tiles;
     {
         std::vector<double> tab;
-        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax);
+        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax, &dc.gtab_stride);
         CK(dalloc(h, &pe, tab.size())); CK(cudaMemcpy(pe, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
         dc.gtab = pe;
     }
@@ -358,9 +359,9 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     const int work = std::max((dc.nk + 511) / 512, (n_tiles + dc.g_atoms / TILE + 15) / 16);
     dc.sweep_parts = std::max(1, std::min(2 * h->n_sm, work));
     size_t off[10];
-    h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, SWEEP_THREADS, off);
+    h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, SWEEP_THREADS, off);
     h->chain_threads = dc.n_chains >= 3 * h->n_sm ? 256 : dc.n_chains >= 3 * h->n_sm / 2 ? 512 : 1024;
-    h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
+    h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, h->chain_threads, off);
     if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
                                                  dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
     CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));

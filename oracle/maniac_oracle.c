@@ -634,6 +634,19 @@ void orc_system_energy(orc_t* o, double out[MMC_NE]) {
     if (out) memcpy(out, o->energy, sizeof(double) * MMC_NE);
 }
 
+/* The set-up half of ComputeEwaldRecip (energy_utils.f90:270-287) WITHOUT the O(N K) amplitude sum and without the pair
+ * sweep: W(k) and every molecule's 1-D phase tables (ComputeAllFourierTerms, ewald_phase.f90:340-356), tracked A(k) = 0,
+ * tracked energies = 0.  With the reference's default (Q1: A(k) is never stored at start-up) the per-move records depend on
+ * the start-up only through the tracked energies, so a chain prepared this way steps exactly like one whose tracked
+ * energies were zeroed after ComputeSystemEnergy -- used where the start-up sums of a 50 000-atom framework (tens of
+ * seconds of CPU) would dominate a bounded sample: bench.py's CPU leg and the bench-system parity runs. */
+void orc_prepare_fourier(orc_t* o) {
+    reciprocal_weights(o);
+    all_fourier_terms(o);
+    memset(o->A, 0, sizeof(cplx) * o->nk);
+    memset(o->energy, 0, sizeof(double) * MMC_NE);
+}
+
 /* ---------------- Monte Carlo bookkeeping, monte_carlo_utils.f90 ------------------------------------ */
 
 static void set_total(double e[MMC_NE], int all) {

@@ -33,6 +33,7 @@ def lib():
         L.orc_create.restype = C.c_void_p; L.orc_create.argtypes = [C.POINTER(MmcDesc)]
         L.orc_destroy.argtypes = [C.c_void_p]
         L.orc_system_energy.argtypes = [C.c_void_p, dp]
+        L.orc_prepare_fourier.argtypes = [C.c_void_p]; L.orc_prepare_fourier.restype = None
         L.orc_num_kvectors.argtypes = [C.c_void_p]
         L.orc_get_kvectors.argtypes = [C.c_void_p, ip, ip, ip, dp, dp]
         L.orc_set_params.argtypes = [C.c_void_p, dp, C.c_double]
@@ -78,6 +79,10 @@ class Oracle:
 
     def system_energy(self):
         out = np.zeros(MMC_NE); lib().orc_system_energy(self.h, _dp(out)); return out
+
+    def prepare_fourier(self):
+        """W(k) + every molecule's phase tables, tracked A(k) and energies zero: the start-up without its O(N K) and O(N^2) sums"""
+        lib().orc_prepare_fourier(self.h)
 
     def energy(self):
         out = np.zeros(MMC_NE); lib().orc_get_energy(self.h, _dp(out)); return out

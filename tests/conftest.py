@@ -48,11 +48,12 @@ def rel_err(a, b, floor=1.0):
 # ---- move-record comparison (GPU vs oracle, oracle vs fixture) ----------------------------------------------------
 REL_TOL = 1e-10    # BASELINE.json north_star: energies within 1e-10 relative in FP64
 FLOOR_FRAC = 1e-3  # a component smaller than 1e-3 |E_total| of its own record is measured against that floor
+FLOOR_K = 1e-6     # absolute floor in Kelvin (all-zero records)
 
 
 def record_errors(a, b):
     """Per-component relative errors of the old/new energy vectors of two record arrays (b = the reference side).
-    err_i = |a_i - b_i| / max(|b_i|, FLOOR_FRAC * |b_total|, 1e-6 K): every component (LJ, real Coulomb, reciprocal,
+    err_i = |a_i - b_i| / max(|b_i|, FLOOR_FRAC * |b_total|, FLOOR_K): every component (LJ, real Coulomb, reciprocal,
     self, intra, total) is held to the tolerance on its OWN magnitude, not on the largest one of the record; the floor only
     keeps components that are (near) zero next to the record's total from dividing by nothing.
     Returns (max error over old_e, max over new_e, max relative error of prob)."""
@@ -61,7 +62,7 @@ def record_errors(a, b):
         x, y = np.asarray(a[key], dtype=float), np.asarray(b[key], dtype=float)
         if x.size == 0:
             out.append(0.0); continue
-        scale = np.maximum(np.maximum(np.abs(y), FLOOR_FRAC * np.abs(y[..., 5:6])), 1e-6)
+        scale = np.maximum(np.maximum(np.abs(y), FLOOR_FRAC * np.abs(y[..., 5:6])), FLOOR_K)
         out.append(float(np.max(np.abs(x - y) / scale)))
     pa, pb = np.asarray(a["prob"], dtype=float), np.asarray(b["prob"], dtype=float)
     out.append(float(np.max(np.abs(pa - pb) / np.maximum(pb, 1e-3))) if pa.size else 0.0)

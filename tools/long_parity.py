@@ -40,6 +40,8 @@ def oracle_reference(s, n_moves, chunk, tape, start_energy=True):
     o = orc.Oracle(s)
     if start_energy:
         o.system_energy()
+    else:
+        o.prepare_fourier()     # phase tables of every molecule, A(k) = 0, tracked energies = 0 (what the device chain starts from)
     recs, offs, ckpt = [], [0], []
     pos = 0
     for a in range(0, n_moves, chunk):
@@ -55,6 +57,7 @@ class Tally:
     def __init__(self, label):
         self.label, self.moves, self.flips = label, 0, 0
         self.e_old = self.e_new = self.e_p = 0.0
+        self.worst = None      # (error, which vector, move, kind, component, reference value, absolute difference, reference total)
         self.flip_notes = []
         self.mismatch = 0      # chunks whose move sequence differed for another reason than a flip (must stay 0)
 
@@ -67,6 +70,13 @@ class Tally:
         if good:
             eo, en, ep = record_errors(got[:good], ref[:good])
             self.e_old, self.e_new, self.e_p = max(self.e_old, eo), max(self.e_new, en), max(self.e_p, ep)
+            from conftest import FLOOR_FRAC, FLOOR_K
+            for key in ("old_e", "new_e"):       # where the largest error sits (for the log)
+                x, y = got[key][:good], ref[key][:good]
+                err = np.abs(x - y) / np.maximum(np.maximum(np.abs(y), FLOOR_FRAC * np.abs(y[:, 5:6])), FLOOR_K)
+                i, c = np.unravel_index(int(np.argmax(err)), err.shape)
+                if self.worst is None or err[i, c] > self.worst[0]:
+                    self.worst = (float(err[i, c]), key, int(base + i), int(ref["kind"][i]), int(c), float(y[i, c]), float(abs(x[i, c] - y[i, c])), float(y[i, 5]))
         self.moves += good
         if good == n:
             return False
@@ -84,6 +94,7 @@ class Tally:
     def row(self):
         return {"run": self.label, "moves_compared": self.moves, "max_rel_err_old_e": self.e_old, "max_rel_err_new_e": self.e_new,
                 "max_rel_err_prob": self.e_p, "accept_reject_flips": self.flips, "sequence_mismatches": self.mismatch,
+                "worst": None if self.worst is None else dict(zip(("rel_err", "vector", "move", "kind", "component", "ref_value_K", "abs_diff_K", "ref_total_K"), self.worst)),
                 "notes": self.flip_notes}
 
 

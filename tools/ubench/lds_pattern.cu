@@ -23,13 +23,13 @@ __global__ void k(const int* idx, double* out, long long* cyc, int iters) {
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 int main() {
-    const char* names[] = {"distinct consecutive", "uniform (1 address)", "2 addresses (half warps)", "3 addresses (11/11/10)", "2 addresses interleaved", "4 addresses (8 each)", "stride 2 elements"};
-    int pat[7][32];
-    for (int l = 0; l < 32; l++) { pat[0][l] = l; pat[1][l] = 5; pat[2][l] = l < 16 ? 3 : 40; pat[3][l] = l < 11 ? 3 : l < 22 ? 17 : 60; pat[4][l] = (l & 1) ? 3 : 40; pat[5][l] = 7 + 13 * (l / 8); pat[6][l] = 2 * l; }
+    const char* names[] = {"distinct consecutive", "uniform (1 address)", "2 addresses (half warps)", "3 addresses (11/11/10)", "2 addresses interleaved", "4 addresses (8 each)", "stride 2 elements", "MMA A fragment, row stride 36", "MMA A fragment, row stride 40"};
+    int pat[9][32];
+    for (int l = 0; l < 32; l++) { pat[0][l] = l; pat[1][l] = 5; pat[2][l] = l < 16 ? 3 : 40; pat[3][l] = l < 11 ? 3 : l < 22 ? 17 : 60; pat[4][l] = (l & 1) ? 3 : 40; pat[5][l] = 7 + 13 * (l / 8); pat[6][l] = 2 * l; pat[7][l] = (l & 3) * 36 + (l >> 2); pat[8][l] = (l & 3) * 40 + (l >> 2); }
     int* d_idx; double* d_out; long long* d_cyc;
     cudaMalloc(&d_idx, 128); cudaMalloc(&d_out, 1024 * 8 * 148); cudaMalloc(&d_cyc, 8 * 148);
     const int iters = 2000, threads = 512;
-    for (int w = 0; w < 2; w++) for (int p = 0; p < 7; p++) {
+    for (int w = 0; w < 2; w++) for (int p = 0; p < 9; p++) {
         cudaMemcpy(d_idx, pat[p], 128, cudaMemcpyHostToDevice);
         if (w == 0) k<16><<<148, threads, 32768>>>(d_idx, d_out, d_cyc, iters); else k<8><<<148, threads, 32768>>>(d_idx, d_out, d_cyc, iters);
         long long c; cudaDeviceSynchronize(); cudaMemcpy(&c, d_cyc, 8, cudaMemcpyDeviceToHost);
