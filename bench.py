@@ -230,7 +230,9 @@ def run_own(args, rank, world, local_rank):
     for c in range(C):
         gpu.set_chain_params(c, chain_fugacity(s, rank * C + c), s.temperature)
         gpu.set_chain_id(c, rank * C + c)
-        gpu.system_energy(c)
+    t_start = time.perf_counter()
+    gpu.system_energy_all()     # ComputeSystemEnergy of every chain: the framework's S(k) once per handle, guests per chain
+    startup_s = time.perf_counter() - t_start
     stream = torch.cuda.ExternalStream(gpu.stream(), device=local_rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local_rank}")
     g_mols, g_atoms = gpu.chain_capacity()
@@ -379,7 +381,7 @@ def run_own(args, rank, world, local_rank):
                    "call": "mmc_upload_chains + mmc_run_batch_async + mmc_download_chains per step, pinned host buffers"},
            "gpu_launches": int(launches), "roofline": roofline, "roofline_pair": roofline_pair,
            "clocks": clk, "mean_guests_per_chain": float(counts.mean()), "max_guests_per_chain": int(counts.max()),
-           "warnings": warnings}
+           "warnings": warnings, "startup_system_energy_all_s": startup_s}
     gpu.close()
     if world == 1 and not args.no_cpu_baseline:
         nt = host_threads()

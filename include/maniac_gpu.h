@@ -172,6 +172,11 @@ int mmc_get_step_sizes(mmc_t* handle, int chain, double* translation_step, doubl
  * Stores the result as the chain's tracked `energy` and, with MMC_INIT_SK_FULL, the tracked
  * A(k) := S(k) (with MMC_INIT_SK_ZERO it is zeroed, the reference's de-facto behaviour). */
 int mmc_system_energy(mmc_t* handle, int chain, double out[MMC_NE]);
+/* The same for EVERY chain of the handle in one launch set with one synchronisation.  The inactive residues' share --
+ * their structure factor (ComputeRecipAmplitude over the framework, ewald_energy.f90:40-74), their mutual pair energy and
+ * Ewald self term (energy_utils.f90:270-330) -- is identical for all chains and is computed once per handle; each chain adds
+ * its guests (A_chain(k) = S_framework(k) + S_guests(k)).  out: [n_chains][MMC_NE] or NULL. */
+int mmc_system_energy_all(mmc_t* handle, double* out);
 
 /* ---- strict mode: one trial move per call, host draws the random numbers -------------------- */
 
@@ -299,6 +304,10 @@ int mmc_pair_work(mmc_t* handle, int64_t out[2]);
  * of one launch of {pair sweep, reciprocal sweep, step tail} in ms[0..2] and the number of
  * launches of each in n[0..2].  Advances the chains like mmc_run_batch_async. */
 int mmc_profile_kernels(mmc_t* handle, int n_steps, uint64_t seed, double ms[3], int64_t n[3]);
+/* diagnostic builds (-DMMC_PHASE_TIMING) only: clock cycles per phase of the batched kernel, summed over CTAs and trials:
+ * out[0..6] = propose, stage, cull + real-space sweep, block sum, reciprocal sweep, block sum, finalize + commit;
+ * out[7] = trials counted.  All zero in production builds. */
+int mmc_dbg_phase_cycles(mmc_t* handle, int64_t out[8]);
 /* FP64 FMA peak micro-benchmark (register-resident DFMA chains): returns TFLOP/s */
 int mmc_measure_fp64_peak(int device, double* tflops);
 

@@ -65,8 +65,8 @@ struct DevConst {
     const int* stype;
     const double* tbox;            // [6][n_tiles]
     int n_tiles;
-    const double* gtab;            // [(MMC_GTAB_DEG+1)][gtab_stride] Coulomb kernel table for this alpha
-    int gtab_base, gtab_stride;    // segment index of s = gtab_smin; segments in use = row stride
+    const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
+    int gtab_base;                 // segment index of s = gtab_smin
     double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
     // reciprocal work items (build_sweep_layout): one per (kx, ky) row and kz >= 0, serving k(+kz) and k(-kz).
     // .x = kx | (ky+kmax_y)<<10 | kz<<21 | flag<<31, .y = index of k(+kz); index of k(-kz) = .y - 2 kz + flag
@@ -126,7 +126,7 @@ struct ChainState {
     int* rcount;          // [C][MMC_MAX_RES] molecules in the reservoir pool (reservoir%num_residues)
     double* roff;         // [C][r_atoms][3] their site offsets (reservoir%site_offset)
     unsigned int* chain_id;  // [C] Philox stream of each chain (default: the chain index); global ids make a sweep independent of how chains are dealt to GPUs
-    unsigned long long* pair_count;  // [2] executed real-space work since mmc_init: distances formed, pairs inside reach
+    unsigned long long* pair_count;  // [10] executed real-space work since mmc_init: distances formed, pairs inside reach; [2..9] = phase cycles of -DMMC_PHASE_TIMING builds
     int* error_flag;      // [1] MMC_ERRF_* bits, sticky until read by the host
 };
 
@@ -223,18 +223,20 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
 #ifndef MMC_GTAB_MBITS
 #define MMC_GTAB_MBITS 4
 #endif
-#define MMC_GTAB_MAXSEG (16 << MMC_GTAB_MBITS)   // 16 octaves; also the row stride: layout [degree][segment]
+#define MMC_GTAB_MAXSEG (12 << MMC_GTAB_MBITS)   // 12 octaves (r = 1 A up to 64 A); also the COMPILE-TIME row stride of the layout
+                                                 // [degree][segment]: the coefficient loads get immediate offsets (a run-time stride
+                                                 // cost one integer multiply-add per load and 10 % of the real-space phase, r2b A/B)
 __device__ __noinline__ double coul_kernel_slow(double s, double alpha) { const double r = sqrt(s); return erfc(alpha * r) / r; }
-__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base, int stride) {
+__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base) {
     const int hi = __double2hiint(s), lo = __double2loint(s);
     const int idx = (hi >> (20 - MMC_GTAB_MBITS)) - base;
     const double f = __hiloint2double(0x3FF00000 | ((hi & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
                                           (int)((unsigned)lo >> (32 - MMC_GTAB_MBITS)), lo << MMC_GTAB_MBITS);
     const double t = fma(2.0, f, -3.0);
     const double* c = tab + idx;
-    double p = c[MMC_GTAB_DEG * stride];
+    double p = c[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
 #pragma unroll
-    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, c[d * stride]);
+    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, c[d * MMC_GTAB_MAXSEG]);
     return p;
 }
 // 1/a: MUFU.RCP64H seed + two Newton steps

@@ -32,6 +32,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             if (cs.trial[c].error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
         }
         __syncthreads();
+        MMC_TSTAMP(0);
         sweep_trial<NT, TRI>(dc, cs, c, s, 0, 1, phases);
         if (threadIdx.x == 0) {
             Trial& t = cs.trial[c];
@@ -55,6 +56,10 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             }
         }
         __syncthreads();
+#ifdef MMC_PHASE_TIMING
+        if (threadIdx.x == 0) s.mol->phase[7] += 1ull;
+#endif
+        MMC_TSTAMP(6);
     }
     pair_count_flush(cs, s);
 }

@@ -16,6 +16,16 @@
 #pragma once
 #include "common.cuh"
 
+// -DMMC_PHASE_TIMING: thread 0 of every CTA timestamps the phase boundaries of each trial (clock64) and the totals are added
+// to cs.phase_cycles at the end of the launch (mmc_dbg_phase_cycles).  Diagnostic builds only: the stamps cost registers.
+// slots: 0 propose, 1 stage (terms + molecule), 2 cull + real-space sweep, 3 block sum, 4 reciprocal sweep, 5 block sum,
+//        6 finalize + accept + commit + record, 7 trials
+#ifdef MMC_PHASE_TIMING
+#define MMC_TSTAMP(slot) do { if (threadIdx.x == 0) { const long long t_ = clock64(); s.mol->phase[slot] += (unsigned long long)(t_ - s.mol->t_last); s.mol->t_last = t_; } } while (0)
+#else
+#define MMC_TSTAMP(slot) do { } while (0)
+#endif
+
 // moved molecule staged in shared memory
 struct MolS {
     double po[MMC_MAX_MOL_ATOMS][3], pn[MMC_MAX_MOL_ATOMS][3];
@@ -29,6 +39,9 @@ struct MolS {
     signed char term[2 * MMC_MAX_MOL_ATOMS];  // reciprocal terms: +(a+1) = atom a added, -(a+1) = atom a removed
     double sums[6];        // block sums of this trial: parked here between the phases so they hold no registers
     unsigned int work[2];  // executed real-space work of this CTA (distances formed, pairs inside reach)
+#ifdef MMC_PHASE_TIMING
+    long long t_last; unsigned long long phase[8];
+#endif
 };
 
 struct SweepCtx {
@@ -59,10 +72,10 @@ __host__ __device__ inline int recip_zstride(int kmax_z) {
     // (4 terms x 4 kz, an 8-byte load is served per half warp) fall into 16 distinct 8-byte bank pairs
     return ((kmax_z + 1 + 7) / 8) * 8 + 4;
 }
-__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int gtab_stride, int threads, size_t off[10]) {
+__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[10]) {
     size_t o = 0;
     const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = kmax[2] + 1, zs = 2 * max_nat + 1;
-    off[0] = o; o += ((size_t)(MMC_GTAB_DEG + 1) * gtab_stride * sizeof(double) + 15) / 16 * 16;
+    off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
     off[1] = o; o += (size_t)max_nat * ntypes * sizeof(double2);
     off[2] = o; o += (size_t)2 * max_nat * nx * sizeof(double2);
     off[3] = o; o += (size_t)2 * max_nat * ny * sizeof(double2);
@@ -87,7 +100,7 @@ __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, con
 
 __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned char* smem, int threads) {
     size_t off[10];
-    sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, threads, off);
+    sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
     SweepCtx s;
     s.gtab = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
     s.X = (double2*)(smem + off[2]); s.Y = (double2*)(smem + off[3]);
@@ -109,7 +122,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
 
 // once per kernel: the Coulomb kernel table
 __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const SweepCtx& s) {
-    for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * dc.gtab_stride; i += blockDim.x) s.gtab[i] = dc.gtab[i];
+    for (int i = threadIdx.x; i < (MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG; i += blockDim.x) s.gtab[i] = dc.gtab[i];
 }
 
 // Stages the moved molecule of the pending Trial of chain c for the real-space sweep: positions, charges, LJ rows,
@@ -262,7 +275,7 @@ __device__ __forceinline__ void stage_terms(const DevConst& dc, const ChainState
 }
 
 // ----------------------------------------------------------------------------------------------
-struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase, gstride; };
+struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase; };
 
 // one (moved atom, other atom) pair at one geometry; SHIFT: the other atom was already moved to the periodic
 // image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
@@ -282,7 +295,7 @@ __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc
         work += 0x10000u;
         if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
             double g;
-            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase, pc.gstride);
+            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase);
             else g = coul_kernel_slow(r2, pc.alpha);
             e_c = fma(qq, g, e_c);
         }
@@ -372,7 +385,7 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
-    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base, dc.gtab_stride};
+    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base};
     const bool cull = dc.reach2 < 1e300;
     int item0 = 0;
     for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
@@ -732,6 +745,7 @@ __device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState
     const bool swap = cs.trial[c].kind == MMC_SWAP;
     stage_terms<TRI>(dc, cs, c, s);
     stage_molecule(dc, cs, c, s, swap ? 1 : 0);
+    MMC_TSTAMP(1);
     {
         double pa[4] = {0, 0, 0, 0};
         unsigned cnt = 0u;   // executed work of this thread in this trial: low 16 bits = distances formed, high 16 = pairs inside reach
@@ -743,22 +757,36 @@ __device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState
         }
         const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt & 0xffffu), w1 = __reduce_add_sync(0xffffffffu, cnt >> 16);
         if ((threadIdx.x & 31) == 0 && (w0 | w1)) { atomicAdd(&s.mol->work[0], w0); atomicAdd(&s.mol->work[1], w1); }
+#ifdef MMC_PHASE_TIMING
+        __syncthreads(); MMC_TSTAMP(2);
+#endif
         block_sum<4, NT>(pa, s.red);
         if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];
+        MMC_TSTAMP(3);
     }
     {
         double ra[2] = {0, 0};
         if (phases & 2) recip_phase<NT, TRI>(dc, cs, c, s, part, n_parts, ra);
+#ifdef MMC_PHASE_TIMING
+        __syncthreads(); MMC_TSTAMP(4);
+#endif
         block_sum<2, NT>(ra, s.red);
         if (threadIdx.x == 0) { s.mol->sums[4] = ra[0]; s.mol->sums[5] = ra[1]; }
     }
     __syncthreads();
+    MMC_TSTAMP(5);
 }
 
 // executed-work counters of the real-space sweep (bench.py's executed-flop figure): cs.pair_count[0] += distances
 // formed, [1] += pairs inside reach (Coulomb table and/or LJ evaluated).  One atomic pair per CTA per launch.
 __device__ __forceinline__ void pair_count_init(const SweepCtx& s) {
-    if (threadIdx.x == 0) { s.mol->work[0] = 0u; s.mol->work[1] = 0u; }
+    if (threadIdx.x == 0) {
+        s.mol->work[0] = 0u; s.mol->work[1] = 0u;
+#ifdef MMC_PHASE_TIMING
+        for (int i = 0; i < 8; i++) s.mol->phase[i] = 0ull;
+        s.mol->t_last = clock64();
+#endif
+    }
 }
 __device__ __forceinline__ void pair_count_flush(const ChainState& cs, const SweepCtx& s) {
     __syncthreads();
@@ -766,6 +794,9 @@ __device__ __forceinline__ void pair_count_flush(const ChainState& cs, const Swe
         atomicAdd(cs.pair_count, (unsigned long long)s.mol->work[0]);
         atomicAdd(cs.pair_count + 1, (unsigned long long)s.mol->work[1]);
     }
+#ifdef MMC_PHASE_TIMING
+    if (threadIdx.x == 0) for (int i = 0; i < 8; i++) atomicAdd(cs.pair_count + 2 + i, s.mol->phase[i]);
+#endif
 }
 
 // strict mode / sharded step: grid = (dc.sweep_parts, chains) CTAs; the sweep_parts CTAs of one row share the pending

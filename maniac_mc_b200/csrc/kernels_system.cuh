@@ -243,7 +243,7 @@ __global__ void k_erfc_test(DevConst dc, const double* x, int n, double* out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double r = x[i] / dc.alpha, s = r * r;
-    const double g = (s >= dc.gtab_smin && s < dc.gtab_smax) ? coul_kernel_tab(s, dc.gtab, dc.gtab_base, dc.gtab_stride) : coul_kernel_slow(s, dc.alpha);
+    const double g = (s >= dc.gtab_smin && s < dc.gtab_smax) ? coul_kernel_tab(s, dc.gtab, dc.gtab_base) : coul_kernel_slow(s, dc.alpha);
     out[i] = r * g;
 }
 
@@ -256,4 +256,200 @@ __global__ void k_fp64_peak(double* out, int iters) {
         a4 = fma(a4, m, b); a5 = fma(a5, m, b); a6 = fma(a6, m, b); a7 = fma(a7, m, b);
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+// ====================================================================================================================
+// Start-up for MANY chains at once (mmc_system_energy_all).  ComputeSystemEnergy (energy_utils.f90:18-35) splits into a part
+// that is the same for every chain of a handle -- the inactive residues ("framework"): their structure factor
+// S_fw(k) = sum_fw q e^{i k r} (ComputeRecipAmplitude over the inactive atoms, ewald_energy.f90:40-74), their mutual pair
+// energy and their Ewald self term (energy_utils.f90:307-330) -- computed ONCE per handle, and a per-chain part over the
+// guests only: guest-framework and guest-guest pairs, S_guests(k), self and intra-residue terms.  A_chain = S_fw + S_guests.
+// The single-chain path above (mmc_system_energy) is kept as the independent evaluation the tests compare against.
+
+// sums the super-chunk partials of k_sys_sk in order -> out[k] (the framework's S_fw)
+__global__ void __launch_bounds__(RECIP_THREADS) k_sys_sk_store(DevConst dc, SysScratch ss, double2* out) {
+    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
+    if (ik >= dc.nk) return;
+    double are = 0.0, aim = 0.0;
+    for (int s = 0; s < ss.n_super; s++) { const double2 p = ss.sk_part[(size_t)s * dc.nk + ik]; are += p.x; aim += p.y; }
+    out[ik] = make_double2(are, aim);
+}
+
+// -alpha/sqrt(pi) sum q^2 over the inactive atoms (ComputeEwaldSelf, framework share), in K; one block
+__global__ void __launch_bounds__(SYS_THREADS) k_sys_fw_self(DevConst dc, double* out) {
+    __shared__ double red[2 * SYS_THREADS / 32];
+    double v[2] = {0.0, 0.0};
+    const double f = dc.alpha / sqrt(MMC_PI);
+    for (int j = threadIdx.x; j < dc.n_fw; j += SYS_THREADS) { const double q = dc.fq[j]; if (fabs(q) >= MMC_ERR) v[0] -= f * (q * q); }
+    block_sum<2, SYS_THREADS>(v, red);
+    if (threadIdx.x == 0) out[0] = v[0] * dc.coul_const;
+}
+
+struct SysAll {
+    const double2* sfw;    // [nk] framework structure factor
+    const double* fwc;     // [3] framework-framework LJ, Coulomb (K), framework self (K)
+    double* pair_part;     // [C][n_other_tiles][2]
+    double* recip_part;    // [C][n_k_tiles]
+    double* out;           // [C][MMC_NE] (device copy of the results, same values as cs.energy)
+    int n_other_tiles, n_fw_mols, store_sk, chain0;
+};
+
+// guest slot g of a chain -> (residue, molecule, atom)
+__device__ __forceinline__ void guest_slot(const DevConst& dc, int g, int& r, int& m, int& a) {
+    r = dc.active_list[0];
+    for (int i = 0; i < dc.n_active; i++) { const int rr = dc.active_list[i]; if (g >= dc.g_atom_base[rr]) r = rr; }
+    const int na = dc.natoms[r], l = g - dc.g_atom_base[r];
+    m = l / na; a = l - m * na;
+}
+
+// grid = (n_other_tiles, chains): block (T, c) holds 256 "other" atoms j of the flat order framework ++ guest slots of chain
+// c (one per thread) and walks the chain's guest atoms i; the unordered inter-molecular pair (i, j) is taken where j is a
+// framework atom or a guest atom behind i in the flat order (the ordering test of energy_utils.f90:157-158)
+__global__ void __launch_bounds__(SYS_THREADS) k_sys_pair_guests(DevConst dc, ChainState cs, SysAll sa) {
+    __shared__ double sx[SYS_THREADS], sy[SYS_THREADS], sz[SYS_THREADS], sq[SYS_THREADS];
+    __shared__ int st[SYS_THREADS], smol[SYS_THREADS], sflat[SYS_THREADS];
+    __shared__ double red[2 * SYS_THREADS / 32];
+    const int c = sa.chain0 + blockIdx.y, T = blockIdx.x, tid = threadIdx.x;
+    const int j = T * SYS_THREADS + tid;
+    double xj = 0, yj = 0, zj = 0, qj = 0; int tj = 0, mj = -1;
+    if (dc.n_active > 0) {
+        if (j < dc.n_fw) { xj = dc.fx[j]; yj = dc.fy[j]; zj = dc.fz[j]; qj = dc.fq[j]; tj = dc.ftype[j]; mj = dc.fmol[j]; }
+        else if (j < dc.n_fw + dc.g_atoms) {
+            int r, m, a; guest_slot(dc, j - dc.n_fw, r, m, a);
+            if (m < cs.count[c * MMC_MAX_RES + r]) {
+                const size_t ia = (size_t)c * dc.g_atoms + (j - dc.n_fw);
+                xj = cs.gx[ia]; yj = cs.gy[ia]; zj = cs.gz[ia]; qj = dc.q[r][a]; tj = dc.type[r][a];
+                mj = sa.n_fw_mols + dc.g_mol_base[r] + m;
+            }
+        }
+    }
+    double acc[2] = {0.0, 0.0};
+    for (int ia = 0; ia < dc.n_active; ia++) {
+        const int r = dc.active_list[ia], na = dc.natoms[r];
+        const int n_at = cs.count[c * MMC_MAX_RES + r] * na;
+        for (int i0 = 0; i0 < n_at; i0 += SYS_THREADS) {
+            __syncthreads();
+            const int i = i0 + tid;
+            if (i < n_at) {
+                const int m = i / na, a = i - m * na;
+                const size_t gi = (size_t)c * dc.g_atoms + dc.g_atom_base[r] + i;
+                sx[tid] = cs.gx[gi]; sy[tid] = cs.gy[gi]; sz[tid] = cs.gz[gi]; sq[tid] = dc.q[r][a]; st[tid] = dc.type[r][a];
+                smol[tid] = sa.n_fw_mols + dc.g_mol_base[r] + m; sflat[tid] = dc.n_fw + dc.g_atom_base[r] + i;
+            }
+            __syncthreads();
+            if (mj >= 0) {
+                const int nn = min(SYS_THREADS, n_at - i0);
+                for (int ii = 0; ii < nn; ii++) {
+                    if (smol[ii] == mj || !(j < dc.n_fw || j > sflat[ii])) continue;
+                    // ComputeDistance: delta = pos(second) - pos(first), first = the lower flat index
+                    const bool i_first = sflat[ii] < j;
+                    double dx = i_first ? xj - sx[ii] : sx[ii] - xj, dy = i_first ? yj - sy[ii] : sy[ii] - yj, dz = i_first ? zj - sz[ii] : sz[ii] - zj;
+                    min_image3(dc, dx, dy, dz);
+                    const double rr = sqrt(dx * dx + dy * dy + dz * dz);
+                    const int ti = i_first ? st[ii] : tj, t2 = i_first ? tj : st[ii];
+                    sys_pair_eval(dc, rr, dc.lj[ti * dc.ntypes + t2], i_first ? sq[ii] : qj, i_first ? qj : sq[ii], acc[0], acc[1]);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    block_sum<2, SYS_THREADS>(acc, red);
+    if (tid == 0) { double* o = sa.pair_part + ((size_t)blockIdx.y * sa.n_other_tiles + T) * 2; o[0] = acc[0]; o[1] = acc[1]; }
+}
+
+// grid = (n_k_tiles, chains): S_guests(k) of chain c for 256 k-vectors (1-D phase tables of a chunk of guest atoms in shared
+// memory, direct cos / sin as ComputePhaseFactors1D), A = S_fw + S_guests stored as the tracked A(k) (init_sk = full) or zeroed
+// (Q1 default), energy partial sum f W |A|^2
+__global__ void __launch_bounds__(RECIP_THREADS) k_sys_sk_guests(DevConst dc, ChainState cs, SysAll sa, int chunk) {
+    extern __shared__ double2 s_tab[];  // [chunk][3][kstride]
+    __shared__ double s_q[SK_CHUNK];
+    __shared__ double red[2 * RECIP_THREADS / 32];
+    const int ks = dc.kstride, c = sa.chain0 + blockIdx.y;
+    const int ik = blockIdx.x * RECIP_THREADS + threadIdx.x;
+    int4 kv = make_int4(0, 0, 0, 0);
+    if (ik < dc.nk) kv = dc.kvec[ik];
+    double are = 0.0, aim = 0.0;
+    for (int ia = 0; ia < dc.n_active; ia++) {
+        const int r = dc.active_list[ia], na = dc.natoms[r];
+        const int n_at = cs.count[c * MMC_MAX_RES + r] * na;
+        const size_t base = (size_t)c * dc.g_atoms + dc.g_atom_base[r];
+        for (int a0 = 0; a0 < n_at; a0 += chunk) {
+            const int nn = min(chunk, n_at - a0);
+            __syncthreads();
+            for (int i = threadIdx.x; i < nn * 3 * ks; i += blockDim.x) {
+                const int k = i % ks, ax = (i / ks) % 3, a = i / (3 * ks);
+                double2 v = make_double2(0.0, 0.0);
+                if (k <= dc.kmax[ax]) {
+                    const double pos[3] = {cs.gx[base + a0 + a], cs.gy[base + a0 + a], cs.gz[base + a0 + a]};
+                    const double theta = MMC_TWOPI * frac_coord(dc, pos, ax);
+                    double s, co; sincos((double)k * theta, &s, &co);
+                    v = make_double2(co, s);
+                }
+                s_tab[i] = v;
+            }
+            if (threadIdx.x < nn) s_q[threadIdx.x] = dc.q[r][(a0 + threadIdx.x) % na];
+            __syncthreads();
+            if (ik < dc.nk) {
+                for (int a = 0; a < nn; a++) {
+                    const double2* tb = s_tab + (size_t)a * 3 * ks;
+                    double2 px = tb[kv.x];
+                    double2 py = tb[ks + abs(kv.y)]; if (kv.y < 0) py.y = -py.y;
+                    double2 pz = tb[2 * ks + abs(kv.z)]; if (kv.z < 0) pz.y = -pz.y;
+                    const double2 pxy = make_double2(px.x * py.x - px.y * py.y, px.x * py.y + px.y * py.x);
+                    const double2 p = make_double2(pxy.x * pz.x - pxy.y * pz.y, pxy.x * pz.y + pxy.y * pz.x);
+                    const double q = s_q[a];
+                    are += q * p.x; aim += q * p.y;
+                }
+            }
+        }
+    }
+    double v[2] = {0.0, 0.0};
+    if (ik < dc.nk) {
+        const double2 f = sa.sfw[ik];
+        are += f.x; aim += f.y;
+        v[0] = dc.fw[ik] * (are * are + aim * aim);
+        double2* A = cs.A + ((size_t)c * 2 + cs.cur[c]) * dc.nk;
+        A[ik] = sa.store_sk ? make_double2(are, aim) : make_double2(0.0, 0.0);
+    }
+    __syncthreads();
+    block_sum<2, RECIP_THREADS>(v, red);
+    if (threadIdx.x == 0) sa.recip_part[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = v[0];
+}
+
+// grid = chains: ordered sums of the chain's partials, guest self and intra terms, tracked energies
+__global__ void __launch_bounds__(SYS_THREADS) k_sys_finish_all(DevConst dc, ChainState cs, SysAll sa, int n_k_tiles) {
+    __shared__ double red[4 * SYS_THREADS / 32];
+    const int c = sa.chain0 + blockIdx.x;
+    double v[4] = {0.0, 0.0, 0.0, 0.0};   // lj, coul, recip, intra
+    const double* pp = sa.pair_part + (size_t)blockIdx.x * sa.n_other_tiles * 2;
+    for (int i = threadIdx.x; i < sa.n_other_tiles; i += SYS_THREADS) { v[0] += pp[2 * i]; v[1] += pp[2 * i + 1]; }
+    const double* rp = sa.recip_part + (size_t)blockIdx.x * n_k_tiles;
+    for (int i = threadIdx.x; i < n_k_tiles; i += SYS_THREADS) v[2] += rp[i];
+    for (int i = 0; i < dc.n_active; i++) {   // ComputeTotalIntraResidueCoulombEnergy energy_utils.f90:55-81 (active residues only)
+        const int r = dc.active_list[i], nat = dc.natoms[r], cnt = cs.count[c * MMC_MAX_RES + r];
+        for (int m = threadIdx.x; m < cnt; m += SYS_THREADS) {
+            double e = 0.0;
+            const size_t b = (size_t)c * dc.g_atoms + dc.g_atom_base[r] + (size_t)m * nat;
+            for (int a1 = 0; a1 < nat - 1; a1++)
+                for (int a2 = a1 + 1; a2 < nat; a2++) {
+                    double dx = cs.gx[b + a2] - cs.gx[b + a1], dy = cs.gy[b + a2] - cs.gy[b + a1], dz = cs.gz[b + a2] - cs.gz[b + a1];
+                    min_image3(dc, dx, dy, dz);
+                    const double rr = sqrt(dx * dx + dy * dy + dz * dz);
+                    if (rr > MMC_ERR) e += dc.q[r][a1] * dc.q[r][a2] * (erfc(dc.alpha * rr) - 1.0) / rr;
+                }
+            v[3] += e * dc.coul_const;
+        }
+    }
+    block_sum<4, SYS_THREADS>(v, red);
+    if (threadIdx.x == 0) {
+        double self = sa.fwc[2];
+        for (int i = 0; i < dc.n_active; i++) { const int r = dc.active_list[i]; self += dc.self_e[r] * cs.count[c * MMC_MAX_RES + r]; }
+        double* E = cs.energy + (size_t)c * MMC_NE;
+        E[MMC_E_NONCOUL] = sa.fwc[0] + v[0];
+        E[MMC_E_COUL] = sa.fwc[1] + v[1] * dc.coul_const;
+        E[MMC_E_RECIP] = v[2] * dc.recip_const;
+        E[MMC_E_SELF] = self; E[MMC_E_INTRA] = v[3];
+        E[MMC_E_TOTAL] = E[MMC_E_RECIP] + E[MMC_E_NONCOUL] + E[MMC_E_COUL] + E[MMC_E_SELF] + E[MMC_E_INTRA];   // energy_utils.f90:32-33
+        if (sa.out) for (int i = 0; i < MMC_NE; i++) sa.out[(size_t)blockIdx.x * MMC_NE + i] = E[i];
+    }
 }

@@ -65,6 +65,9 @@ struct mmc_handle {
     size_t snap_off[6] = {0, 0, 0, 0, 0, 0}, snap_bytes = 0;   // count, com, offsets, energies, counters, error flag
     std::vector<int> snap_count[2];        // compacted [C][nres] counts handed to the caller
     cudaStream_t copy_stream = nullptr;
+    // mmc_system_energy_all: the framework's share of the start-up, computed once per handle
+    double2* d_sfw = nullptr; double* d_fwc = nullptr; bool fw_ready = false;
+    double *d_pair_part = nullptr, *d_recip_part = nullptr, *d_eall = nullptr;
 };
 
 template <typename T>
@@ -198,15 +201,14 @@ static uint32_t morton3(uint32_t x, uint32_t y, uint32_t z) {
 // Coulomb kernel table (common.cuh coul_kernel_tab): g(s) = erfc(alpha sqrt(s))/sqrt(s) on segments
 // [2^e (1 + j/8), 2^e (1 + (j+1)/8)), degree-9 interpolation at Chebyshev nodes solved in long double.
 // Domain: s_min (0.25 A^2, raised if more than MMC_GTAB_MAXSEG segments would be needed) to (xmax/alpha)^2.
-static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out, int* stride_out) {
+static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out) {
     const int D = MMC_GTAB_DEG, M = MMC_GTAB_MBITS, NS = 1 << M;
     const double smax = (xmax / alpha) * (xmax / alpha);
     int e_hi = 0; std::frexp(smax, &e_hi);   // smax in [2^(e_hi-1), 2^e_hi)
     int e_lo = 0;   // s >= 1 A^2: closer pairs (overlapping insertions only) take coul_kernel_slow
     while ((e_hi - e_lo) * NS > MMC_GTAB_MAXSEG) e_lo++;
     const int nseg = (e_hi - e_lo) * NS;
-    tab.assign((size_t)(D + 1) * nseg, 0.0);   // layout [degree][segment], row stride = the segments in use
-    *stride_out = nseg;
+    tab.assign((size_t)(D + 1) * MMC_GTAB_MAXSEG, 0.0);
     const long double pi = 3.14159265358979323846264338327950288L;
     long double nodes[D + 1];
     for (int k = 0; k <= D; k++) nodes[k] = cosl(pi * (2 * k + 1) / (2.0L * (D + 1)));
@@ -229,7 +231,7 @@ static void build_coulomb_table(double alpha, double xmax, std::vector<double>& 
                 for (int k = c; k <= D + 1; k++) V[r][k] -= f * V[c][k];
             }
         }
-        for (int c = 0; c <= D; c++) tab[(size_t)c * nseg + seg] = (double)(V[c][D + 1] / V[c][c]);
+        for (int c = 0; c <= D; c++) tab[(size_t)c * MMC_GTAB_MAXSEG + seg] = (double)(V[c][D + 1] / V[c][c]);
     }
     const double smin = std::ldexp(1.0, e_lo);
     union { double d; uint64_t u; } cv; cv.d = smin;
@@ -294,7 +296,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     dc.sx = px; dc.sy = py; dc.sz = pz; dc.sq = pq; dc.stype = pt; dc.tbox = pb; dc.n_tiles = n_tiles;
     {
         std::vector<double> tab;
-        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax, &dc.gtab_stride);
+        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax);
         CK(dalloc(h, &pe, tab.size())); CK(cudaMemcpy(pe, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
         dc.gtab = pe;
     }
@@ -359,9 +361,9 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     const int work = std::max((dc.nk + 511) / 512, (n_tiles + dc.g_atoms / TILE + 15) / 16);
     dc.sweep_parts = std::max(1, std::min(2 * h->n_sm, work));
     size_t off[10];
-    h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, SWEEP_THREADS, off);
+    h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, SWEEP_THREADS, off);
     h->chain_threads = dc.n_chains >= 3 * h->n_sm ? 256 : dc.n_chains >= 3 * h->n_sm / 2 ? 512 : 1024;
-    h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, dc.gtab_stride, h->chain_threads, off);
+    h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
     if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
                                                  dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
     CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
@@ -550,7 +552,7 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
             CKB(cudaMemcpy(cs.roff, ro.data(), ro.size() * sizeof(double), cudaMemcpyHostToDevice));
         }
     }
-    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.chain_id, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 2));
+    CKB(dalloc(h, &cs.tape_pos, C)); CKB(dalloc(h, &cs.chain_id, C)); CKB(dalloc(h, &cs.error_flag, 1)); CKB(dalloc(h, &cs.pair_count, 10));
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
     CKB(cudaMallocHost((void**)&h->h_tape_pos, C * sizeof(long long)));
@@ -868,6 +870,65 @@ extern "C" int mmc_system_energy(mmc_t* h, int c, double out[MMC_NE]) {
     CK(cudaMemcpyAsync(h->h_out, h->cs.energy + (size_t)c * MMC_NE, MMC_NE * sizeof(double), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (out) memcpy(out, h->h_out, MMC_NE * sizeof(double));
+    return 0;
+}
+
+// The framework's share of ComputeSystemEnergy -- S_fw(k), framework-framework pair energy, framework self term -- is the same
+// for every chain of the handle: computed once, on first use.
+static int ensure_framework_terms(mmc_handle* h) {
+    if (h->fw_ready) return 0;
+    const DevConst& dc = h->dc; cudaStream_t st = h->stream;
+    CK(dalloc(h, &h->d_sfw, (size_t)dc.nk)); CK(dalloc(h, &h->d_fwc, 4));   // zero filled: right for a system without framework
+    if (dc.n_fw > 0) {
+        SysScratch f = h->ss;     // a view of the scratch arrays restricted to the inactive atoms
+        f.n = dc.n_fw; f.n_tiles = (f.n + SYS_THREADS - 1) / SYS_THREADS;
+        const int n_chunks = (f.n + h->sk_chunk - 1) / h->sk_chunk;
+        f.n_super = n_chunks < 128 ? n_chunks : 128;
+        CK(cudaMemsetAsync(f.tile_min, 0x7f, f.n_tiles * sizeof(int), st));
+        CK(cudaMemsetAsync(f.tile_max, 0xff, f.n_tiles * sizeof(int), st));
+        k_sys_gather<<<(f.n + 255) / 256, 256, 0, st>>>(dc, h->cs, f, 0, h->n_fw_mols);
+        k_sys_pair<<<dim3(f.n_tiles, f.n_tiles), SYS_THREADS, 0, st>>>(dc, f);
+        k_sum_rows<<<1, SYS_THREADS, 0, st>>>(f.part, (long long)f.n_tiles * f.n_tiles, 2, h->d_fwc, 1.0, dc.coul_const);
+        k_sys_sk<<<dim3(dc.n_k_tiles, f.n_super), RECIP_THREADS, h->sk_smem, st>>>(dc, f, h->sk_chunk);
+        k_sys_sk_store<<<dc.n_k_tiles, RECIP_THREADS, 0, st>>>(dc, f, h->d_sfw);
+        k_sys_fw_self<<<1, SYS_THREADS, 0, st>>>(dc, h->d_fwc + 2);
+        h->launches += 6;
+        CK(cudaGetLastError());
+    }
+    h->fw_ready = true;
+    return 0;
+}
+
+// ComputeSystemEnergy for EVERY chain of the handle in one launch set and one synchronisation: the framework terms come
+// from ensure_framework_terms, each chain adds its guests (A_chain = S_fw + S_guests).  out: [n_chains][MMC_NE] or NULL.
+extern "C" int mmc_system_energy_all(mmc_t* h, double* out) {
+    if (!h) return fail("null handle");
+    CK(cudaSetDevice(h->device));
+    const DevConst& dc = h->dc; cudaStream_t st = h->stream; const int C = dc.n_chains;
+    if (ensure_framework_terms(h)) return 1;
+    SysAll sa;
+    sa.n_other_tiles = (dc.n_fw + dc.g_atoms + SYS_THREADS - 1) / SYS_THREADS;
+    if (!h->d_pair_part) {
+        CK(dalloc(h, &h->d_pair_part, (size_t)C * sa.n_other_tiles * 2));
+        CK(dalloc(h, &h->d_recip_part, (size_t)C * dc.n_k_tiles));
+        CK(dalloc(h, &h->d_eall, (size_t)C * MMC_NE));
+    }
+    sa.sfw = h->d_sfw; sa.fwc = h->d_fwc; sa.pair_part = h->d_pair_part; sa.recip_part = h->d_recip_part; sa.out = h->d_eall;
+    sa.n_fw_mols = h->n_fw_mols; sa.store_sk = h->init_sk == MMC_INIT_SK_FULL; sa.chain0 = 0;
+    const size_t smem = (size_t)h->sk_chunk * 3 * dc.kstride * sizeof(double2);
+    for (int c0 = 0; c0 < C; c0 += 32768) {   // gridDim.y limit
+        const int nc = std::min(32768, C - c0);
+        SysAll sb = sa; sb.chain0 = c0;
+        sb.pair_part = sa.pair_part + (size_t)c0 * sa.n_other_tiles * 2; sb.recip_part = sa.recip_part + (size_t)c0 * dc.n_k_tiles;
+        sb.out = sa.out + (size_t)c0 * MMC_NE;
+        k_sys_pair_guests<<<dim3(sa.n_other_tiles, nc), SYS_THREADS, 0, st>>>(dc, h->cs, sb);
+        k_sys_sk_guests<<<dim3(dc.n_k_tiles, nc), RECIP_THREADS, smem, st>>>(dc, h->cs, sb, h->sk_chunk);
+        k_sys_finish_all<<<nc, SYS_THREADS, 0, st>>>(dc, h->cs, sb, dc.n_k_tiles);
+        h->launches += 3;
+    }
+    CK(cudaGetLastError());
+    if (out) CK(cudaMemcpyAsync(out, h->d_eall, (size_t)C * MMC_NE * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return 0;
 }
 
@@ -1270,6 +1331,18 @@ extern "C" int mmc_pair_work(mmc_t* h, int64_t out[2]) {
     unsigned long long v[2];
     CK(cudaMemcpy(v, h->cs.pair_count, sizeof v, cudaMemcpyDeviceToHost));
     out[0] = (int64_t)v[0]; out[1] = (int64_t)v[1];
+    return 0;
+}
+
+// -DMMC_PHASE_TIMING builds: summed clock64 cycles of thread 0 of every CTA per phase since mmc_init (slots: propose, stage,
+// cull + real-space sweep, block sum, reciprocal sweep, block sum, finalize + commit, trials); zeros in production builds
+extern "C" int mmc_dbg_phase_cycles(mmc_t* h, int64_t out[8]) {
+    if (!h || !out) return fail("mmc_dbg_phase_cycles: null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    unsigned long long v[8];
+    CK(cudaMemcpy(v, h->cs.pair_count + 2, sizeof v, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 8; i++) out[i] = (int64_t)v[i];
     return 0;
 }
 

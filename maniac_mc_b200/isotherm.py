@@ -138,7 +138,7 @@ class IsothermSweep:
             f[self.res] = builders.fugacity_from_atm(self.f_atm[cid.point], system.temperature)
             self.gpu.set_chain_params(c, f, system.temperature)
             self.gpu.set_chain_id(c, cid.seed)     # global Philox stream: the sweep does not depend on the dealing
-            self.gpu.system_energy(c)
+        self.gpu.system_energy_all()               # one launch set for all chains; the framework's share is computed once
         self.avg = BlockAverages(len(self.ids))
         self.step = 0
         g_mols, g_atoms = self.gpu.chain_capacity()

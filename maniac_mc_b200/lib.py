@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles",
 ]
 
 _lib = None
@@ -78,6 +78,7 @@ def load():
     L.mmc_get_chain_state.argtypes = [vp, C.c_int, ip, dp, dp]
     L.mmc_set_step_sizes.argtypes = [vp, C.c_int, C.c_double, C.c_double]
     L.mmc_system_energy.argtypes = [vp, C.c_int, dp]
+    L.mmc_system_energy_all.argtypes = [vp, dp]
     L.mmc_trial_energy.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_trial_commit.argtypes = [vp, C.c_int, C.c_int]
     L.mmc_trial_energy_swap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
@@ -94,6 +95,7 @@ def load():
     L.mmc_dbg_table_lookup.argtypes = [vp, C.c_int, dp, C.c_int, dp]
     L.mmc_dbg_erfc.argtypes = [vp, dp, C.c_int, dp]
     L.mmc_dbg_set_tracked.argtypes = [vp, C.c_int, dp, dp]
+    L.mmc_dbg_phase_cycles.argtypes = [vp, C.POINTER(C.c_int64)]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
     L.mmc_pair_work.argtypes = [vp, C.POINTER(C.c_int64)]
@@ -254,6 +256,13 @@ class ManiacGPU:
         _ck(load().mmc_system_energy(self.h, chain, _dp(e)))
         return e
 
+    def system_energy_all(self):
+        """ComputeSystemEnergy of every chain in one launch set (the framework's share is computed once per handle);
+        returns [n_chains, 6]"""
+        e = np.zeros((self.n_chains, MMC_NE))
+        _ck(load().mmc_system_energy_all(self.h, _dp(e)))
+        return e
+
     def trial_energy(self, kind, res, mol, com_new=None, offs_new=None, chain=0):
         old, new = np.zeros(MMC_NE), np.zeros(MMC_NE)
         c = None if com_new is None else np.ascontiguousarray(com_new, dtype=np.float64)
@@ -390,6 +399,13 @@ class ManiacGPU:
         a, b = C.c_int(), C.c_int()
         _ck(load().mmc_shard_range(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def phase_cycles(self):
+        """-DMMC_PHASE_TIMING builds: per-phase clock cycles (summed over CTAs and trials) and the trial count"""
+        v = (C.c_int64 * 8)()
+        _ck(load().mmc_dbg_phase_cycles(self.h, v))
+        names = ("propose", "stage", "real_space", "sum4", "reciprocal", "sum2", "finalize_commit", "trials")
+        return dict(zip(names, (int(x) for x in v)))
 
     def pair_work(self):
         """(distances formed, pairs inside reach) by the per-move sweeps since mmc_init"""

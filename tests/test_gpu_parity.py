@@ -28,6 +28,36 @@ def test_system_energy(name):
     g.close()
 
 
+@pytest.mark.parametrize("name,init_sk", [("zif8_h2o", 1), ("zif8_h2o", 0), ("h2o_gas", 1), ("slit", 1), ("zif8_ch4o_h2o", 1), ("dipole_tri", 1)])
+def test_system_energy_all_equals_per_chain(name, init_sk):
+    """mmc_system_energy_all (framework S(k), framework pair and self terms once per handle + the guests of every chain in one
+    launch set) against the independent per-chain evaluation and the oracle: energies 1e-12 (sum order only), A(k) 1e-10."""
+    s = load_system(name, init_sk=init_sk)
+    C = 3
+    g = ManiacGPU(s, n_chains=C)
+    # give chain 1 a different guest population so that the chains differ
+    r = int(np.flatnonzero(s.is_active == 1)[0]); mo, ao = s.mol_offsets(); na = int(s.natoms[r])
+    if int(s.count[r]) > 1:
+        cnt = s.count.copy(); cnt[r] -= 1
+        keep_m = np.ones(len(s.com), dtype=bool); keep_m[mo[r] + int(s.count[r]) - 1] = False
+        keep_a = np.ones(len(s.offsets), dtype=bool); keep_a[ao[r] + (int(s.count[r]) - 1) * na: ao[r] + int(s.count[r]) * na] = False
+        g.set_chain_state(1, cnt, s.com[keep_m], s.offsets[keep_a])
+    e_all = g.system_energy_all()
+    a_all = [g.sk(c) for c in range(C)]
+    tracked = [g.sync_to_host(c)[3] for c in range(C)]
+    for c in range(C):
+        assert np.array_equal(tracked[c], e_all[c])
+        e_one = g.system_energy(c)
+        assert rel_err(e_all[c], e_one) < 1e-12
+        np.testing.assert_allclose(a_all[c], g.sk(c), atol=1e-10)
+    assert rel_err(e_all[0], orc.Oracle(s).system_energy()) < 1e-12
+    if int(s.count[r]) > 1:
+        assert not np.array_equal(e_all[0], e_all[1])
+    e2 = g.system_energy_all()            # second call: cached framework terms
+    assert np.array_equal(e2, e_all)
+    g.close()
+
+
 def test_kvectors_and_weights():
     s = load_system("h2o_gas"); g = ManiacGPU(s); o = orc.Oracle(s)
     for a, b in zip(g.kvectors(), o.kvectors()):

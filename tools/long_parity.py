@@ -57,6 +57,7 @@ class Tally:
     def __init__(self, label):
         self.label, self.moves, self.flips = label, 0, 0
         self.e_old = self.e_new = self.e_p = 0.0
+        self.max_abs = 0.0     # largest absolute difference [K] over components below 1e6 K (overlapping insertions excluded)
         self.worst = None      # (error, which vector, move, kind, component, reference value, absolute difference, reference total)
         self.flip_notes = []
         self.mismatch = 0      # chunks whose move sequence differed for another reason than a flip (must stay 0)
@@ -70,10 +71,11 @@ class Tally:
         if good:
             eo, en, ep = record_errors(got[:good], ref[:good])
             self.e_old, self.e_new, self.e_p = max(self.e_old, eo), max(self.e_new, en), max(self.e_p, ep)
-            from conftest import FLOOR_FRAC, FLOOR_K
+            from conftest import record_scale
             for key in ("old_e", "new_e"):       # where the largest error sits (for the log)
                 x, y = got[key][:good], ref[key][:good]
-                err = np.abs(x - y) / np.maximum(np.maximum(np.abs(y), FLOOR_FRAC * np.abs(y[:, 5:6])), FLOOR_K)
+                err = np.abs(x - y) / record_scale(y)
+                self.max_abs = max(self.max_abs, float(np.max(np.where(np.abs(y) < 1e6, np.abs(x - y), 0.0))))
                 i, c = np.unravel_index(int(np.argmax(err)), err.shape)
                 if self.worst is None or err[i, c] > self.worst[0]:
                     self.worst = (float(err[i, c]), key, int(base + i), int(ref["kind"][i]), int(c), float(y[i, c]), float(abs(x[i, c] - y[i, c])), float(y[i, 5]))
@@ -93,7 +95,7 @@ class Tally:
 
     def row(self):
         return {"run": self.label, "moves_compared": self.moves, "max_rel_err_old_e": self.e_old, "max_rel_err_new_e": self.e_new,
-                "max_rel_err_prob": self.e_p, "accept_reject_flips": self.flips, "sequence_mismatches": self.mismatch,
+                "max_rel_err_prob": self.e_p, "max_abs_diff_K": self.max_abs, "accept_reject_flips": self.flips, "sequence_mismatches": self.mismatch,
                 "worst": None if self.worst is None else dict(zip(("rel_err", "vector", "move", "kind", "component", "ref_value_K", "abs_diff_K", "ref_total_K"), self.worst)),
                 "notes": self.flip_notes}
 
