@@ -239,6 +239,22 @@ __device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, i
     for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, c[d * MMC_GTAB_MAXSEG]);
     return p;
 }
+// two evaluations in lockstep (old and new geometry of one pair): two independent Horner chains instead of two dependent
+// ones back to back -- the real-space sweep is bound by the latency of these chains (r2c phase timing), not by a pipe
+__device__ __forceinline__ void coul_kernel_tab2(double sa, double sb, const double* tab, int base, double& ga, double& gb) {
+    const int hia = __double2hiint(sa), loa = __double2loint(sa), hib = __double2hiint(sb), lob = __double2loint(sb);
+    const int ia = (hia >> (20 - MMC_GTAB_MBITS)) - base, ib = (hib >> (20 - MMC_GTAB_MBITS)) - base;
+    const double fa = __hiloint2double(0x3FF00000 | ((hia & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
+                                           (int)((unsigned)loa >> (32 - MMC_GTAB_MBITS)), loa << MMC_GTAB_MBITS);
+    const double fb = __hiloint2double(0x3FF00000 | ((hib & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
+                                           (int)((unsigned)lob >> (32 - MMC_GTAB_MBITS)), lob << MMC_GTAB_MBITS);
+    const double ta = fma(2.0, fa, -3.0), tb = fma(2.0, fb, -3.0);
+    const double* ca = tab + ia; const double* cb = tab + ib;
+    double pa = ca[MMC_GTAB_DEG * MMC_GTAB_MAXSEG], pb = cb[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+#pragma unroll
+    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) { pa = fma(pa, ta, ca[d * MMC_GTAB_MAXSEG]); pb = fma(pb, tb, cb[d * MMC_GTAB_MAXSEG]); }
+    ga = pa; gb = pb;
+}
 // 1/a: MUFU.RCP64H seed + two Newton steps
 __device__ __forceinline__ double mmc_rcp(double a) {
     double y;

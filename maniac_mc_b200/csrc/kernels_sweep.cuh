@@ -307,6 +307,46 @@ __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc
     }
 }
 
+// the same pair at the OLD and the NEW geometry in one go: every step of the two evaluations is independent of the other
+// geometry's, so the two dependent chains (distance -> table index -> 8 FMAs; reciprocal -> sixth power) interleave.
+// Per geometry the operations and their order are those of pair_one, the sums go to the same accumulators: bit-identical.
+template <bool SHIFT, bool TRI>
+__device__ __forceinline__ void pair_two(const DevConst& dc, const PairConst& pc, const double* s_gtab, double dxo, double dyo, double dzo,
+                                         double dxn, double dyn, double dzn, double qq, bool charged, double2 lj, double (&acc)[4], unsigned& work) {
+    if (!SHIFT) {
+        if (TRI) { min_image_tri(dc, dxo, dyo, dzo); min_image_tri(dc, dxn, dyn, dzn); }
+        else {
+            dxo = min_image_fast(dxo, pc.Lx, pc.iLx); dyo = min_image_fast(dyo, pc.Ly, pc.iLy); dzo = min_image_fast(dzo, pc.Lz, pc.iLz);
+            dxn = min_image_fast(dxn, pc.Lx, pc.iLx); dyn = min_image_fast(dyn, pc.Ly, pc.iLy); dzn = min_image_fast(dzn, pc.Lz, pc.iLz);
+        }
+    }
+    const double r2o = fma(dxo, dxo, fma(dyo, dyo, dzo * dzo)), r2n = fma(dxn, dxn, fma(dyn, dyn, dzn * dzn));
+    const bool in_o = r2o < pc.reach2, in_n = r2n < pc.reach2;
+    if (!(in_o | in_n)) return;
+    work += (in_o ? 0x10000u : 0u) + (in_n ? 0x10000u : 0u);
+    // a geometry out of reach is evaluated at the other one's distance and discarded (keeps the table index in range)
+    const double so = in_o ? r2o : r2n, sn = in_n ? r2n : r2o;
+    if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
+        double go, gn;
+        if (fmin(so, sn) >= pc.smin && fmax(so, sn) < pc.smax) coul_kernel_tab2(so, sn, s_gtab, pc.gbase, go, gn);
+        else {
+            go = (so >= pc.smin && so < pc.smax) ? coul_kernel_tab(so, s_gtab, pc.gbase) : coul_kernel_slow(so, pc.alpha);
+            gn = (sn >= pc.smin && sn < pc.smax) ? coul_kernel_tab(sn, s_gtab, pc.gbase) : coul_kernel_slow(sn, pc.alpha);
+        }
+        if (in_o) acc[1] = fma(qq, go, acc[1]);
+        if (in_n) acc[3] = fma(qq, gn, acc[3]);
+    }
+    if (lj.y != 0.0) {  // 4 eps [(sigma/r)^12 - (sigma/r)^6], energy_utils.f90:417-423
+        const bool lo = in_o && r2o < pc.rc2, ln = in_n && r2n < pc.rc2;
+        if (lo | ln) {
+            const double s2o = lj.x * mmc_rcp(so), s2n = lj.x * mmc_rcp(sn);
+            const double s6o = s2o * s2o * s2o, s6n = s2n * s2n * s2n;
+            if (lo) acc[0] = fma(lj.y, fma(s6o, s6o, -s6o), acc[0]);
+            if (ln) acc[2] = fma(lj.y, fma(s6n, s6n, -s6n), acc[2]);
+        }
+    }
+}
+
 // one "other" atom against every atom of the moved molecule, old and/or new geometry
 // TRI: tilted cell; the OLD / NEW sets are then also masked at run time (one instantiation serves every move type)
 template <bool OLD, bool NEW, bool SHIFT, bool TRI>
@@ -338,6 +378,13 @@ __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& p
         if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
         cnt += (use_old ? 1u : 0u) + (use_new ? 1u : 0u);
+#ifndef MMC_NO_PAIR_TWO
+        if (OLD && NEW && !TRI) {   // translation / rotation in an orthorhombic cell: both geometries in lockstep
+            pair_two<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2],
+                                 qq, charged, lj, acc, cnt);
+            continue;
+        }
+#endif
         if (use_old) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt);
         if (use_new) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt);
     }
@@ -525,6 +572,17 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
                 if (kb > ka) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + ka), "r"((kb - ka) * 16) : "memory");
             }
         }
+        const int base_p = k0 + m - (1 - has0);                   // k(+kz) = base_p + kz, k(-kz) = k0 + m - kz
+        // Software pipeline over the kz blocks: the A(k) / f W loads of block j + 1 are issued BEFORE block j is computed, so
+        // two blocks' worth of memory requests are in flight per warp.  (r2c phase timing: 1 090 cycles per block with one
+        // block in flight -- the whole DRAM / L2 latency exposed 170 times per trial and warp.)
+        const double2 zero2 = make_double2(0.0, 0.0);
+        int kz = 8 * jlo + g;
+        bool ok = kz <= m && (kz >= 1 || has0);
+        double2 ap = ok ? A[base_p + kz] : zero2;
+        double2 am = (ok && kz != 0) ? A[k0 + m - kz] : zero2;
+        double w = ok ? dc.fw[base_p + kz] : 0.0;   // f W depends on kx and |k|^2 only: the same for +kz and -kz in an orthorhombic cell
+        double wm = (TRI && ok && kz != 0) ? dc.fw[k0 + m - kz] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
         // B fragments: row rg + g / 2, component g % 2
         const int rb = rg + (g >> 1);
         const bool rb_ok = rb < r1;
@@ -534,12 +592,17 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
 #pragma unroll
             for (int kb = 0; kb < KB; kb++) bf[kb] = recip_bfrag(s, nterm, 4 * kb + t, rb_ok, ix, iy, g & 1);
         }
-        const int base_p = k0 + m - (1 - has0);                   // k(+kz) = base_p + kz, k(-kz) = k0 + m - kz
         for (int j = jlo; j < jhi; j++) {
-            const int kz = 8 * j + g;
+            const int kzn = kz + 8;                                  // >= 8: never the kz = 0 column
+            const bool okn = j + 1 < jhi && kzn <= m;
+            double2 apn = zero2, amn = zero2; double wn = 0.0, wmn = 0.0;
+            if (okn) {
+                apn = A[base_p + kzn]; amn = A[k0 + m - kzn]; wn = dc.fw[base_p + kzn];
+                wmn = TRI ? dc.fw[k0 + m - kzn] : wn;
+            }
             double s1 = 0.0, s4 = 0.0, s3 = 0.0, s2 = 0.0;
-            const double* zr = s.ZR + t * s.zS + kz;
-            const double* zi = s.ZI + t * s.zS + kz;
+            const double* zr = s.ZR + t * s.zS + 8 * j + g;
+            const double* zi = s.ZI + t * s.zS + 8 * j + g;
             if (KB > 0) {
 #pragma unroll
                 for (int kb = 0; kb < KB; kb++) {
@@ -553,24 +616,20 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
                     dmma_884(s3, s2, zi[4 * kb * s.zS], b);
                 }
             }
-            if (kz <= m && (kz >= 1 || has0)) {
+            if (ok) {
                 const int kpl = base_p + kz, kmi = k0 + m - kz;
-                const bool two = kz != 0;
-                const double2 ap = A[kpl];
-                const double2 am = two ? A[kmi] : make_double2(0.0, 0.0);
-                const double w = dc.fw[kpl];   // f W depends on kx and |k|^2 only: the same for +kz and -kz in an orthorhombic cell
                 const double2 bp = make_double2(ap.x + (s1 - s2), ap.y + (s3 + s4));
                 An[kpl] = bp;
                 acc[0] = fma(w, fma(ap.x, ap.x, ap.y * ap.y), acc[0]);  // amplitude_squared helper_utils.f90:125
                 acc[1] = fma(w, fma(bp.x, bp.x, bp.y * bp.y), acc[1]);
-                if (two) {
+                if (kz != 0) {
                     const double2 bm = make_double2(am.x + (s1 + s2), am.y + (s4 - s3));
                     An[kmi] = bm;
-                    const double wm = TRI ? dc.fw[kmi] : w;   // a tilted cell has |k(+kz)| != |k(-kz)|
                     acc[0] = fma(wm, fma(am.x, am.x, am.y * am.y), acc[0]);
                     acc[1] = fma(wm, fma(bm.x, bm.x, bm.y * bm.y), acc[1]);
                 }
             }
+            ap = apn; am = amn; w = wn; wm = wmn; kz = kzn; ok = okn;
         }
     }
 }

@@ -87,5 +87,7 @@ def compare_records(a, b, tol=REL_TOL):
     e_old, e_new, e_p = record_errors(a, b)
     assert e_old < tol, f"old_e per-component relative error {e_old:.3e} >= {tol:g}"
     assert e_new < tol, f"new_e per-component relative error {e_new:.3e} >= {tol:g}"
-    assert e_p < 1e-9, f"acceptance probability relative error {e_p:.3e}"
+    # p = min(1, c exp(-dE / T)): its relative error is |error of dE| / T, i.e. ~1e-16 (|E_old| + |E_new|) / T -- 3e-9 for the 8e7 K
+    # totals of the 50 000-atom frameworks at 300 K; the accept / reject identity above is the sharp test
+    assert e_p < 1e-7, f"acceptance probability relative error {e_p:.3e}"
     return e_old, e_new, e_p
