@@ -53,6 +53,7 @@ def parse_args():
     p.add_argument("--guests", type=int, default=200)
     p.add_argument("--cpu-moves", type=int, default=100, help="moves per host thread per reference-arm step; the cpu_baseline sample is 4x that")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-extras", action="store_true", help="skip the strict_mode and c5_isotherm objects")
     return p.parse_args()
 
 
@@ -215,6 +216,78 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
+def c5_isotherm(rank, world, local_rank, steps=1000, reps=5):
+    """BASELINE configs[4], the FIXED-size sweep of the north star: 64 fugacity points x 8 replicas = 512 chains of the
+    reference's ZIF-8 + H2O example IN TOTAL, dealt round-robin to the ranks (strong scaling: 512 / world chains per GPU).
+    Device-timed on the library's stream, MAX over ranks.  Returns the object for the JSON line (rank 0) or None."""
+    import torch
+    import torch.distributed as dist
+    from maniac_mc_b200 import builders, isotherm as iso
+    from maniac_mc_b200.lib import ManiacGPU
+    from maniac_mc_b200.system import System
+    s = System.load(os.path.join(ROOT, "tests", "golden", "zif8_h2o.npz"))
+    s.init_sk, s.deletion_mode = 1, 1
+    n_points, replicas = 64, 8
+    ids = iso.deal_chains(n_points, replicas, world, rank)
+    f_atm = iso.fugacity_points(n_points, FUG_LO_ATM, FUG_HI_ATM)
+    res = int(np.flatnonzero(s.is_active)[0])
+    gpu = ManiacGPU(s, n_chains=len(ids), device=local_rank)
+    for c, cid in enumerate(ids):
+        f = s.fugacity.copy(); f[res] = builders.fugacity_from_atm(f_atm[cid.point], s.temperature)
+        gpu.set_chain_params(c, f, s.temperature); gpu.set_chain_id(c, cid.seed)
+    gpu.system_energy_all()
+    stream = torch.cuda.ExternalStream(gpu.stream(), device=local_rank)
+    for _ in range(2):
+        gpu.run_batch_async(steps, seed=5)
+    gpu.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(reps):
+        gpu.run_batch_async(steps, seed=5)
+    ev1.record(stream)
+    gpu.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t[0])
+    threads = gpu.chain_threads() if hasattr(gpu, "chain_threads") else None
+    gpu.close()
+    if rank != 0:
+        return None
+    total = n_points * replicas
+    return {"workload": "c5_isotherm: 64 fugacity points x 8 replicas = 512 chains of ZIF-8 + H2O (2208-atom framework, K = 297) in TOTAL, "
+                        "dealt round-robin to the ranks", "scaling": "strong", "chains_total": total, "chains_per_gpu": len(ids),
+            "steps_per_chain": steps * reps, "value": total * steps * reps / (ms * 1e-3), "unit": "moves/s", "ms": ms,
+            "cta_threads": threads}
+
+
+def strict_mode(gpu_c4, s_c4, local_rank, cpu_moves_per_s_per_core):
+    """The drop-in (strict) mode the unmodified Fortran move routines call: one host-driven translation move per call,
+    mmc_trial_step (one launch per move) and the two-call form mmc_trial_energy + mmc_trial_commit, timed by wall clock
+    around a C loop inside the library (mmc_dbg_strict_loop) on the bench system and on the reference's ZIF-8 example."""
+    from maniac_mc_b200.lib import ManiacGPU
+    from maniac_mc_b200.system import System
+    from oracle.oracle import Oracle
+    out = {}
+    z = System.load(os.path.join(ROOT, "tests", "golden", "zif8_h2o.npz")); z.init_sk, z.deletion_mode = 1, 1
+    gz = ManiacGPU(z, n_chains=1, device=local_rank); gz.system_energy_all()
+    o = Oracle(z); o.system_energy()
+    t0 = time.perf_counter(); o.run(4000, seed=3, chain=0, step0=0, records=False); cpu_z = 4000 / (time.perf_counter() - t0)
+    for name, g, n, cpu in (("zif8_h2o", gz, 4000, cpu_z), ("c4_large_k", gpu_c4, 2000, cpu_moves_per_s_per_core)):
+        g.strict_loop(200, seed=1, fused=True)                     # warm-up
+        tf, af, lf = g.strict_loop(n, seed=2, fused=True)
+        t2, a2, l2 = g.strict_loop(n, seed=2, fused=False)
+        out[name] = {"moves_per_s": n / tf, "us_per_move": 1e6 * tf / n, "launches_per_move": lf / n, "accepted": af,
+                     "entry": "mmc_trial_step (energies + accept test + commit in one launch, result through host-mapped memory)",
+                     "two_call_form": {"moves_per_s": n / t2, "us_per_move": 1e6 * t2 / n, "launches_per_move": l2 / n,
+                                       "entry": "mmc_trial_energy + mmc_trial_commit"},
+                     "cpu_port_single_chain_moves_per_s": cpu, "moves": n, "move_type": "translation (host proposal, host uniform)"}
+    gz.close()
+    return out
+
+
 def run_own(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -313,6 +386,8 @@ def run_own(args, rank, world, local_rank):
     d2h = h2d + h_e.numel() * 8 + h_ctr.numel() * 8
     if rank != 0:
         gpu.close()
+        if not args.no_extras:
+            c5_isotherm(rank, world, local_rank)
         return
     # ---- roofline of the dominant kernel (rank 0): instrumented replay right after the timed region.
     # mmc_profile_kernels runs the SAME 32 proposals of every chain three times with CUDA events on the library's
@@ -382,7 +457,7 @@ def run_own(args, rank, world, local_rank):
            "gpu_launches": int(launches), "roofline": roofline, "roofline_pair": roofline_pair,
            "clocks": clk, "mean_guests_per_chain": float(counts.mean()), "max_guests_per_chain": int(counts.max()),
            "warnings": warnings, "startup_system_energy_all_s": startup_s}
-    gpu.close()
+    cpu_per_core = None
     if world == 1 and not args.no_cpu_baseline:
         nt = host_threads()
         cs = CpuSample(s, nt)
@@ -392,6 +467,19 @@ def run_own(args, rank, world, local_rank):
         out["cpu_baseline"] = {"value": nt * n_cpu / dt, "unit": "moves/s", "cores": nt, "kind": "port",
                                "sample": f"{nt} host threads x {n_cpu} MC moves of the same c4_large_k system, one "
                                          f"independent chain per thread (oracle port, gcc -O2, init_sk=zero), {dt:.1f} s wall"}
+        cpu_per_core = nt * n_cpu / dt / nt
+        del cs
+    if not args.no_extras:
+        try:
+            out["strict_mode"] = strict_mode(gpu, s, local_rank, cpu_per_core)
+        except Exception as e:   # never lose the headline line to an extra
+            out["strict_mode"] = {"error": str(e)}
+    gpu.close()
+    if not args.no_extras:
+        try:
+            out["c5_isotherm"] = c5_isotherm(rank, world, local_rank)
+        except Exception as e:
+            out["c5_isotherm"] = {"error": str(e)}
     print(json.dumps(out))
 
 

@@ -203,6 +203,16 @@ int mmc_trial_commit(mmc_t* handle, int chain, int accept);
 int mmc_trial_energy_swap(mmc_t* handle, int chain, int res_old, int mol, int res_new,
                           const double* com_new, const double* offs_new, double old_e[MMC_NE], double new_e[MMC_NE]);
 
+/* One strict-mode move in ONE launch: mmc_trial_energy + the accept test + mmc_trial_commit.  `u` is the uniform the move
+ * routine draws for its Metropolis test (`if (rand_uniform() <= probability)`, translation.f90:66, rotation.f90:62,
+ * create_molecule.f90:77, delete_molecule.f90:80): no draw happens between the proposal and that one, so drawing it before
+ * the call leaves the random stream untouched.  The library evaluates mc_acceptance_probability (monte_carlo_utils.f90:184-221),
+ * takes the decision u <= prob and applies Accept* / Reject*.  res_new is read for kind = MMC_SWAP only.
+ * Outputs: old_e / new_e (type(energy_state)), *prob, *accepted = 1 / 0; any pointer may be NULL. */
+int mmc_trial_step(mmc_t* handle, int chain, int kind, int res, int mol, int res_new,
+                   const double* com_new, const double* offs_new, double u,
+                   double old_e[MMC_NE], double new_e[MMC_NE], double* prob, int* accepted);
+
 /* once per block (PrintStatus / UpdateFiles, monte_carlo.f90:82-84): tracked energies,
  * counts and packed coordinates of one chain */
 int mmc_sync_to_host(mmc_t* handle, int chain, int* count, double* com, double* offsets,
@@ -287,6 +297,10 @@ int mmc_dbg_intra_singlemol(mmc_t* handle, int chain, int res, int mol, double* 
 int mmc_dbg_table_lookup(mmc_t* handle, int which, const double* r, int n, double* out);
 /* device erfc used by the pair sweep, for accuracy tests */
 int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
+/* measurement helper (bench.py strict_mode): n_moves translation moves of one chain driven from the host the way the
+ * Fortran Translation routine drives them, through mmc_trial_step (fused = 1: one launch per move) or through
+ * mmc_trial_energy + mmc_trial_commit (fused = 0); wall seconds and accepted moves */
+int mmc_dbg_strict_loop(mmc_t* handle, int chain, int n_moves, uint64_t seed, int fused, double* seconds, int64_t* n_accepted);
 /* test support: overwrite a chain's tracked energies (6 doubles) and / or tracked A(k) (2*K doubles); NULL = keep */
 int mmc_dbg_set_tracked(mmc_t* handle, int chain, const double* energies, const double* sk);
 /* timing of the last pair / recip sweeps in a batched run is taken by the caller with

@@ -28,17 +28,17 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         if (threadIdx.x == 0) {   // the RNG source is re-read here: it must not occupy registers during the sweeps
             RngSrc rs = ctl->rng;
             rs.step += (unsigned long long)st;
-            propose_move(dc, cs, rs, c);
-            if (cs.trial[c].error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
+            propose_move(dc, cs, rs, c, *s.trial);
+            if (s.trial->error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
         }
         __syncthreads();
         MMC_TSTAMP(0);
-        sweep_trial<NT, TRI>(dc, cs, c, s, 0, 1, phases);
+        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, 0, 1, phases);
         if (threadIdx.x == 0) {
-            Trial& t = cs.trial[c];
+            Trial& t = *s.trial;   // shared memory: the single-thread sections no longer round-trip ~2 kB through global memory
             const int kind = t.kind;
             if (kind > 0) {
-                finalize_trial(dc, cs, c, s.mol->sums);
+                finalize_trial(dc, cs, c, t, s.mol->sums);
                 RngSrc rs = ctl->rng;
                 rs.step += (unsigned long long)st;
                 Rng rng{&rs, cs, c, t.draw};  // the accept draw follows the proposal's draws
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
                 const int acc = (phases == 3 && u <= t.prob) ? 1 : 0;
                 // AcceptDeletionMove draws three more uniforms to place the molecule in the reservoir box (delete_molecule.f90:150-151)
                 if (acc && kind == MMC_DELETION && dc.has_reservoir) { rng.next(); rng.next(); rng.next(); }
-                commit_trial(dc, cs, c, acc);
+                commit_trial(dc, cs, c, t, acc);
             }
             if (ctl->recs) {
                 mmc_move_record& rec = ctl->recs[(size_t)c * ctl->rec_stride + ctl->rec_base + st];

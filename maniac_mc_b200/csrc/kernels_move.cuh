@@ -43,9 +43,11 @@ __device__ inline void rotate_offsets(int axis, double theta, int nat, const dou
 // Fills the Trial of chain c for a move of `kind` on (res, mol) with proposed geometry
 // com_new/off_new (ignored for deletion).  Mirrors which sweeps ComputeOldEnergy /
 // ComputeNewEnergy (monte_carlo_utils.f90:347,275) request for each move type.  Single thread.
-__device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int c, int kind, int r, int m,
-                                   const double* com_new, const double (*off_new)[3], int r2 = -1) {
-    Trial& t = cs.trial[c];
+// `t` is the caller's Trial: shared memory in the batched kernel and in the fused strict-mode kernel, cs.trial[c] (global) on
+// the k-sharded path.  write_slot: also write the proposed geometry of a creation / swap into its slot (done by ONE CTA when
+// several build the same trial).
+__device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, int kind, int r, int m,
+                                   const double* com_new, const double (*off_new)[3], int r2 = -1, bool write_slot = true) {
     const int nat = dc.natoms[r];
     if (kind != MMC_SWAP) r2 = r;
     const int nat2 = dc.natoms[r2];
@@ -77,7 +79,7 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
             t.do_old = 0; t.do_new = 1; t.r_plus = 1; t.r_minus = 0; t.excl = 0;
             // like the reference (create_molecule.f90:180-199) the geometry is written into the slot at
             // proposal time and stays there even if the move is rejected
-            {
+            if (write_slot) {
                 double* com = g_com(dc, cs, c, r, m);
                 for (int d = 0; d < 3; d++) com[d] = com_new[d];
                 for (int a = 0; a < nat; a++) {
@@ -91,7 +93,7 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
             // removed molecule (r, m): old sweep with its own atoms, excluded from both sweeps; inserted molecule of type
             // r2 in slot count(r2), outside the swept range; like a creation its geometry is written at proposal time
             t.do_old = 1; t.do_new = 1; t.r_plus = 1; t.r_minus = 1; t.excl = 1;
-            {
+            if (write_slot) {
                 const int m2 = cs.count[c * MMC_MAX_RES + r2];
                 double* com = g_com(dc, cs, c, r2, m2);
                 for (int d = 0; d < 3; d++) com[d] = com_new[d];
@@ -128,13 +130,12 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
 struct HostTrial { int chain, kind, res, mol, res2; double com[3]; double off[MMC_MAX_MOL_ATOMS][3]; };
 
 __global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
-    if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, ht.kind, ht.res, ht.mol, ht.com, ht.off, ht.res2);
+    if (threadIdx.x == 0) build_trial(dc, cs, ht.chain, cs.trial[ht.chain], ht.kind, ht.res, ht.mol, ht.com, ht.off, ht.res2);
 }
 
 // batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
 // proposal geometry, draw order as in SURVEY 3.8.  Single thread per chain.
-__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c) {
-    Trial& t = cs.trial[c];
+__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c, Trial& t) {
     t.kind = 0; t.error = 0; t.accepted = 0;
     for (int i = 0; i < MMC_NE; i++) { t.old_e[i] = 0.0; t.new_e[i] = 0.0; }
     Rng rng{&rs, cs, c, 0};
@@ -168,7 +169,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                 com_new[d] = dc.lo[d] + f_modulo(x - dc.lo[d], dc.L[d], dc.invL[d]);  // ApplyPBC
             }
             for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_new[a][d] = cs.goff[g_atom(dc, c, r, m, a) * 3 + d];
-            build_trial(dc, cs, c, MMC_TRANSLATION, r, m, com_new, off_new);
+            build_trial(dc, cs, c, t, MMC_TRANSLATION, r, m, com_new, off_new);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation) {
         if (nat != 1 && m >= 0) {  // Rotation rotation.f90:34-75
@@ -180,7 +181,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             rotate_offsets(axis, theta, nat, off_old, off_new);
             const double* com = g_com(dc, cs, c, r, m);
             for (int d = 0; d < 3; d++) com_new[d] = com[d];
-            build_trial(dc, cs, c, MMC_ROTATION, r, m, com_new, off_new);
+            build_trial(dc, cs, c, t, MMC_ROTATION, r, m, com_new, off_new);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation + dc.p_swap) {
         // swap (identity exchange): remove (r, m), insert a molecule of another active type at the same
@@ -204,7 +205,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                     const int axis = (int)(rng.next() * 3.0) + 1;
                     rotate_offsets(axis, theta, nat2, tmpl, off_new);
                 } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
-                build_trial(dc, cs, c, MMC_SWAP, r, m, com_new, off_new, r2);
+                build_trial(dc, cs, c, t, MMC_SWAP, r, m, com_new, off_new, r2);
             }
         }
     } else {
@@ -234,12 +235,12 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                         rotate_offsets(axis, theta, nat, tmpl, off_new);
                     } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
                 }
-                build_trial(dc, cs, c, MMC_CREATION, r, m, com_new, off_new);
+                build_trial(dc, cs, c, t, MMC_CREATION, r, m, com_new, off_new);
                 t.rsv = rsv;
             }
         } else if (cnt != 0) {  // DeleteMolecule delete_molecule.f90:41-199
             ctr.trial_deletions++;
-            build_trial(dc, cs, c, MMC_DELETION, r, m, nullptr, nullptr);
+            build_trial(dc, cs, c, t, MMC_DELETION, r, m, nullptr, nullptr);
         }
     }
     t.draw = rng.draw;
@@ -265,8 +266,7 @@ __device__ inline double intra_energy(const DevConst& dc, int nat, const double*
 // Assembles type(energy_state) old/new from the six sweep sums exactly as ComputeOldEnergy /
 // ComputeNewEnergy do for each move type (monte_carlo_utils.f90:275-396) and the acceptance probability.
 // v = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2}.  Single thread.
-__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, const double* v) {
-    Trial& t = cs.trial[c];
+__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, const double* v) {
     if (t.kind <= 0) return;
     const double lj_o = v[0], c_o = v[1] * dc.coul_const, lj_n = v[2], c_n = v[3] * dc.coul_const;
     const double rec_o = v[4] * dc.recip_const, rec_n = v[5] * dc.recip_const;
@@ -307,8 +307,7 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
 // AcceptMove / AcceptCreationMove / AcceptDeletionMove (monte_carlo_utils.f90:410, create_molecule.f90:96,
 // delete_molecule.f90:126).  Rejection needs no work: coordinates are only written here and A(k) is
 // double buffered.  Single thread.
-__device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, int c, int accept) {
-    Trial& t = cs.trial[c];
+__device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, int accept) {
     if (t.kind <= 0) return;
     t.accepted = accept;
     if (!accept) { t.kind = -t.kind; return; }  // negative kind = finished trial (cannot be committed twice)
@@ -406,7 +405,7 @@ __global__ void __launch_bounds__(TAIL_THREADS) k_finalize(DevConst dc, ChainSta
         for (int k = 0; k < 6; k++) v[k] += pp[i * 6 + k];
     block_sum<6, TAIL_THREADS>(v, red);
     if (threadIdx.x == 0) {
-        finalize_trial(dc, cs, chain, v);
+        finalize_trial(dc, cs, chain, cs.trial[chain], v);
         if (out) {
             const Trial& t = cs.trial[chain];
             for (int i = 0; i < MMC_NE; i++) { out[i] = t.old_e[i]; out[MMC_NE + i] = t.new_e[i]; }
@@ -415,7 +414,7 @@ __global__ void __launch_bounds__(TAIL_THREADS) k_finalize(DevConst dc, ChainSta
     }
 }
 __global__ void k_commit(DevConst dc, ChainState cs, int chain, int accept) {
-    if (threadIdx.x == 0) commit_trial(dc, cs, chain, accept);
+    if (threadIdx.x == 0) commit_trial(dc, cs, chain, cs.trial[chain], accept);
 }
 
 // ---- k-sharded mode: ONE system (or a few chains) spread over several GPUs (optional mode) ------------
@@ -430,7 +429,7 @@ __global__ void k_propose_all(DevConst dc, ChainState cs, const BatchCtl* ctl, i
     if (threadIdx.x != 0) return;
     const int c = c0 + blockIdx.x;
     RngSrc rs = ctl->rng;
-    propose_move(dc, cs, rs, c);
+    propose_move(dc, cs, rs, c, cs.trial[c]);
     if (cs.trial[c].error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
 }
 __global__ void __launch_bounds__(TAIL_THREADS) k_part_sum(DevConst dc, ChainState cs, int c0, double* sums /* [chains][6] */) {
@@ -452,14 +451,14 @@ __global__ void k_finish(DevConst dc, ChainState cs, const BatchCtl* ctl, int c0
     Trial& t = cs.trial[c];
     const int kind = t.kind;
     if (kind > 0) {
-        finalize_trial(dc, cs, c, sums + (size_t)blockIdx.x * 6);
+        finalize_trial(dc, cs, c, t, sums + (size_t)blockIdx.x * 6);
         if (decide) {
             RngSrc rs = ctl->rng;
             Rng rng{&rs, cs, c, t.draw};
             const double u = rng.next();
             const int acc = u <= t.prob ? 1 : 0;
             if (acc && kind == MMC_DELETION && dc.has_reservoir) { rng.next(); rng.next(); rng.next(); }  // reservoir placement draws
-            commit_trial(dc, cs, c, acc);
+            commit_trial(dc, cs, c, t, acc);
         }
     }
     if (out) {

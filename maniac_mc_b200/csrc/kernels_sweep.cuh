@@ -15,6 +15,7 @@
 // k by conjugation as the reference does (:105-107).
 #pragma once
 #include "common.cuh"
+#include "kernels_move.cuh"
 
 // -DMMC_PHASE_TIMING: thread 0 of every CTA timestamps the phase boundaries of each trial (clock64) and the totals are added
 // to cs.phase_cycles at the end of the launch (mmc_dbg_phase_cycles).  Diagnostic builds only: the stamps cost registers.
@@ -63,6 +64,7 @@ struct SweepCtx {
     uint16_t* list;  // [CULL_CHUNK]
     double* red;     // [6 * warps]
     MolS* mol;
+    Trial* trial;         // the pending trial of this CTA's chain (batched kernel, fused strict-mode kernel)
     int nx, ny, nz, zs;   // nz = kmax_z + 1
 };
 
@@ -72,7 +74,7 @@ __host__ __device__ inline int recip_zstride(int kmax_z) {
     // (4 terms x 4 kz, an 8-byte load is served per half warp) fall into 16 distinct 8-byte bank pairs
     return ((kmax_z + 1 + 7) / 8) * 8 + 4;
 }
-__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[10]) {
+__host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, const int kmax[3], int threads, size_t off[12]) {
     size_t o = 0;
     const int nx = kmax[0] + 1, ny = 2 * kmax[1] + 1, nz = kmax[2] + 1, zs = 2 * max_nat + 1;
     off[0] = o; o += (size_t)(MMC_GTAB_DEG + 1) * MMC_GTAB_MAXSEG * sizeof(double);
@@ -95,11 +97,12 @@ __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, con
 #else
     off[9] = o; o += (size_t)2 * (threads / 4) * zs * sizeof(double2);
 #endif
+    off[10] = o; o += (sizeof(Trial) + 15) / 16 * 16;
     return o;
 }
 
 __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned char* smem, int threads) {
-    size_t off[10];
+    size_t off[12];
     sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, threads, off);
     SweepCtx s;
     s.gtab = (double*)(smem + off[0]); s.lj = (double2*)(smem + off[1]);
@@ -110,7 +113,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
 #else
     s.Z = (double2*)(smem + off[4]);
 #endif
-    s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]);
+    s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]); s.trial = (Trial*)(smem + off[10]);
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
     s.list = (uint16_t*)(smem + off[8]);
 #ifndef MMC_RECIP_DMMA
@@ -131,8 +134,7 @@ __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const Swee
 //   pass 0: both sets in one sweep (every move but the swap)
 //   pass 1: swap, removed molecule only (old geometry)      pass 2: swap, inserted molecule only (new geometry)
 // All threads; ends with a barrier.
-__device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int pass) {
-    const Trial& t = cs.trial[c];
+__device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int pass) {
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
     const bool use_new_set = pass == 2;
@@ -190,8 +192,7 @@ __device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainSt
 // sign folded into Z.  Added atoms come from the NEW set (p_plus, q2), removed atoms from the OLD set (p_old, q).
 // All threads; ends with a barrier.
 template <bool TRI>
-__device__ __forceinline__ void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s) {
-    const Trial& t = cs.trial[c];
+__device__ __forceinline__ void stage_terms(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t) {
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
     if (tid == 0) {
@@ -378,7 +379,7 @@ __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& p
         if (!charged && lj.y == 0.0) continue;
         // ComputeDistance: delta = pos(other) - pos(moved)
         cnt += (use_old ? 1u : 0u) + (use_new ? 1u : 0u);
-#ifndef MMC_NO_PAIR_TWO
+#ifdef MMC_PAIR_TWO   // opt-in: measured 1.7 % SLOWER than the two pair_one calls (r2d A/B, profiles/r2d_ab.log): the compiler already interleaves them
         if (OLD && NEW && !TRI) {   // translation / rotation in an orthorhombic cell: both geometries in lockstep
             pair_two<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2],
                                  qq, charged, lj, acc, cnt);
@@ -465,10 +466,32 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
         }
         __syncthreads();
         const int nlist = m.nlist;
+#ifndef MMC_NO_TILE_PREFETCH
+        {   // the next tile's atom is loaded (L2 latency) before this tile's pairs are evaluated
+            int it = (gw + gstride - item0 % gstride) % gstride;
+            double xn = 0.0, yn = 0.0, zn = 0.0, qn = 0.0; int tn = 0; bool vn = false;
+            if (it < nlist) {
+                const int j = (base + (int)s.list[it]) * TILE + lane;
+                vn = j < dc.n_fw;
+                if (vn) { xn = dc.sx[j]; yn = dc.sy[j]; zn = dc.sz[j]; qn = dc.sq[j]; tn = dc.stype[j]; }
+            }
+            while (it < nlist) {
+                const double xj = xn, yj = yn, zj = zn, qj = qn; const int tj = tn; const bool v = vn;
+                it += gstride;
+                if (it < nlist) {
+                    const int j = (base + (int)s.list[it]) * TILE + lane;
+                    vn = j < dc.n_fw;
+                    if (vn) { xn = dc.sx[j]; yn = dc.sy[j]; zn = dc.sz[j]; qn = dc.sq[j]; tn = dc.stype[j]; }
+                }
+                if (v) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, xj, yj, zj, qj, tj, acc, cnt);
+            }
+        }
+#else
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
             const int j = (base + (int)s.list[it]) * TILE + lane;
             if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc, cnt);
         }
+#endif
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
     }
@@ -800,10 +823,10 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
 // the reciprocal sweep so that its item loop does not carry them in registers (64 registers per thread at 4 CTAs/SM).
 // TRI: compiled for tilted cells (dc.tri); the orthorhombic kernels carry none of that code
 template <int NT, bool TRI>
-__device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts, int phases) {
-    const bool swap = cs.trial[c].kind == MMC_SWAP;
-    stage_terms<TRI>(dc, cs, c, s);
-    stage_molecule(dc, cs, c, s, swap ? 1 : 0);
+__device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int part, int n_parts, int phases) {
+    const bool swap = t.kind == MMC_SWAP;
+    stage_terms<TRI>(dc, cs, c, s, t);
+    stage_molecule(dc, cs, c, s, t, swap ? 1 : 0);
     MMC_TSTAMP(1);
     {
         double pa[4] = {0, 0, 0, 0};
@@ -811,7 +834,7 @@ __device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState
         if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
         if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
             __syncthreads();
-            stage_molecule(dc, cs, c, s, 2);
+            stage_molecule(dc, cs, c, s, t, 2);
             if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
         }
         const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt & 0xffffu), w1 = __reduce_add_sync(0xffffffffu, cnt >> 16);
@@ -869,11 +892,69 @@ __global__ void __launch_bounds__(SWEEP_THREADS) k_sweep(DevConst dc, ChainState
     const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
     sweep_load_tables(dc, s);
     pair_count_init(s);
-    if (dc.tri) sweep_trial<SWEEP_THREADS, true>(dc, cs, c, s, part, n_parts, 3);
-    else sweep_trial<SWEEP_THREADS, false>(dc, cs, c, s, part, n_parts, 3);
+    if (dc.tri) sweep_trial<SWEEP_THREADS, true>(dc, cs, c, s, cs.trial[c], part, n_parts, 3);
+    else sweep_trial<SWEEP_THREADS, false>(dc, cs, c, s, cs.trial[c], part, n_parts, 3);
     if (threadIdx.x == 0) {
         double* out = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
         for (int i = 0; i < 6; i++) out[i] = s.mol->sums[i];
     }
     pair_count_flush(cs, s);
+}
+
+// ---- strict mode, fused: ONE launch per trial ------------------------------------------------------------------------
+// grid = dc.sweep_parts CTAs sharing the trial of one chain.  Every CTA builds the Trial in its own shared memory from the
+// host's proposal (kernel argument: no H2D copy, no separate set-up launch), sweeps its share of the tiles and of the (kx, ky)
+// rows and leaves six partial sums in cs.part; the LAST CTA to finish (ticket counter) adds the partials in a fixed order,
+// assembles old / new energies and the acceptance probability (ComputeOldEnergy / ComputeNewEnergy /
+// mc_acceptance_probability, monte_carlo_utils.f90:184-396) and writes them straight into host-mapped pinned memory, followed
+// by a sequence number the host spins on: no device-to-host copy, no stream synchronisation.  decide != 0: the host passed the
+// accept uniform it drew for this move (the Fortran move routines draw it right after the energies, so drawing it before the
+// call leaves the stream's order unchanged) and the same CTA commits (AcceptMove / Reject*, :410-510) -- one launch per move.
+// decide == 0: the Trial is parked in cs.trial[c] for a later mmc_trial_commit (k_commit).
+struct StrictOut { double old_e[MMC_NE], new_e[MMC_NE], prob; int accepted, error; unsigned long long seq; };
+
+__global__ void __launch_bounds__(SWEEP_THREADS) k_strict_trial(DevConst dc, ChainState cs, HostTrial ht, int decide, double u,
+                                                                unsigned int* ticket, StrictOut* out, unsigned long long seq) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_last;
+    const int c = ht.chain, tid = threadIdx.x;
+    const int part = blockIdx.x, n_parts = gridDim.x;
+    const SweepCtx s = sweep_carve(dc, smem, SWEEP_THREADS);
+    Trial& t = *s.trial;
+    sweep_load_tables(dc, s);
+    pair_count_init(s);
+    if (tid == 0) {
+        t.error = 0; t.accepted = 0; t.draw = 0; t.prob = 0.0;
+        for (int i = 0; i < MMC_NE; i++) { t.old_e[i] = 0.0; t.new_e[i] = 0.0; }
+        build_trial(dc, cs, c, t, ht.kind, ht.res, ht.mol, ht.com, ht.off, ht.res2, blockIdx.x == 0);
+    }
+    __syncthreads();
+    if (dc.tri) sweep_trial<SWEEP_THREADS, true>(dc, cs, c, s, t, part, n_parts, 3);
+    else sweep_trial<SWEEP_THREADS, false>(dc, cs, c, s, t, part, n_parts, 3);
+    if (tid == 0) {
+        double* o = cs.part + ((size_t)c * dc.sweep_parts + blockIdx.x) * 6;
+        for (int i = 0; i < 6; i++) o[i] = s.mol->sums[i];
+        __threadfence();
+        s_last = atomicAdd(ticket, 1u) == (unsigned)(gridDim.x - 1);
+    }
+    pair_count_flush(cs, s);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double v[6] = {0, 0, 0, 0, 0, 0};
+    const double* pp = cs.part + (size_t)c * dc.sweep_parts * 6;
+    for (int i = tid; i < n_parts; i += SWEEP_THREADS)
+        for (int k = 0; k < 6; k++) v[k] += __ldcg(pp + i * 6 + k);
+    block_sum<6, SWEEP_THREADS>(v, s.red);
+    if (tid == 0) {
+        finalize_trial(dc, cs, c, t, v);
+        int acc = -1;
+        if (decide) { acc = u <= t.prob ? 1 : 0; commit_trial(dc, cs, c, t, acc); }
+        else cs.trial[c] = t;
+        for (int i = 0; i < MMC_NE; i++) { out->old_e[i] = t.old_e[i]; out->new_e[i] = t.new_e[i]; }
+        out->prob = t.prob; out->accepted = acc; out->error = 0;
+        *ticket = 0u;
+        __threadfence_system();
+        *(volatile unsigned long long*)&out->seq = seq;
+    }
 }

@@ -14,6 +14,8 @@
 #include "kernels_chain.cuh"
 #include "kernels_system.cuh"
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <numeric>
 
 static thread_local std::string g_err;
@@ -68,6 +70,8 @@ struct mmc_handle {
     // mmc_system_energy_all: the framework's share of the start-up, computed once per handle
     double2* d_sfw = nullptr; double* d_fwc = nullptr; bool fw_ready = false;
     double *d_pair_part = nullptr, *d_recip_part = nullptr, *d_eall = nullptr;
+    // fused strict-mode trial (k_strict_trial): ticket counter, result block in host-mapped pinned memory, sequence number
+    unsigned int* d_ticket = nullptr; StrictOut* h_sout = nullptr; StrictOut* d_sout = nullptr; unsigned long long strict_seq = 0;
 };
 
 template <typename T>
@@ -128,6 +132,7 @@ extern "C" void mmc_destroy(mmc_t* h) {
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->h_tape_pos) cudaFreeHost(h->h_tape_pos);
+    if (h->h_sout) cudaFreeHost(h->h_sout);
     for (auto& s : h->snap) {
         if (s.dev) cudaFree(s.dev);
         if (s.host) cudaFreeHost(s.host);
@@ -372,13 +377,14 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     h->n_sm = prop.multiProcessorCount;
     const int work = std::max((dc.nk + 511) / 512, (n_tiles + dc.g_atoms / TILE + 15) / 16);
     dc.sweep_parts = std::max(1, std::min(2 * h->n_sm, work));
-    size_t off[10];
+    size_t off[12];
     h->sweep_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, SWEEP_THREADS, off);
     h->chain_threads = dc.n_chains >= 3 * h->n_sm ? 256 : dc.n_chains >= 3 * h->n_sm / 2 ? 512 : 1024;
     h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
     if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
                                                  dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
     CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
+    CK(cudaFuncSetAttribute(k_strict_trial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
     if (h->dc.tri) {
         CK(cudaFuncSetAttribute(k_chain_run<256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
         CK(cudaFuncSetAttribute(k_chain_run<512, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
@@ -568,6 +574,10 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &h->d_out, 16)); CKB(dalloc(h, &h->d_ctl, 1));
     CKB(cudaMallocHost((void**)&h->h_out, 16 * sizeof(double)));
     CKB(cudaMallocHost((void**)&h->h_tape_pos, C * sizeof(long long)));
+    CKB(dalloc(h, &h->d_ticket, 1));
+    CKB(cudaHostAlloc((void**)&h->h_sout, sizeof(StrictOut), cudaHostAllocMapped));
+    memset(h->h_sout, 0, sizeof(StrictOut));
+    CKB(cudaHostGetDevicePointer((void**)&h->d_sout, h->h_sout, 0));
     memset(h->h_tape_pos, 0, C * sizeof(long long));
     {
         std::vector<unsigned int> ids(C);
@@ -982,21 +992,58 @@ static int check_trial(mmc_handle* h, int c, int kind, int res, int mol, const d
     return 0;
 }
 
-static int trial_energy_impl(mmc_handle* h, const HostTrial& ht, double old_e[MMC_NE], double new_e[MMC_NE], const char* who) {
+// One launch per strict-mode trial (k_strict_trial): the result comes back through host-mapped pinned memory and the host
+// spins on its sequence number -- no D2H copy, no stream synchronisation.  Round 1 needed k_set_trial + k_sweep + k_finalize +
+// a copy + a synchronisation (37 us per c4_large_k trial).
+static int strict_trial(mmc_handle* h, const HostTrial& ht, int decide, double u, const char* who) {
     const DevConst& dc = h->dc;
     if (dc.shard_count > 1) return fail("%s: this handle is shard %d of %d; use mmc_shard_trial_begin/_end", who, dc.shard_rank, dc.shard_count);
     CK(cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
-    k_set_trial<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht);
-    launch_sweeps(h, st, ht.chain);
-    k_finalize<<<1, TAIL_THREADS, 0, st>>>(dc, h->cs, ht.chain, h->d_out);
-    h->launches += 2;
+    const unsigned long long seq = ++h->strict_seq;
+    k_strict_trial<<<dc.sweep_parts, SWEEP_THREADS, h->sweep_smem, st>>>(dc, h->cs, ht, decide, u, h->d_ticket, h->d_sout, seq);
+    h->launches += 1;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(h->h_out, h->d_out, (2 * MMC_NE + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    if (old_e) memcpy(old_e, h->h_out, MMC_NE * sizeof(double));
-    if (new_e) memcpy(new_e, h->h_out + MMC_NE, MMC_NE * sizeof(double));
+    volatile StrictOut* o = h->h_sout;
+    for (unsigned long long spins = 0; o->seq != seq; spins++) {
+        if ((spins & 0xfffffull) == 0xfffffull) {      // every ~1e6 spins: has the stream died?
+            const cudaError_t e = cudaStreamQuery(st);
+            if (e != cudaSuccess && e != cudaErrorNotReady) return fail("%s: kernel failed: %s", who, cudaGetErrorString(e));
+            if (e == cudaSuccess && o->seq != seq) return fail("%s: the trial kernel finished without reporting a result", who);
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    return 0;
+}
+
+static int trial_energy_impl(mmc_handle* h, const HostTrial& ht, double old_e[MMC_NE], double new_e[MMC_NE], const char* who) {
+    if (strict_trial(h, ht, 0, 0.0, who)) return 1;
+    if (old_e) memcpy(old_e, (const void*)h->h_sout->old_e, MMC_NE * sizeof(double));
+    if (new_e) memcpy(new_e, (const void*)h->h_sout->new_e, MMC_NE * sizeof(double));
     h->pending_chain = ht.chain; h->pending_kind = ht.kind; h->pending_res = ht.res;
+    return 0;
+}
+
+// SaveMoleculeState + ComputeOldEnergy + ComputeNewEnergy + mc_acceptance_probability + the accept test + Accept* / Reject* of
+// ONE move in one launch: `u` is the uniform the move routine draws for its accept test (translation.f90:66, rotation.f90:62,
+// create_molecule.f90:77, delete_molecule.f90:80), handed over with the proposal.  accepted: 1 / 0.
+extern "C" int mmc_trial_step(mmc_t* h, int c, int kind, int res, int mol, int res_new, const double* com_new, const double* offs_new, double u,
+                              double old_e[MMC_NE], double new_e[MMC_NE], double* prob, int* accepted) {
+    HostTrial ht;
+    if (check_trial(h, c, kind, res, mol, com_new, offs_new, ht, "mmc_trial_step", kind == MMC_SWAP ? res_new : -1)) return 1;
+    if (strict_trial(h, ht, 1, u, "mmc_trial_step")) return 1;
+    const StrictOut* o = h->h_sout;
+    if (old_e) memcpy(old_e, o->old_e, MMC_NE * sizeof(double));
+    if (new_e) memcpy(new_e, o->new_e, MMC_NE * sizeof(double));
+    if (prob) *prob = o->prob;
+    if (accepted) *accepted = o->accepted;
+    if (o->accepted == 1) {
+        int* cnt = h->h_count.data() + (size_t)c * MMC_MAX_RES;
+        if (kind == MMC_CREATION) cnt[res]++;
+        if (kind == MMC_DELETION) cnt[res]--;
+        if (kind == MMC_SWAP) { cnt[res]--; cnt[ht.res2]++; }
+    }
+    h->pending_chain = -1;
     return 0;
 }
 
@@ -1300,6 +1347,61 @@ extern "C" int mmc_dbg_intra_singlemol(mmc_t* h, int c, int res, int mol, double
     if (e_intra) *e_intra = o[MMC_E_INTRA];
     return 0;
 }
+// Measurement helper for bench.py's strict_mode object: n_moves translation moves of chain c driven from the host EXACTLY as
+// the Fortran Translation routine drives them (translation.f90:36-112: pick a molecule, displace its centre of mass by
+// (u - 1/2) step, ApplyPBC, energies, Metropolis test, accept / reject), through the public entry points -- fused = 1:
+// mmc_trial_step, one launch per move; fused = 0: mmc_trial_energy + host decision + mmc_trial_commit.  The host keeps its
+// own mirror of the coordinates like the Fortran driver does.  Returns wall seconds and the number of accepted moves.
+extern "C" int mmc_dbg_strict_loop(mmc_t* h, int c, int n_moves, uint64_t seed, int fused, double* seconds, int64_t* n_accepted) {
+    CHECK_CHAIN(h, c);
+    if (n_moves < 1 || !seconds) return fail("mmc_dbg_strict_loop: bad arguments");
+    const DevConst& dc = h->dc;
+    if (dc.tri) return fail("mmc_dbg_strict_loop: orthorhombic cells only");
+    if (dc.n_active < 1) return fail("mmc_dbg_strict_loop: no active residue");
+    const int r = dc.active_list[0], na = dc.natoms[r];
+    std::vector<int> cnt(dc.nres);
+    size_t nm = 0, nat = 0, mo = 0, ao = 0;
+    for (int q = 0; q < dc.nres; q++) { const size_t cap = dc.is_active[q] ? dc.cap[q] : dc.cap[q]; if (q < r) { } nm += cap; nat += cap * dc.natoms[q]; }
+    std::vector<double> com(3 * nm + 3), off(3 * nat + 3);
+    if (download_chain(h, c, cnt.data(), com.data(), off.data())) return 1;
+    for (int q = 0; q < r; q++) { mo += cnt[q]; ao += (size_t)cnt[q] * dc.natoms[q]; }
+    if (cnt[r] < 1) return fail("mmc_dbg_strict_loop: chain %d has no molecule of the first active type", c);
+    double tstep = 1.0, temp = 300.0;
+    CK(cudaMemcpy(&tstep, h->cs.tstep + c, sizeof(double), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&temp, h->cs.temp + c, sizeof(double), cudaMemcpyDeviceToHost));
+    uint64_t x = seed * 6364136223846793005ull + 1442695040888963407ull;
+    auto uni = [&]() { x = x * 6364136223846793005ull + 1442695040888963407ull; return (double)(x >> 11) * (1.0 / 9007199254740992.0); };
+    int64_t nacc = 0;
+    double o[MMC_NE], nw[MMC_NE];
+    CK(cudaStreamSynchronize(h->stream));
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < n_moves; i++) {
+        const int m = std::min((int)(uni() * cnt[r]), cnt[r] - 1);
+        double* cm = com.data() + (mo + m) * 3; const double* of = off.data() + (ao + (size_t)m * na) * 3;
+        double cn[3];
+        for (int d = 0; d < 3; d++) {
+            double v = cm[d] + (uni() - 0.5) * tstep - dc.lo[d];
+            v -= std::floor(v / dc.L[d]) * dc.L[d];
+            cn[d] = dc.lo[d] + v;
+        }
+        int acc = 0;
+        if (fused) {
+            double p;
+            if (mmc_trial_step(h, c, MMC_TRANSLATION, r, m, -1, cn, of, uni(), o, nw, &p, &acc)) return 1;
+        } else {
+            if (mmc_trial_energy(h, c, MMC_TRANSLATION, r, m, cn, of, o, nw)) return 1;
+            const double p = std::fmin(1.0, std::exp(-(nw[MMC_E_TOTAL] - o[MMC_E_TOTAL]) / temp));
+            acc = uni() <= p;
+            if (mmc_trial_commit(h, c, acc)) return 1;
+        }
+        if (acc) { nacc++; for (int d = 0; d < 3; d++) cm[d] = cn[d]; }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (n_accepted) *n_accepted = nacc;
+    return 0;
+}
+
 // test support: overwrite a chain's tracked energies and / or its tracked A(k) (resynchronising a long parity run with
 // its CPU checker after an accept/reject flip; the reference has no counterpart)
 extern "C" int mmc_dbg_set_tracked(mmc_t* h, int c, const double* energies, const double* sk) {

@@ -53,7 +53,7 @@ class StrictDriver:
     """Holds the host mirror of primary%mol_com / site_offset / num_residues for the ACTIVE residues
     exactly like the Fortran driver does, and the ``energy`` / ``counter`` globals."""
 
-    def __init__(self, system: System, gpu: ManiacGPU | None = None, chain=0, recalibrate=False):
+    def __init__(self, system: System, gpu: ManiacGPU | None = None, chain=0, recalibrate=False, fused=False):
         self.sys = system
         self.gpu = gpu if gpu is not None else ManiacGPU(system)
         self.chain = chain
@@ -68,6 +68,9 @@ class StrictDriver:
             self.com.append(com); self.off.append(off)
         self.translation_step, self.rotation_step = s.translation_step, s.rotation_step
         self.recalibrate = recalibrate
+        # fused: one mmc_trial_step per move (energies + accept test with the uniform drawn here + commit in ONE launch) instead of
+        # mmc_trial_energy + host decision + mmc_trial_commit; the uniform is drawn at the same place of the stream either way
+        self.fused = fused
         self.counter = dict(translations=0, rotations=0, creations=0, deletions=0, trial_translations=0,
                             trial_rotations=0, trial_creations=0, trial_deletions=0, swaps=0, trial_swaps=0)
         self.energy = np.zeros(6)
@@ -134,6 +137,22 @@ class StrictDriver:
                 out[a, i] = R[i, 0] * v[0] + R[i, 1] * v[1] + R[i, 2] * v[2]
         return out
 
+    def _trial(self, rng, kind, r, m, com, off, prob, r2=-1):
+        """energies, acceptance probability and decision of one move; `prob(old, new)` is the host's acceptance rule"""
+        if self.fused:
+            u = rng()
+            return self.gpu.trial_step(kind, r, m, com, off, u=u, res_new=r2, chain=self.chain)
+        if kind == MMC_SWAP:
+            old, new = self.gpu.trial_energy_swap(r, m, r2, com, off, chain=self.chain)
+        else:
+            old, new = self.gpu.trial_energy(kind, r, m, com, off, chain=self.chain)
+        p = prob(old, new)
+        return old, new, p, rng() <= p
+
+    def _commit(self, acc):
+        if not self.fused:
+            self.gpu.trial_commit(acc, chain=self.chain)
+
     def _record(self, kind, r, m, acc, old, new, p):
         rec = np.zeros(1, dtype=RECORD_DTYPE)[0]
         rec["kind"], rec["res"], rec["mol"], rec["accepted"], rec["prob"] = kind, r, m, acc, p
@@ -170,12 +189,11 @@ class StrictDriver:
             for d in range(3):
                 x = com[d] + u[d] * self.translation_step
                 com[d] = self.sys.box_lo[d] + f_modulo(x - self.sys.box_lo[d], self.sys.box_len[d])  # ApplyPBC
-        old, new = self.gpu.trial_energy(MMC_TRANSLATION, r, m, com, self.off[r][m], chain=self.chain)
-        p = self.mc_acceptance_probability(old, new, r, MMC_TRANSLATION)
-        acc = rng() <= p
+        old, new, p, acc = self._trial(rng, MMC_TRANSLATION, r, m, com, self.off[r][m],
+                                       lambda o, n: self.mc_acceptance_probability(o, n, r, MMC_TRANSLATION))
         if acc:
             self._accept_move(old, new); self.counter["translations"] += 1; self.com[r][m] = com
-        self.gpu.trial_commit(acc, chain=self.chain)
+        self._commit(acc)
         return self._record(MMC_TRANSLATION, r, m, acc, old, new, p)
 
     def Rotation(self, rng, r, m):
@@ -183,12 +201,11 @@ class StrictDriver:
             return None
         self.counter["trial_rotations"] += 1
         off = self.ApplyRandomRotation(rng, self.off[r][m], full=False)
-        old, new = self.gpu.trial_energy(MMC_ROTATION, r, m, self.com[r][m], off, chain=self.chain)
-        p = self.mc_acceptance_probability(old, new, r, MMC_ROTATION)
-        acc = rng() <= p
+        old, new, p, acc = self._trial(rng, MMC_ROTATION, r, m, self.com[r][m], off,
+                                       lambda o, n: self.mc_acceptance_probability(o, n, r, MMC_ROTATION))
         if acc:
             self._accept_move(old, new); self.counter["rotations"] += 1; self.off[r][m] = off
-        self.gpu.trial_commit(acc, chain=self.chain)
+        self._commit(acc)
         return self._record(MMC_ROTATION, r, m, acc, old, new, p)
 
     def CreateMolecule(self, rng, r, m):
@@ -206,27 +223,25 @@ class StrictDriver:
         else:
             off = self.ApplyRandomRotation(rng, self.off[r][0], full=True)  # geometry of slot 1 (Q9)
         self.com[r][m] = com; self.off[r][m] = off  # written at proposal time, kept on reject
-        old, new = self.gpu.trial_energy(MMC_CREATION, r, m, com, off, chain=self.chain)
-        p = self.mc_acceptance_probability(old, new, r, MMC_CREATION)
-        acc = rng() <= p
+        old, new, p, acc = self._trial(rng, MMC_CREATION, r, m, com, off,
+                                       lambda o, n: self.mc_acceptance_probability(o, n, r, MMC_CREATION))
         if acc:
             self._accept_insdel(old, new); self.counter["creations"] += 1
             if self.has_reservoir and self.rsv[r]:   # AcceptCreationMove :118-130: pool slot <- last pool slot
                 self.rsv[r][rsv] = self.rsv[r][-1]; self.rsv[r].pop()
         else:
             self.count[r] -= 1
-        self.gpu.trial_commit(acc, chain=self.chain)
+        self._commit(acc)
         return self._record(MMC_CREATION, r, m, acc, old, new, p)
 
     def DeleteMolecule(self, rng, r, m):
         if self.count[r] == 0:
             return None
         self.counter["trial_deletions"] += 1
-        old, new = self.gpu.trial_energy(MMC_DELETION, r, m, chain=self.chain)
         last = self.count[r] - 1
-        self.count[r] -= 1
-        p = self.mc_acceptance_probability(old, new, r, MMC_DELETION)
-        acc = rng() <= p
+        self.count[r] -= 1          # N is read after the count update (monte_carlo_utils.f90:199-214)
+        old, new, p, acc = self._trial(rng, MMC_DELETION, r, m, None, None,
+                                       lambda o, n: self.mc_acceptance_probability(o, n, r, MMC_DELETION))
         if acc:
             self._accept_insdel(old, new); self.counter["deletions"] += 1
             if self.has_reservoir:   # AcceptDeletionMove delete_molecule.f90:148-166 (appends slot `last`, three placement draws)
@@ -235,7 +250,7 @@ class StrictDriver:
             self.com[r][m] = self.com[r][last]; self.off[r][m] = self.off[r][last]  # RemoveMolecule
         else:
             self.count[r] += 1
-        self.gpu.trial_commit(acc, chain=self.chain)
+        self._commit(acc)
         return self._record(MMC_DELETION, r, m, acc, old, new, p)
 
     # mc_acceptance_probability_swap monte_carlo_utils.f90:228-268 (counts before the move)
@@ -265,15 +280,13 @@ class StrictDriver:
         com = self.com[r][m].copy()
         off = self.ApplyRandomRotation(rng, self.off[r2][0], full=True)
         self.com[r2][m2] = com; self.off[r2][m2] = off
-        old, new = self.gpu.trial_energy_swap(r, m, r2, com, off, chain=self.chain)
-        p = self.mc_acceptance_probability_swap(old, new, r, r2)
-        acc = rng() <= p
+        old, new, p, acc = self._trial(rng, MMC_SWAP, r, m, com, off, lambda o, n: self.mc_acceptance_probability_swap(o, n, r, r2), r2=r2)
         if acc:
             self._accept_insdel(old, new); self.counter["swaps"] += 1
             last = self.count[r] - 1
             self.com[r][m] = self.com[r][last]; self.off[r][m] = self.off[r][last]
             self.count[r] -= 1; self.count[r2] += 1
-        self.gpu.trial_commit(acc, chain=self.chain)
+        self._commit(acc)
         return self._record(MMC_SWAP, r + 256 * r2, m, acc, old, new, p)
 
     def AdjustMoveStepSizes(self):  # monte_carlo_utils.f90:99-129 (single-precision ratios, Q6)

@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop",
 ]
 
 _lib = None
@@ -81,6 +81,7 @@ def load():
     L.mmc_system_energy_all.argtypes = [vp, dp]
     L.mmc_trial_energy.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_trial_commit.argtypes = [vp, C.c_int, C.c_int]
+    L.mmc_trial_step.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, C.c_double, dp, dp, dp, ip]
     L.mmc_trial_energy_swap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
     L.mmc_sync_to_host.argtypes = [vp, C.c_int, ip, dp, dp, dp]
     L.mmc_get_sk.argtypes = [vp, C.c_int, dp]
@@ -95,6 +96,7 @@ def load():
     L.mmc_dbg_table_lookup.argtypes = [vp, C.c_int, dp, C.c_int, dp]
     L.mmc_dbg_erfc.argtypes = [vp, dp, C.c_int, dp]
     L.mmc_dbg_set_tracked.argtypes = [vp, C.c_int, dp, dp]
+    L.mmc_dbg_strict_loop.argtypes = [vp, C.c_int, C.c_int, C.c_uint64, C.c_int, dp, C.POINTER(C.c_int64)]
     L.mmc_dbg_phase_cycles.argtypes = [vp, C.POINTER(C.c_int64)]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
@@ -276,6 +278,16 @@ class ManiacGPU:
         _ck(load().mmc_trial_energy_swap(self.h, chain, res_old, mol, res_new, _dp(c), _dp(o), _dp(old), _dp(new)))
         return old, new
 
+    def trial_step(self, kind, res, mol, com_new=None, offs_new=None, u=0.0, res_new=-1, chain=0):
+        """one strict-mode move in one launch (energies + accept test with the host's uniform u + commit);
+        returns (old_e, new_e, prob, accepted)"""
+        old, new = np.zeros(MMC_NE), np.zeros(MMC_NE)
+        c = None if com_new is None else np.ascontiguousarray(com_new, dtype=np.float64)
+        o = None if offs_new is None else np.ascontiguousarray(offs_new, dtype=np.float64)
+        p, a = C.c_double(), C.c_int()
+        _ck(load().mmc_trial_step(self.h, chain, kind, res, mol, res_new, _dp(c), _dp(o), float(u), _dp(old), _dp(new), C.byref(p), C.byref(a)))
+        return old, new, p.value, bool(a.value)
+
     def trial_commit(self, accept, chain=0):
         _ck(load().mmc_trial_commit(self.h, chain, int(bool(accept))))
 
@@ -399,6 +411,13 @@ class ManiacGPU:
         a, b = C.c_int(), C.c_int()
         _ck(load().mmc_shard_range(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def strict_loop(self, n_moves, seed=1, fused=True, chain=0):
+        """n_moves host-driven translation moves through the strict-mode entry points; (seconds, accepted, launches)"""
+        t, a = C.c_double(), C.c_int64()
+        l0 = self.launch_count()
+        _ck(load().mmc_dbg_strict_loop(self.h, chain, n_moves, seed, int(fused), C.byref(t), C.byref(a)))
+        return t.value, int(a.value), self.launch_count() - l0
 
     def phase_cycles(self):
         """-DMMC_PHASE_TIMING builds: per-phase clock cycles (summed over CTAs and trials) and the trial count"""

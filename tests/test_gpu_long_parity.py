@@ -31,7 +31,7 @@ def test_strict_and_batched_trajectories_against_oracle():
     """C1 h2o_ads, C2 500-water box, C3 ZIF-8 + H2O, both quirk settings, strict mode and batched tape replay"""
     import long_parity as lp
     rows = lp.run_all(scale=SCALE, chunk=2000, with_bench=False, log=lambda m: print(m, flush=True))
-    assert len(rows) == 12
+    assert len(rows) == 18
     assert min(r["moves_compared"] for r in rows) >= 200
     check_rows(rows)
 
@@ -46,7 +46,7 @@ def test_bench_system_moves_against_oracle():
     ref, offs, ckpt = lp.oracle_reference(s, n, n, tape, start_energy=start)
     assert set(np.unique(ref["kind"])) >= {1, 2, 3, 4}
     rows = [fn(s, ref, offs, ckpt, n, tape, f"{name} / {mode}", start_energy=start).row()
-            for mode, fn in (("strict", lp.run_strict), ("batched tape", lp.run_batched))]
+            for mode, fn in (("strict", lp.run_strict), ("strict fused", lp.run_strict_fused), ("batched tape", lp.run_batched))]
     for r in rows:
         print(r)
         assert r["moves_compared"] == n

@@ -137,6 +137,30 @@ def test_strict_mode_trajectory(name, init_sk, deletion):
     g.close()
 
 
+@pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("zif8_h2o", 1, 1), ("mfi_co2", 1, 1), ("zif8_ch4o_h2o", 1, 1), ("dipole_tri", 1, 1)])
+def test_strict_mode_fused_trial_step(name, init_sk, deletion):
+    """mmc_trial_step: energies + acceptance probability + accept test (with the uniform the host drew) + commit in ONE launch,
+    results through host-mapped memory.  Same tape through the oracle: identical accept sequence, energies 1e-10; and the
+    state left on the device equals the oracle's."""
+    s = load_system(name, init_sk=init_sk, deletion_mode=deletion)
+    if name == "zif8_ch4o_h2o":
+        s.p_translation, s.p_rotation, s.p_swap = 0.25, 0.25, 0.3
+    tape = np.random.default_rng(43).random(6000)
+    o = orc.Oracle(s); o.system_energy(); ref = o.run(400, tape=tape)
+    g = ManiacGPU(s); drv = StrictDriver(s, g, fused=True); drv.ComputeSystemEnergy()
+    l0 = g.launch_count()
+    rng = TapeRng(tape); got = drv.MonteCarloLoop(rng, 1, 400)
+    assert g.launch_count() - l0 == int((ref["kind"] > 0).sum())          # exactly one launch per attempted move
+    compare_records(got, ref)
+    assert rng.pos == o.tape_used
+    cnt, com, off, e = g.sync_to_host(); c2, com2, off2 = o.state()
+    assert np.array_equal(cnt, c2) and np.array_equal(drv.count, c2)
+    np.testing.assert_allclose(com, com2, atol=1e-11); np.testing.assert_allclose(off, off2, atol=1e-12)
+    assert rel_err(e, o.energy()) < TOL and rel_err(drv.energy, o.energy()) < TOL
+    np.testing.assert_allclose(g.sk(), o.sk(), atol=1e-9)
+    g.close()
+
+
 @pytest.mark.parametrize("name,init_sk,deletion", [("zif8_h2o", 0, 0), ("h2o_ads", 1, 1), ("lj_gas", 0, 0), ("mfi_co2", 0, 0),
                                                    ("slit", 1, 1)])
 def test_batched_tape_replay(name, init_sk, deletion):

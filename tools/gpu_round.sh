@@ -11,7 +11,7 @@ if [ "$3" != "noref" ]; then
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2>&1; cat gpurun_out/${tag}_bench_ref.json
 fi
 if [ "$4" == "noncu" ]; then exit 0; fi
-CMD="python bench.py --moves 32 --steps 1 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --moves 32 --steps 1 --warmup 3 --no-cpu-baseline --no-extras"
 $CMD > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'k_chain_run|k_sweep|k_advance' -c 300 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu1.log 2>&1
 $CMD > gpurun_out/${tag}_plain2.log 2>&1 &&

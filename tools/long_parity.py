@@ -2,7 +2,7 @@
 
 Every case runs ONE recorded uniform stream through the oracle (the reference's sequential chain restated in C) and through
 the library twice -- strict mode (host proposals, one mmc_trial_energy + mmc_trial_commit per move, what the unmodified
-Fortran move routines would call) and batched mode (device proposals replaying the tape) -- and reports per run:
+Fortran move routines would call; and its one-launch form mmc_trial_step) and batched mode (device proposals replaying the tape) -- and reports per run:
 moves compared, the largest per-component relative error of the old/new energy vectors (conftest.record_errors), the
 largest relative error of the acceptance probability and the NUMBER OF ACCEPT/REJECT FLIPS.  A flip is not hidden: the
 two probabilities at the flip are printed (the uniform lies between them) and the GPU chain is resynchronised with the
@@ -116,11 +116,11 @@ def system_at(s, ckpt):
     return t
 
 
-def run_strict(s, ref, offs, ckpt, chunk, tape, label, start_energy=True):
+def run_strict(s, ref, offs, ckpt, chunk, tape, label, start_energy=True, fused=False):
     from maniac_mc_b200.driver import StrictDriver, TapeRng
     from maniac_mc_b200.lib import ManiacGPU
     t = Tally(label)
-    g = ManiacGPU(s); drv = StrictDriver(s, g)
+    g = ManiacGPU(s); drv = StrictDriver(s, g, fused=fused)
     if start_energy:
         drv.ComputeSystemEnergy()
     n_moves = len(ref)
@@ -131,12 +131,17 @@ def run_strict(s, ref, offs, ckpt, chunk, tape, label, start_energy=True):
         if t.add(got, ref[a:a + n], a):
             g.close()
             s2 = system_at(s, ckpt[ci])
-            g = ManiacGPU(s2); drv = StrictDriver(s2, g)
+            g = ManiacGPU(s2); drv = StrictDriver(s2, g, fused=fused)
             g.system_energy()
             g.dbg_set_tracked(ckpt[ci][1], ckpt[ci][2])
             drv.energy = ckpt[ci][1].copy()
     g.close()
     return t
+
+
+def run_strict_fused(s, ref, offs, ckpt, chunk, tape, label, start_energy=True):
+    """strict mode through mmc_trial_step: one launch per move, the accept test on the device with the host's uniform"""
+    return run_strict(s, ref, offs, ckpt, chunk, tape, label, start_energy, fused=True)
 
 
 def run_batched(s, ref, offs, ckpt, chunk, tape, label, start_energy=True):
@@ -204,7 +209,7 @@ def run_all(scale=1.0, chunk=2000, with_bench=True, log=print, seed=2025):
         ths[i].join()
         ref, offs, ckpt = refs[i]
         acc = float(ref["accepted"].mean())
-        for mode, fn in (("strict", run_strict), ("batched tape", run_batched)):
+        for mode, fn in (("strict", run_strict), ("strict fused", run_strict_fused), ("batched tape", run_batched)):
             t0 = time.time()
             t = fn(s, ref, offs, ckpt, min(chunk, n), tapes[i], f"{name} / {mode}", start_energy=start)
             r = t.row(); r["seconds"] = round(time.time() - t0, 1); r["accept_ratio"] = round(acc, 4)
