@@ -25,11 +25,19 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
     sweep_load_tables(dc, s);
     pair_count_init(s);
     for (int st = 0; st < n_steps; st++) {
-        if (threadIdx.x == 0) {   // the RNG source is re-read here: it must not occupy registers during the sweeps
-            RngSrc rs = ctl->rng;
-            rs.step += (unsigned long long)st;
-            propose_move(dc, cs, rs, c, *s.trial);
-            if (s.trial->error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
+        if (threadIdx.x < 32) {
+            // the step's uniforms: Philox4x32-10 is ~120 dependent integer instructions per draw; 16 lanes compute draws
+            // 0..15 side by side instead of thread 0 computing 6-10 of them one after the other (tape replay reads the tape)
+            const bool philox = ctl->rng.tape == nullptr;
+            if (philox && threadIdx.x < MMC_PRE_DRAWS)
+                s.mol->u[threadIdx.x] = philox_uniform(ctl->rng.seed, cs.chain_id[c], ctl->rng.step + (unsigned long long)st, threadIdx.x);
+            __syncwarp();
+            if (threadIdx.x == 0) {   // the RNG source is re-read here: it must not occupy registers during the sweeps
+                RngSrc rs = ctl->rng;
+                rs.step += (unsigned long long)st;
+                propose_move(dc, cs, rs, c, *s.trial, philox ? s.mol->u : nullptr);
+                if (s.trial->error) atomicOr(cs.error_flag, MMC_ERRF_CAPACITY);
+            }
         }
         __syncthreads();
         MMC_TSTAMP(0);
@@ -41,7 +49,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
                 finalize_trial(dc, cs, c, t, s.mol->sums);
                 RngSrc rs = ctl->rng;
                 rs.step += (unsigned long long)st;
-                Rng rng{&rs, cs, c, t.draw};  // the accept draw follows the proposal's draws
+                Rng rng{&rs, cs, c, t.draw, rs.tape ? nullptr : s.mol->u};  // the accept draw follows the proposal's draws
                 const double u = rng.next();
                 const int acc = (phases == 3 && u <= t.prob) ? 1 : 0;
                 // AcceptDeletionMove draws three more uniforms to place the molecule in the reservoir box (delete_molecule.f90:150-151)

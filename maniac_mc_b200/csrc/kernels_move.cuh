@@ -13,8 +13,10 @@ __device__ __forceinline__ size_t g_atom(const DevConst& dc, int c, int r, int m
     return (size_t)c * dc.g_atoms + dc.g_atom_base[r] + (size_t)m * dc.natoms[r] + a;
 }
 
+#define MMC_PRE_DRAWS 16   // uniforms of one MC step computed ahead by 16 lanes (a step draws at most 9 + 1 + 3)
 struct Rng {
     const RngSrc* src; ChainState cs; int c; int draw;
+    const double* pre = nullptr;   // Philox draws 0 .. MMC_PRE_DRAWS-1 of this step, computed in parallel (same values as below)
     __device__ double next() {
         if (src->tape) {
             // a tape shorter than the draws consumed must not run into the next chain's tape (a host-side replay aborts on
@@ -23,6 +25,7 @@ struct Rng {
             if (p >= src->tape_stride) { atomicOr(cs.error_flag, MMC_ERRF_TAPE); return 0.5; }
             return src->tape[(size_t)c * src->tape_stride + p];
         }
+        if (pre && draw < MMC_PRE_DRAWS) return pre[draw++];
         return philox_uniform(src->seed, cs.chain_id[c], src->step, (uint32_t)draw++);
     }
 };
@@ -135,10 +138,10 @@ __global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
 
 // batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
 // proposal geometry, draw order as in SURVEY 3.8.  Single thread per chain.
-__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c, Trial& t) {
+__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c, Trial& t, const double* pre = nullptr) {
     t.kind = 0; t.error = 0; t.accepted = 0;
     for (int i = 0; i < MMC_NE; i++) { t.old_e[i] = 0.0; t.new_e[i] = 0.0; }
-    Rng rng{&rs, cs, c, 0};
+    Rng rng{&rs, cs, c, 0, pre};
     if (dc.n_active == 0) { t.draw = 0; return; }
     // PickRandomResidueType monte_carlo_utils.f90:136-164
     const int r = dc.active_list[(int)(rng.next() * dc.n_active)];

@@ -40,6 +40,7 @@ struct MolS {
     signed char term[2 * MMC_MAX_MOL_ATOMS];  // reciprocal terms: +(a+1) = atom a added, -(a+1) = atom a removed
     double sums[6];        // block sums of this trial: parked here between the phases so they hold no registers
     unsigned int work[2];  // executed real-space work of this CTA (distances formed, pairs inside reach)
+    double u[16];          // this step's Philox uniforms, drawn ahead by 16 lanes (MMC_PRE_DRAWS)
 #ifdef MMC_PHASE_TIMING
     long long t_last; unsigned long long phase[8];
 #endif

@@ -383,17 +383,20 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     h->chain_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, h->chain_threads, off);
     if (h->chain_smem > 200 * 1024) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
                                                  dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->chain_smem);
-    CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
-    CK(cudaFuncSetAttribute(k_strict_trial, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->sweep_smem));
-    if (h->dc.tri) {
-        CK(cudaFuncSetAttribute(k_chain_run<256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-        CK(cudaFuncSetAttribute(k_chain_run<512, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-        CK(cudaFuncSetAttribute(k_chain_run<1024, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-    } else {
-        CK(cudaFuncSetAttribute(k_chain_run<256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-        CK(cudaFuncSetAttribute(k_chain_run<512, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-        CK(cudaFuncSetAttribute(k_chain_run<1024, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->chain_smem));
-    }
+    // The opt-in limit is a property of the FUNCTION, shared by every handle of the process: set it to the ceiling once instead
+    // of to this handle's need (a second, smaller system must not lower it under a live handle's launches -- r2e: "invalid
+    // argument" on the bench system's strict-mode launch after a ZIF-8 handle had been created)
+    const int smem_cap = 200 * 1024;
+    if (h->sweep_smem > (size_t)smem_cap) return fail("kmax=(%d,%d,%d) with %d-atom molecules needs %zu B of shared memory for the phase tables",
+                                                       dc.kmax[0], dc.kmax[1], dc.kmax[2], dc.max_nat, h->sweep_smem);
+    CK(cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_strict_trial, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<256, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<512, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<1024, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<512, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    CK(cudaFuncSetAttribute(k_chain_run<1024, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     CK(dalloc(h, &h->cs.part, (size_t)dc.n_chains * dc.sweep_parts * 6));
     return 0;
 }

@@ -11,9 +11,14 @@ import bench  # noqa: E402
 from maniac_mc_b200.lib import ManiacGPU  # noqa: E402
 
 chains = int(sys.argv[1]) if len(sys.argv) > 1 else 592
-args = argparse.Namespace(framework=50000, guests=200)
-s = bench.make_system(args)
+workload = sys.argv[2] if len(sys.argv) > 2 else "c4_large_k"
+if workload == "c4_large_k":
+    s = bench.make_system(argparse.Namespace(framework=50000, guests=200))
+else:       # a fixture of tests/golden, e.g. zif8_h2o (the C5 isotherm's system)
+    from maniac_mc_b200.system import System
+    s = System.load(os.path.join(ROOT, "tests", "golden", workload + ".npz")); s.init_sk, s.deletion_mode = 1, 1
 g = ManiacGPU(s, n_chains=chains)
+print(f"# workload {workload}: K = {g.nk}")
 for c in range(chains):
     g.set_chain_params(c, bench.chain_fugacity(s, c), s.temperature); g.set_chain_id(c, c)
 g.system_energy_all()
