@@ -297,6 +297,16 @@ int mmc_dbg_intra_singlemol(mmc_t* handle, int chain, int res, int mol, double* 
 int mmc_dbg_table_lookup(mmc_t* handle, int which, const double* r, int n, double* out);
 /* device erfc used by the pair sweep, for accuracy tests */
 int mmc_dbg_erfc(mmc_t* handle, const double* x, int n, double* out);
+/* Allocation-free variant of mmc_dbg_erfc.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernel and same results as mmc_dbg_erfc, but it calls no cudaMalloc / cudaFree / allocating routine: the
+ * device staging scratch is one file-scope device array of MMC_NOALLOC_MAX_N inputs + MMC_NOALLOC_MAX_N outputs (1 MiB) that
+ * every GPU loading the library holds until exit.  x and out are host buffers of n doubles owned by the caller.
+ * n > MMC_NOALLOC_MAX_N is rejected with an error.  All calls on one GPU share the scratch: it keeps the last call's contents
+ * (nothing needs clearing: every slot that is read was written by this call first), and calls that overlap on the same GPU
+ * race on it -- serialise them.  Returns after its own work has drained. */
+#define MMC_NOALLOC_MAX_N 65536
+int mmc_erfc_noalloc(mmc_t* handle, const double* x, int n, double* out);
 /* measurement helper (bench.py strict_mode): n_moves translation moves of one chain driven from the host the way the
  * Fortran Translation routine drives them, through mmc_trial_step (fused = 1: one launch per move) or through
  * mmc_trial_energy + mmc_trial_commit (fused = 0); wall seconds and accepted moves */

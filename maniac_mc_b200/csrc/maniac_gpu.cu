@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <mutex>
 #include <numeric>
 
 static thread_local std::string g_err;
@@ -1439,6 +1440,55 @@ extern "C" int mmc_dbg_table_lookup(mmc_t* h, int which, const double* r, int n,
     return run_elementwise(h, which, r, n, out);
 }
 extern "C" int mmc_dbg_erfc(mmc_t* h, const double* x, int n, double* out) { return run_elementwise(h, -1, x, n, out); }
+
+// ---- allocation-free variant of mmc_dbg_erfc (no counterpart in the reference) ----
+// For callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the same kernel as mmc_dbg_erfc (k_erfc_test: the per-move sweep's erfc, Coulomb-kernel table + slow path), but
+// the device staging scratch that run_elementwise cudaMallocs and frees on every call lives in ONE file-scope device array of
+// fixed size.  Every GPU that loads the library holds these 2 x MMC_NOALLOC_MAX_N doubles (1 MiB) until the process exits.
+//   * g_noalloc_scratch below is, in HOST code, only a host-side stand-in for the symbol -- NOT a device address.  The device
+//     address is taken once per device, with that device current, by cudaGetSymbolAddress and cached; only that pointer is
+//     ever handed to a kernel or a copy.
+//   * All calls on one GPU share the array and it keeps the previous call's contents.  Nothing here has to start at zero:
+//     the first n input slots are overwritten by the upload and the first n output slots by the kernel before they are read,
+//     and nothing beyond n is read.  Calls that OVERLAP on the GPU (two handles / two host threads on one device) race on it:
+//     the caller serialises them.  This function itself returns only after its own work on the stream has drained.
+static __device__ __align__(256) double g_noalloc_scratch[2 * MMC_NOALLOC_MAX_N];   // [0, MAX): input staging, [MAX, 2 MAX): output
+#define MMC_NOALLOC_MAX_DEVICES 64
+static double* g_noalloc_ptr[MMC_NOALLOC_MAX_DEVICES] = {nullptr};   // device address of g_noalloc_scratch on device d
+static std::mutex g_noalloc_mutex;
+
+// set-up, once per device; the caller has made `device` current
+static int noalloc_scratch_for(int device, double** out) {
+    if (device < 0 || device >= MMC_NOALLOC_MAX_DEVICES) return fail("mmc_erfc_noalloc: device ordinal %d not supported (max %d)", device, MMC_NOALLOC_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        double* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return fail("mmc_erfc_noalloc: cudaGetSymbolAddress failed on device %d: %s", device, cudaGetErrorString(e));
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return 0;
+}
+
+extern "C" int mmc_erfc_noalloc(mmc_t* h, const double* x, int n, double* out) {
+    if (!h || !x || !out) return fail("mmc_erfc_noalloc: null argument");
+    if (n < 1) return fail("mmc_erfc_noalloc: n must be >= 1");
+    if (n > MMC_NOALLOC_MAX_N) return fail("mmc_erfc_noalloc: n = %d exceeds the fixed scratch of MMC_NOALLOC_MAX_N = %d values; split the call or use mmc_dbg_erfc", n, MMC_NOALLOC_MAX_N);
+    CK(cudaSetDevice(h->device));
+    double* scratch = nullptr;
+    if (noalloc_scratch_for(h->device, &scratch)) return 1;
+    double* d_in = scratch; double* d_out = scratch + MMC_NOALLOC_MAX_N;
+    cudaStream_t st = h->stream;
+    CK(cudaMemcpyAsync(d_in, x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+    k_erfc_test<<<(n + 255) / 256, 256, 0, st>>>(h->dc, d_in, n, d_out);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, d_out, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return 0;
+}
 extern "C" void* mmc_stream(mmc_t* h) { return h ? (void*)h->stream : nullptr; }
 extern "C" int64_t mmc_launch_count(const mmc_t* h) { return h ? h->launches : -1; }
 extern "C" int mmc_pair_work(mmc_t* h, int64_t out[2]) {

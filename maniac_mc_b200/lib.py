@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop", "mmc_erfc_noalloc",
 ]
 
 _lib = None
@@ -95,6 +95,7 @@ def load():
     L.mmc_dbg_intra_singlemol.argtypes = [vp, C.c_int, C.c_int, C.c_int, dp]
     L.mmc_dbg_table_lookup.argtypes = [vp, C.c_int, dp, C.c_int, dp]
     L.mmc_dbg_erfc.argtypes = [vp, dp, C.c_int, dp]
+    L.mmc_erfc_noalloc.argtypes = [vp, dp, C.c_int, dp]
     L.mmc_dbg_set_tracked.argtypes = [vp, C.c_int, dp, dp]
     L.mmc_dbg_strict_loop.argtypes = [vp, C.c_int, C.c_int, C.c_uint64, C.c_int, dp, C.POINTER(C.c_int64)]
     L.mmc_dbg_phase_cycles.argtypes = [vp, C.POINTER(C.c_int64)]
@@ -373,6 +374,11 @@ class ManiacGPU:
     def dbg_erfc(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64); out = np.zeros_like(x)
         _ck(load().mmc_dbg_erfc(self.h, _dp(x), len(x), _dp(out))); return out
+
+    def erfc_noalloc(self, x):
+        """mmc_erfc_noalloc: same results as dbg_erfc without any device allocation (fixed 65536-value scratch per GPU)"""
+        x = np.ascontiguousarray(x, dtype=np.float64); out = np.zeros_like(x)
+        _ck(load().mmc_erfc_noalloc(self.h, _dp(x), len(x), _dp(out))); return out
 
     def dbg_set_tracked(self, energies=None, sk=None, chain=0):
         """overwrite tracked energies [6] and / or tracked A(k) (complex [K]) of one chain (test support)"""
