@@ -79,6 +79,23 @@ module maniac_gpu_iface
             type(c_ptr), value :: handle
             integer(c_int), value :: chain, accept
         end function
+        !> one strict-mode move in ONE launch: energies + mc_acceptance_probability + the test u <= prob + Accept*/Reject*
+        integer(c_int) function mmc_trial_step(handle, chain, kind, res, mol, res_new, com_new, offs_new, u, old_e, new_e, prob, accepted) &
+                bind(C, name="mmc_trial_step")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle
+            integer(c_int), value :: chain, kind, res, mol, res_new
+            real(c_double), intent(in) :: com_new(3), offs_new(*)
+            real(c_double), value :: u
+            real(c_double), intent(out) :: old_e(6), new_e(6), prob
+            integer(c_int), intent(out) :: accepted
+        end function
+        !> ComputeSystemEnergy of every chain of the handle (framework terms once per handle); out(6, n_chains)
+        integer(c_int) function mmc_system_energy_all(handle, out) bind(C, name="mmc_system_energy_all")
+            import :: c_int, c_ptr, c_double
+            type(c_ptr), value :: handle
+            real(c_double), intent(out) :: out(*)
+        end function
         integer(c_int) function mmc_sync_to_host(handle, chain, count, com, offsets, energies) bind(C, name="mmc_sync_to_host")
             import :: c_int, c_ptr, c_double
             type(c_ptr), value :: handle
