@@ -66,6 +66,7 @@ struct SweepCtx {
     double* red;     // [6 * warps]
     MolS* mol;
     Trial* trial;         // the pending trial of this CTA's chain (batched kernel, fused strict-mode kernel)
+    unsigned char* cscr;  // [warps][32] lane ids exchanged by compact_push
     int nx, ny, nz, zs;   // nz = kmax_z + 1
 };
 
@@ -99,6 +100,7 @@ __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, con
     off[9] = o; o += (size_t)2 * (threads / 4) * zs * sizeof(double2);
 #endif
     off[10] = o; o += (sizeof(Trial) + 15) / 16 * 16;
+    off[11] = o; o += (size_t)(threads / 32) * 32;   // compacted sweep: 32 lane ids per warp
     return o;
 }
 
@@ -114,7 +116,7 @@ __device__ __forceinline__ SweepCtx sweep_carve(const DevConst& dc, unsigned cha
 #else
     s.Z = (double2*)(smem + off[4]);
 #endif
-    s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]); s.trial = (Trial*)(smem + off[10]);
+    s.red = (double*)(smem + off[5]); s.mol = (MolS*)(smem + off[6]); s.trial = (Trial*)(smem + off[10]); s.cscr = smem + off[11];
     s.mask = (uint32_t*)(smem + off[7]); s.prefix = (int*)(s.mask + CULL_CHUNK / 32);
     s.list = (uint16_t*)(smem + off[8]);
 #ifndef MMC_RECIP_DMMA
@@ -351,22 +353,30 @@ __device__ __forceinline__ void pair_two(const DevConst& dc, const PairConst& pc
 
 // one "other" atom against every atom of the moved molecule, old and/or new geometry
 // TRI: tilted cell; the OLD / NEW sets are then also masked at run time (one instantiation serves every move type)
-template <bool OLD, bool NEW, bool SHIFT, bool TRI>
+// SHIFT path, step 1: move the other atom to the periodic image nearest the molecule's centre (exact for every pair within
+// reach, shift_ok) and test it against the molecule's sphere.  Returns false when it is beyond reach of every moved atom.
+template <bool TRI>
+__device__ __forceinline__ bool pair_shift(const DevConst& dc, const PairConst& pc, const MolS& m, double& xj, double& yj, double& zj) {
+    double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
+    if (TRI) {   // the image inside the brick around the molecule's centre
+        min_image_tri_brick(dc, dx, dy, dz);
+        xj = m.cc[0] + dx; yj = m.cc[1] + dy; zj = m.cc[2] + dz;
+    } else {
+        const double big = 6755399441055744.0;
+        const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
+        xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
+        dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
+    }
+    return !(fma(dx, dx, fma(dy, dy, dz * dz)) > m.cc[3]);
+}
+
+// PREP: the atom was already shifted and sphere-tested by pair_shift (compacted sweep)
+template <bool OLD, bool NEW, bool SHIFT, bool TRI, bool PREP = false>
 __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
                                           double qj, int tj, double (&acc)[4], unsigned& cnt) {
     const MolS& m = *s.mol;
-    if (SHIFT) {
-        double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
-        if (TRI) {   // the image inside the brick around the molecule's centre: exact for every pair within reach (shift_ok)
-            min_image_tri_brick(dc, dx, dy, dz);
-            xj = m.cc[0] + dx; yj = m.cc[1] + dy; zj = m.cc[2] + dz;
-        } else {
-            const double big = 6755399441055744.0;
-            const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
-            xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
-            dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
-        }
-        if (fma(dx, dx, fma(dy, dy, dz * dz)) > m.cc[3]) return;  // beyond reach of every atom of the molecule
+    if (SHIFT && !PREP) {
+        if (!pair_shift<TRI>(dc, pc, m, xj, yj, zj)) return;  // beyond reach of every atom of the molecule
     }
     const bool use_old = OLD && (!TRI || m.do_old), use_new = NEW && (!TRI || m.do_new);
     const bool qj_ok = fabs(qj) >= MMC_ERR;
@@ -390,6 +400,49 @@ __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& p
         if (use_old) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.po[a][0], yj - m.po[a][1], zj - m.po[a][2], qq, charged, lj, acc[0], acc[1], cnt);
         if (use_new) pair_one<SHIFT, TRI>(dc, pc, s.gtab, xj - m.pn[a][0], yj - m.pn[a][1], zj - m.pn[a][2], qq, charged, lj, acc[2], acc[3], cnt);
     }
+}
+
+// ---- compacted sweep (SHIFT path), opt-in with -DMMC_COMPACT ----------------------------------------------------------
+// Measured NEUTRAL (r2j A/B, profiles/r2j_ab_compact.log: 2.700 vs 2.702 M moves/s): the real-space phase is bound by the BYTES
+// its table look-ups move through the shared-memory pipe, and those scale with the active lanes either way; full warps only
+// save issue slots, which are not the limiter.  Kept for systems whose tiles are much coarser than the sphere.
+// Survivors of the sphere test carried by a warp: lanes [0, n) hold one atom each (already shifted to its nearest image).
+struct CompactQ { double x, y, z, q; int t, n; };
+
+// All 32 lanes call this with their candidate atom (`in`: it passed pair_shift).  The survivors are appended to the carried
+// set in lane order; every time 32 are held the loop over the moved atoms runs on the full warp.  flush: evaluate whatever
+// is left (the last call of a trial).  The lane that holds entry e of the new survivors is found through 32 bytes of
+// per-warp shared scratch (each survivor writes its lane id at its rank), the data moves by warp shuffles.
+template <bool OLD, bool NEW, bool TRI>
+__device__ __forceinline__ void compact_push(const DevConst& dc, const PairConst& pc, const SweepCtx& s, CompactQ& cq, bool in, double xj, double yj,
+                                             double zj, double qj, int tj, bool flush, double (&acc)[4], unsigned& cnt) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    unsigned char* scr = s.cscr + (threadIdx.x >> 5) * 32;
+    const unsigned mask = __ballot_sync(full, in);
+    const int c = __popc(mask);
+    if (in) scr[__popc(mask & ((1u << lane) - 1u))] = (unsigned char)lane;
+    __syncwarp();
+    int n = cq.n, consumed = 0;
+    while (consumed < c || (flush && n > 0)) {
+        const int take = min(c - consumed, 32 - n);
+        if (take > 0) {
+            const int e = lane - n;                                   // lanes [n, n + take) take new survivors consumed + e
+            const bool mine = e >= 0 && e < take;
+            const int src = mine ? (int)scr[consumed + e] : lane;
+            const double vx = __shfl_sync(full, xj, src), vy = __shfl_sync(full, yj, src), vz = __shfl_sync(full, zj, src), vq = __shfl_sync(full, qj, src);
+            const int vt = __shfl_sync(full, tj, src);
+            if (mine) { cq.x = vx; cq.y = vy; cq.z = vz; cq.q = vq; cq.t = vt; }
+            n += take; consumed += take;
+        }
+        if (n == 32 || (flush && consumed == c && n > 0)) {
+            if (lane < n) pair_atom<OLD, NEW, true, TRI, true>(dc, pc, s, dc.ntypes, cq.x, cq.y, cq.z, cq.q, cq.t, acc, cnt);
+            __syncwarp();
+            n = 0;
+        }
+    }
+    cq.n = n;
+    __syncwarp();   // scr is rewritten by the next call
 }
 
 // can tile `t` hold an atom within reach of the moved molecule?  periodic point-to-box distance per axis
@@ -436,6 +489,7 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
     PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base};
     const bool cull = dc.reach2 < 1e300;
+    CompactQ cq = {0.0, 0.0, 0.0, 0.0, 0, 0};   // compacted sweep (SHIFT): survivors carried between tiles
     int item0 = 0;
     for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
         const int n = min(CULL_CHUNK, dc.n_tiles - base);
@@ -467,6 +521,24 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
         }
         __syncthreads();
         const int nlist = m.nlist;
+#ifdef MMC_COMPACT
+        if (SHIFT) {
+            // Compacted sweep: only ~half of the lanes of a visited tile hold an atom inside the molecule's sphere (tile boxes
+            // are coarser than the sphere; r2f ncu: 23.8 of 32 threads active per instruction).  Each warp therefore shifts and
+            // sphere-tests a tile's atoms (cheap), carries the survivors in registers and runs the expensive loop over the moved
+            // atoms (4 x 2 pair evaluations with 9-coefficient table lookups each) only on FULL batches of 32 survivors.
+            // Survivors keep their tile order, so the summation order stays deterministic.
+            for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
+                const int j = (base + (int)s.list[it]) * TILE + lane;
+                double xj = 0.0, yj = 0.0, zj = 0.0, qj = 0.0; int tj = 0; bool in = false;
+                if (j < dc.n_fw) {
+                    xj = dc.sx[j]; yj = dc.sy[j]; zj = dc.sz[j]; qj = dc.sq[j]; tj = dc.stype[j];
+                    in = pair_shift<TRI>(dc, pc, m, xj, yj, zj);
+                }
+                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, acc, cnt);
+            }
+        } else
+#endif
 #ifndef MMC_NO_TILE_PREFETCH
         {   // the next tile's atom is loaded (L2 latency) before this tile's pairs are evaluated
             int it = (gw + gstride - item0 % gstride) % gstride;
@@ -504,6 +576,21 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
         const size_t base = (size_t)c * dc.g_atoms + dc.g_atom_base[r];
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < ntile; it += gstride) {
             const int i = it * 32 + lane;
+#ifdef MMC_COMPACT
+            if (SHIFT) {
+                double xj = 0.0, yj = 0.0, zj = 0.0, qj = 0.0; int tj = 0; bool in = false;
+                if (i < n_at) {
+                    const int mol = i / na, a = i - mol * na;
+                    if (!(m.excl && r == m.res && mol == m.mol)) {
+                        xj = cs.gx[base + i]; yj = cs.gy[base + i]; zj = cs.gz[base + i];
+                        qj = dc.res_q[r * MMC_MAX_MOL_ATOMS + a]; tj = dc.res_type[r * MMC_MAX_MOL_ATOMS + a];
+                        in = pair_shift<TRI>(dc, pc, m, xj, yj, zj);
+                    }
+                }
+                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, acc, cnt);
+                continue;
+            }
+#endif
             if (i < n_at) {
                 const int mol = i / na, a = i - mol * na;
                 if (!(m.excl && r == m.res && mol == m.mol))
@@ -513,6 +600,9 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
         }
         item0 += ntile;
     }
+#ifdef MMC_COMPACT
+    if (SHIFT) compact_push<OLD, NEW, TRI>(dc, pc, s, cq, false, 0.0, 0.0, 0.0, 0.0, 0, true, acc, cnt);   // the partial last batch
+#endif
 }
 
 template <int NT, bool TRI>

@@ -1,0 +1,9 @@
+#!/bin/bash
+# round 2: warp-level compaction of in-sphere atoms in the real-space sweep: GPU suite, phase timing, A/B
+tag=${1:-r2j}
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -q -x 2>&1 | tail -n 15 > gpurun_out/${tag}_pytest_gpu.log; cat gpurun_out/${tag}_pytest_gpu.log
+MANIAC_GPU_LIB=maniac_mc_b200/ab/lib_T_timing.so python tools/phase_timing.py 592 c4_large_k > gpurun_out/${tag}_phase_timing.log 2>&1
+MANIAC_GPU_LIB=maniac_mc_b200/ab/lib_T_timing.so python tools/phase_timing.py 512 zif8_h2o >> gpurun_out/${tag}_phase_timing.log 2>&1; cat gpurun_out/${tag}_phase_timing.log
+one() { MANIAC_GPU_LIB=$1 python bench.py --no-cpu-baseline --no-extras --steps 5 --warmup 3 2>&1 | python -c "import sys,json; d=json.loads(sys.stdin.readlines()[-1]); r=d['roofline']; print('$2', round(d['value']), r['phase_only_ms'], 'frac', round(r['frac'],4), d['clocks']['sm_mhz'], d['clocks']['reasons'])"; }
+{ for i in 1 2 3; do for v in O_nocompact N_compact; do one maniac_mc_b200/ab/lib_$v.so $v; done; done; } > gpurun_out/${tag}_ab.log 2>&1; cat gpurun_out/${tag}_ab.log
