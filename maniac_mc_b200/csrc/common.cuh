@@ -67,6 +67,7 @@ struct DevConst {
     int n_tiles;
     const double* gtab;            // [(MMC_GTAB_DEG+1)][MMC_GTAB_MAXSEG] Coulomb kernel table for this alpha
     int gtab_base;                 // segment index of s = gtab_smin
+    int gtab_deg_start[2];         // segments >= [0] are fitted with degree D - 1, >= [1] with D - 2 (their top coefficients are not loaded)
     double gtab_smin, gtab_smax;   // table domain in r^2; outside it coul_kernel_slow is used
     // reciprocal work items (build_sweep_layout): one per (kx, ky) row and kz >= 0, serving k(+kz) and k(-kz).
     // .x = kx | (ky+kmax_y)<<10 | kz<<21 | flag<<31, .y = index of k(+kz); index of k(-kz) = .y - 2 kz + flag
@@ -227,21 +228,24 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
                                                  // [degree][segment]: the coefficient loads get immediate offsets (a run-time stride
                                                  // cost one integer multiply-add per load and 10 % of the real-space phase, r2b A/B)
 __device__ __noinline__ double coul_kernel_slow(double s, double alpha) { const double r = sqrt(s); return erfc(alpha * r) / r; }
-__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base) {
+__device__ __forceinline__ double coul_kernel_tab(double s, const double* tab, int base, int i1, int i2) {
     const int hi = __double2hiint(s), lo = __double2loint(s);
     const int idx = (hi >> (20 - MMC_GTAB_MBITS)) - base;
     const double f = __hiloint2double(0x3FF00000 | ((hi & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
                                           (int)((unsigned)lo >> (32 - MMC_GTAB_MBITS)), lo << MMC_GTAB_MBITS);
     const double t = fma(2.0, f, -3.0);
     const double* c = tab + idx;
-    double p = c[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+    // far segments are fitted with a lower degree (build_coulomb_table): their top one / two coefficients are not loaded
+    double p = 0.0;
+    if (idx < i1) p = c[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+    if (idx < i2) p = fma(p, t, c[(MMC_GTAB_DEG - 1) * MMC_GTAB_MAXSEG]);   // p == 0 here for [i1, i2): gives the coefficient itself
 #pragma unroll
-    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) p = fma(p, t, c[d * MMC_GTAB_MAXSEG]);
+    for (int d = MMC_GTAB_DEG - 2; d >= 0; d--) p = fma(p, t, c[d * MMC_GTAB_MAXSEG]);
     return p;
 }
 // two evaluations in lockstep (old and new geometry of one pair): two independent Horner chains instead of two dependent
 // ones back to back -- the real-space sweep is bound by the latency of these chains (r2c phase timing), not by a pipe
-__device__ __forceinline__ void coul_kernel_tab2(double sa, double sb, const double* tab, int base, double& ga, double& gb) {
+__device__ __forceinline__ void coul_kernel_tab2(double sa, double sb, const double* tab, int base, int i1, int i2, double& ga, double& gb) {
     const int hia = __double2hiint(sa), loa = __double2loint(sa), hib = __double2hiint(sb), lob = __double2loint(sb);
     const int ia = (hia >> (20 - MMC_GTAB_MBITS)) - base, ib = (hib >> (20 - MMC_GTAB_MBITS)) - base;
     const double fa = __hiloint2double(0x3FF00000 | ((hia & ((1 << (20 - MMC_GTAB_MBITS)) - 1)) << MMC_GTAB_MBITS) |
@@ -250,9 +254,13 @@ __device__ __forceinline__ void coul_kernel_tab2(double sa, double sb, const dou
                                            (int)((unsigned)lob >> (32 - MMC_GTAB_MBITS)), lob << MMC_GTAB_MBITS);
     const double ta = fma(2.0, fa, -3.0), tb = fma(2.0, fb, -3.0);
     const double* ca = tab + ia; const double* cb = tab + ib;
-    double pa = ca[MMC_GTAB_DEG * MMC_GTAB_MAXSEG], pb = cb[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+    double pa = 0.0, pb = 0.0;
+    if (ia < i1) pa = ca[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+    if (ib < i1) pb = cb[MMC_GTAB_DEG * MMC_GTAB_MAXSEG];
+    if (ia < i2) pa = fma(pa, ta, ca[(MMC_GTAB_DEG - 1) * MMC_GTAB_MAXSEG]);
+    if (ib < i2) pb = fma(pb, tb, cb[(MMC_GTAB_DEG - 1) * MMC_GTAB_MAXSEG]);
 #pragma unroll
-    for (int d = MMC_GTAB_DEG - 1; d >= 0; d--) { pa = fma(pa, ta, ca[d * MMC_GTAB_MAXSEG]); pb = fma(pb, tb, cb[d * MMC_GTAB_MAXSEG]); }
+    for (int d = MMC_GTAB_DEG - 2; d >= 0; d--) { pa = fma(pa, ta, ca[d * MMC_GTAB_MAXSEG]); pb = fma(pb, tb, cb[d * MMC_GTAB_MAXSEG]); }
     ga = pa; gb = pb;
 }
 // 1/a: MUFU.RCP64H seed + two Newton steps

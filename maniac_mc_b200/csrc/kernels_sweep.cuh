@@ -279,7 +279,7 @@ __device__ __forceinline__ void stage_terms(const DevConst& dc, const ChainState
 }
 
 // ----------------------------------------------------------------------------------------------
-struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase; };
+struct PairConst { double Lx, Ly, Lz, iLx, iLy, iLz, reach2, alpha, rc2, smin, smax; int gbase, g1, g2; };
 
 // one (moved atom, other atom) pair at one geometry; SHIFT: the other atom was already moved to the periodic
 // image nearest the molecule, so the plain difference IS the minimum image for every pair within reach
@@ -299,7 +299,7 @@ __device__ __forceinline__ void pair_one(const DevConst& dc, const PairConst& pc
         work += 0x10000u;
         if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
             double g;
-            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase);
+            if (r2 >= pc.smin && r2 < pc.smax) g = coul_kernel_tab(r2, s_gtab, pc.gbase, pc.g1, pc.g2);
             else g = coul_kernel_slow(r2, pc.alpha);
             e_c = fma(qq, g, e_c);
         }
@@ -332,10 +332,10 @@ __device__ __forceinline__ void pair_two(const DevConst& dc, const PairConst& pc
     const double so = in_o ? r2o : r2n, sn = in_n ? r2n : r2o;
     if (charged) {  // CoulombEnergy term erfc(alpha r)/r, energy_utils.f90:425-433
         double go, gn;
-        if (fmin(so, sn) >= pc.smin && fmax(so, sn) < pc.smax) coul_kernel_tab2(so, sn, s_gtab, pc.gbase, go, gn);
+        if (fmin(so, sn) >= pc.smin && fmax(so, sn) < pc.smax) coul_kernel_tab2(so, sn, s_gtab, pc.gbase, pc.g1, pc.g2, go, gn);
         else {
-            go = (so >= pc.smin && so < pc.smax) ? coul_kernel_tab(so, s_gtab, pc.gbase) : coul_kernel_slow(so, pc.alpha);
-            gn = (sn >= pc.smin && sn < pc.smax) ? coul_kernel_tab(sn, s_gtab, pc.gbase) : coul_kernel_slow(sn, pc.alpha);
+            go = (so >= pc.smin && so < pc.smax) ? coul_kernel_tab(so, s_gtab, pc.gbase, pc.g1, pc.g2) : coul_kernel_slow(so, pc.alpha);
+            gn = (sn >= pc.smin && sn < pc.smax) ? coul_kernel_tab(sn, s_gtab, pc.gbase, pc.g1, pc.g2) : coul_kernel_slow(sn, pc.alpha);
         }
         if (in_o) acc[1] = fma(qq, go, acc[1]);
         if (in_n) acc[3] = fma(qq, gn, acc[3]);
@@ -487,7 +487,7 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
-    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base};
+    PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base, dc.gtab_deg_start[0], dc.gtab_deg_start[1]};
     const bool cull = dc.reach2 < 1e300;
     CompactQ cq = {0.0, 0.0, 0.0, 0.0, 0, 0};   // compacted sweep (SHIFT): survivors carried between tiles
     int item0 = 0;

@@ -243,7 +243,7 @@ __global__ void k_erfc_test(DevConst dc, const double* x, int n, double* out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double r = x[i] / dc.alpha, s = r * r;
-    const double g = (s >= dc.gtab_smin && s < dc.gtab_smax) ? coul_kernel_tab(s, dc.gtab, dc.gtab_base) : coul_kernel_slow(s, dc.alpha);
+    const double g = (s >= dc.gtab_smin && s < dc.gtab_smax) ? coul_kernel_tab(s, dc.gtab, dc.gtab_base, dc.gtab_deg_start[0], dc.gtab_deg_start[1]) : coul_kernel_slow(s, dc.alpha);
     out[i] = r * g;
 }
 

@@ -203,7 +203,48 @@ static int upload_chain(mmc_handle* h, int c, const int* count, const double* co
 // Coulomb kernel table (common.cuh coul_kernel_tab): g(s) = erfc(alpha sqrt(s))/sqrt(s) on segments
 // [2^e (1 + j/8), 2^e (1 + (j+1)/8)), degree-9 interpolation at Chebyshev nodes solved in long double.
 // Domain: s_min (0.25 A^2, raised if more than MMC_GTAB_MAXSEG segments would be needed) to (xmax/alpha)^2.
-static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out) {
+// Degree-D interpolant of g(s) = erfc(alpha sqrt(s)) / sqrt(s) on segment j of octave e at Chebyshev nodes, solved in long double;
+// returns the largest sampled |p - g| (long double evaluation of both).  coef[0..D].
+static long double fit_coulomb_segment(double alpha, int e, int j, int D, long double* coef) {
+    const int NS = 1 << MMC_GTAB_MBITS;
+    const long double pi = 3.14159265358979323846264338327950288L;
+    const long double s0 = ldexpl(1.0L + (long double)j / NS, e), w = ldexpl(1.0L / NS, e);
+    auto g = [&](long double t) { const long double sv = s0 + (t + 1.0L) * 0.5L * w, rr = sqrtl(sv); return erfcl((long double)alpha * rr) / rr; };
+    long double V[MMC_GTAB_DEG + 1][MMC_GTAB_DEG + 2];
+    for (int r = 0; r <= D; r++) {
+        const long double node = cosl(pi * (2 * r + 1) / (2.0L * (D + 1)));
+        long double p = 1.0L;
+        for (int c = 0; c <= D; c++) { V[r][c] = p; p *= node; }
+        V[r][D + 1] = g(node);
+    }
+    for (int c = 0; c <= D; c++) {  // Gauss-Jordan with partial pivoting
+        int piv = c;
+        for (int r = c + 1; r <= D; r++) if (fabsl(V[r][c]) > fabsl(V[piv][c])) piv = r;
+        for (int k = 0; k <= D + 1; k++) std::swap(V[c][k], V[piv][k]);
+        for (int r = 0; r <= D; r++) if (r != c) {
+            const long double f = V[r][c] / V[c][c];
+            for (int k = c; k <= D + 1; k++) V[r][k] -= f * V[c][k];
+        }
+    }
+    for (int c = 0; c <= D; c++) coef[c] = V[c][D + 1] / V[c][c];
+    long double err = 0.0L;
+    for (int i = 0; i <= 64; i++) {
+        const long double t = -1.0L + i / 32.0L;
+        long double p = coef[D];
+        for (int c = D - 1; c >= 0; c--) p = p * t + coef[c];
+        err = std::max(err, fabsl(p - g(t)));
+    }
+    return err;
+}
+
+// Coulomb kernel table (common.cuh coul_kernel_tab): g(s) on segments [2^e (1 + j/NS), 2^e (1 + (j+1)/NS)), NS = 2^MMC_GTAB_MBITS,
+// degree <= MMC_GTAB_DEG.  Domain: s_min = 1 A^2 (raised if more than MMC_GTAB_MAXSEG segments would be needed) to (xmax/alpha)^2.
+// The sums need ABSOLUTE accuracy (the near pairs' g ~ 0.1 .. 1 rounds at 1e-17 .. 1e-16), and g falls by 17 decades over the
+// domain: far octaves reach that with fewer terms.  deg_start[0] / [1] = first segment from which degree D - 1 / D - 2 keeps the
+// sampled interpolation error below MMC_GTAB_ABS_TOL in EVERY later segment (round 2: for the bench system's alpha the last
+// octave, r = 16 .. 22.6 A with 65 % of the pairs in reach, needs degree 6: two coefficient loads fewer per pair).
+#define MMC_GTAB_ABS_TOL 1.0e-17L
+static void build_coulomb_table(double alpha, double xmax, std::vector<double>& tab, int* base, double* smin_out, double* smax_out, int deg_start[2]) {
     const int D = MMC_GTAB_DEG, M = MMC_GTAB_MBITS, NS = 1 << M;
     const double smax = (xmax / alpha) * (xmax / alpha);
     int e_hi = 0; std::frexp(smax, &e_hi);   // smax in [2^(e_hi-1), 2^e_hi)
@@ -211,29 +252,21 @@ static void build_coulomb_table(double alpha, double xmax, std::vector<double>& 
     while ((e_hi - e_lo) * NS > MMC_GTAB_MAXSEG) e_lo++;
     const int nseg = (e_hi - e_lo) * NS;
     tab.assign((size_t)(D + 1) * MMC_GTAB_MAXSEG, 0.0);
-    const long double pi = 3.14159265358979323846264338327950288L;
-    long double nodes[D + 1];
-    for (int k = 0; k <= D; k++) nodes[k] = cosl(pi * (2 * k + 1) / (2.0L * (D + 1)));
+    long double coef[MMC_GTAB_DEG + 1];
+    // lowest admissible degree per segment, then made monotone from the far end
+    std::vector<int> deg(nseg, D);
+#ifndef MMC_GTAB_FIXED_DEGREE
+    for (int seg = 0; seg < nseg; seg++)
+        for (int dd = D - 2; dd < D; dd++)
+            if (dd >= 1 && fit_coulomb_segment(alpha, e_lo + seg / NS, seg % NS, dd, coef) <= MMC_GTAB_ABS_TOL) { deg[seg] = dd; break; }
+    for (int seg = nseg - 2; seg >= 0; seg--) deg[seg] = std::max(deg[seg], deg[seg + 1]);
+#endif
+    deg_start[0] = deg_start[1] = MMC_GTAB_MAXSEG;
+    for (int seg = nseg - 1; seg >= 0; seg--) { if (deg[seg] <= D - 1) deg_start[0] = seg; if (deg[seg] <= D - 2) deg_start[1] = seg; }
     for (int seg = 0; seg < nseg; seg++) {
-        const int e = e_lo + seg / NS, j = seg % NS;
-        const long double s0 = ldexpl(1.0L + (long double)j / NS, e), w = ldexpl(1.0L / NS, e);
-        long double V[D + 1][D + 2];
-        for (int r = 0; r <= D; r++) {
-            long double p = 1.0L;
-            for (int c = 0; c <= D; c++) { V[r][c] = p; p *= nodes[r]; }
-            const long double sv = s0 + (nodes[r] + 1.0L) * 0.5L * w, rr = sqrtl(sv);
-            V[r][D + 1] = erfcl((long double)alpha * rr) / rr;
-        }
-        for (int c = 0; c <= D; c++) {  // Gauss-Jordan with partial pivoting
-            int piv = c;
-            for (int r = c + 1; r <= D; r++) if (fabsl(V[r][c]) > fabsl(V[piv][c])) piv = r;
-            for (int k = 0; k <= D + 1; k++) std::swap(V[c][k], V[piv][k]);
-            for (int r = 0; r <= D; r++) if (r != c) {
-                const long double f = V[r][c] / V[c][c];
-                for (int k = c; k <= D + 1; k++) V[r][k] -= f * V[c][k];
-            }
-        }
-        for (int c = 0; c <= D; c++) tab[(size_t)c * MMC_GTAB_MAXSEG + seg] = (double)(V[c][D + 1] / V[c][c]);
+        const int dd = seg >= deg_start[1] ? D - 2 : seg >= deg_start[0] ? D - 1 : D;
+        fit_coulomb_segment(alpha, e_lo + seg / NS, seg % NS, dd, coef);
+        for (int c = 0; c <= dd; c++) tab[(size_t)c * MMC_GTAB_MAXSEG + seg] = (double)coef[c];
     }
     const double smin = std::ldexp(1.0, e_lo);
     union { double d; uint64_t u; } cv; cv.d = smin;
@@ -314,7 +347,7 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     dc.sx = px; dc.sy = py; dc.sz = pz; dc.sq = pq; dc.stype = pt; dc.tbox = pb; dc.n_tiles = n_tiles;
     {
         std::vector<double> tab;
-        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax);
+        build_coulomb_table(dc.alpha, 7.0, tab, &dc.gtab_base, &dc.gtab_smin, &dc.gtab_smax, dc.gtab_deg_start);
         CK(dalloc(h, &pe, tab.size())); CK(cudaMemcpy(pe, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
         dc.gtab = pe;
     }
