@@ -252,7 +252,7 @@ def c5_isotherm(rank, world, local_rank, steps=1000, reps=5):
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t[0])
-    threads = gpu.chain_threads() if hasattr(gpu, "chain_threads") else None
+    threads = list(gpu.chain_launch_config())   # (CTA threads, CTAs per chain: > 1 = the cluster-per-chain kernel)
     gpu.close()
     if rank != 0:
         return None
@@ -260,7 +260,7 @@ def c5_isotherm(rank, world, local_rank, steps=1000, reps=5):
     return {"workload": "c5_isotherm: 64 fugacity points x 8 replicas = 512 chains of ZIF-8 + H2O (2208-atom framework, K = 297) in TOTAL, "
                         "dealt round-robin to the ranks", "scaling": "strong", "chains_total": total, "chains_per_gpu": len(ids),
             "steps_per_chain": steps * reps, "value": total * steps * reps / (ms * 1e-3), "unit": "moves/s", "ms": ms,
-            "cta_threads": threads}
+            "launch_config_threads_ctas_per_chain": threads}
 
 
 def strict_mode(gpu_c4, s_c4, local_rank, cpu_moves_per_s_per_core):

@@ -316,6 +316,10 @@ int mmc_dbg_set_tracked(mmc_t* handle, int chain, const double* energies, const 
 /* timing of the last pair / recip sweeps in a batched run is taken by the caller with
  * CUDA events on this stream */
 void* mmc_stream(mmc_t* handle);
+/* launch configuration of the batched kernel chosen for this handle: CTA size and CTAs per chain (1 = one CTA owns a chain;
+ * 2 / 4 / 8 = a thread-block cluster shares it, chosen when chains <= SMs so that few chains still fill the GPU;
+ * environment variable MANIAC_CLUSTER=<0|2|4|8> overrides the choice at mmc_init) */
+int mmc_chain_launch_config(const mmc_t* handle, int* threads, int* cluster);
 /* kernel launches issued by this handle since init (bench.py's gpu_launches) */
 int64_t mmc_launch_count(const mmc_t* handle);
 /* Executed real-space work of the per-move sweeps since mmc_init (all chains): out[0] = minimum-image distances

@@ -17,6 +17,7 @@
 #define RECIP_THREADS 256   // single-point S(k) kernels
 #define TAIL_THREADS 128
 #define SWEEP_THREADS 256   // strict-mode sweep: CTAs of this size, dc.sweep_parts per chain
+#define CLUSTER_THREADS 512 // k_chain_run_cl: CTA size of the cluster-per-chain kernel (few chains)
 #define TILE 32             // framework atoms per tile (one per lane)
 #define CULL_CHUNK 4096     // tiles culled per pass (shared-memory list)
 

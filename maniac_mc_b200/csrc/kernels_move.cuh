@@ -138,7 +138,9 @@ __global__ void k_set_trial(DevConst dc, ChainState cs, HostTrial ht) {
 
 // batched mode: one step of MonteCarloLoop's selection logic (monte_carlo.f90:44-75) and the
 // proposal geometry, draw order as in SURVEY 3.8.  Single thread per chain.
-__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c, Trial& t, const double* pre = nullptr) {
+// lead: this caller performs the proposal's side effects (trial counters, the geometry of a creation / swap written into its
+// slot).  The CTAs of a cluster that share one chain (k_chain_run_cl) all make the same proposal; only rank 0 leads.
+__device__ inline void propose_move(const DevConst& dc, const ChainState& cs, const RngSrc& rs, int c, Trial& t, const double* pre = nullptr, bool lead = true) {
     t.kind = 0; t.error = 0; t.accepted = 0;
     for (int i = 0; i < MMC_NE; i++) { t.old_e[i] = 0.0; t.new_e[i] = 0.0; }
     Rng rng{&rs, cs, c, 0, pre};
@@ -155,7 +157,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
     double com_new[3]; double off_new[MMC_MAX_MOL_ATOMS][3];
     if (draw <= dc.p_translation) {
         if (m >= 0) {  // Translation translation.f90:36-112
-            ctr.trial_translations++;
+            if (lead) ctr.trial_translations++;
             const double* com = g_com(dc, cs, c, r, m);
             const double step = cs.tstep[c];
             double u[3]; for (int d = 0; d < 3; d++) u[d] = rng.next() - 0.5;
@@ -172,11 +174,11 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                 com_new[d] = dc.lo[d] + f_modulo(x - dc.lo[d], dc.L[d], dc.invL[d]);  // ApplyPBC
             }
             for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_new[a][d] = cs.goff[g_atom(dc, c, r, m, a) * 3 + d];
-            build_trial(dc, cs, c, t, MMC_TRANSLATION, r, m, com_new, off_new);
+            build_trial(dc, cs, c, t, MMC_TRANSLATION, r, m, com_new, off_new, -1, lead);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation) {
         if (nat != 1 && m >= 0) {  // Rotation rotation.f90:34-75
-            ctr.trial_rotations++;
+            if (lead) ctr.trial_rotations++;
             const double theta = (rng.next() - 0.5) * cs.rstep[c];  // ChooseRotationAngle
             const int axis = (int)(rng.next() * 3.0) + 1;
             double off_old[MMC_MAX_MOL_ATOMS][3];
@@ -184,7 +186,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             rotate_offsets(axis, theta, nat, off_old, off_new);
             const double* com = g_com(dc, cs, c, r, m);
             for (int d = 0; d < 3; d++) com_new[d] = com[d];
-            build_trial(dc, cs, c, t, MMC_ROTATION, r, m, com_new, off_new);
+            build_trial(dc, cs, c, t, MMC_ROTATION, r, m, com_new, off_new, -1, lead);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation + dc.p_swap) {
         // swap (identity exchange): remove (r, m), insert a molecule of another active type at the same
@@ -198,7 +200,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             const int m2 = cs.count[c * MMC_MAX_RES + r2], nat2 = dc.natoms[r2];
             if (m2 >= dc.cap[r2]) { t.error = 1; }
             else {
-                ctr.trial_swaps++;
+                if (lead) ctr.trial_swaps++;
                 const double* com = g_com(dc, cs, c, r, m);
                 for (int d = 0; d < 3; d++) com_new[d] = com[d];
                 double tmpl[MMC_MAX_MOL_ATOMS][3];
@@ -208,7 +210,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                     const int axis = (int)(rng.next() * 3.0) + 1;
                     rotate_offsets(axis, theta, nat2, tmpl, off_new);
                 } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
-                build_trial(dc, cs, c, t, MMC_SWAP, r, m, com_new, off_new, r2);
+                build_trial(dc, cs, c, t, MMC_SWAP, r, m, com_new, off_new, r2, lead);
             }
         }
     } else {
@@ -216,7 +218,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             m = cnt;
             if (m >= dc.cap[r]) { t.error = 1; }  // CheckMoleculeIndex -> AbortRun in the reference
             else {
-                ctr.trial_creations++;
+                if (lead) ctr.trial_creations++;
                 if (dc.tri) {   // bounds(:,1) + matmul(matrix, u) with the cell vectors as columns (create_molecule.f90:180-182)
                     double uu[3]; for (int d = 0; d < 3; d++) uu[d] = rng.next();
                     com_new[0] = dc.lo[0] + (dc.L[0] * uu[0] + dc.tilt[0] * uu[1] + dc.tilt[1] * uu[2]);
@@ -238,12 +240,12 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                         rotate_offsets(axis, theta, nat, tmpl, off_new);
                     } else for (int d = 0; d < 3; d++) off_new[0][d] = tmpl[0][d];
                 }
-                build_trial(dc, cs, c, t, MMC_CREATION, r, m, com_new, off_new);
+                build_trial(dc, cs, c, t, MMC_CREATION, r, m, com_new, off_new, -1, lead);
                 t.rsv = rsv;
             }
         } else if (cnt != 0) {  // DeleteMolecule delete_molecule.f90:41-199
-            ctr.trial_deletions++;
-            build_trial(dc, cs, c, t, MMC_DELETION, r, m, nullptr, nullptr);
+            if (lead) ctr.trial_deletions++;
+            build_trial(dc, cs, c, t, MMC_DELETION, r, m, nullptr, nullptr, -1, lead);
         }
     }
     t.draw = rng.draw;

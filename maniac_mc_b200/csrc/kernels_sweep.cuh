@@ -764,7 +764,7 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
     const int r0 = min(nrows, part * rpp), r1 = min(nrows, r0 + rpp);
     if (r0 >= r1) return;
     const int warp = threadIdx.x >> 5;
-    if (n_parts > 1) {   // few rows per CTA: spread (group, kz block) units over the warps
+    if (n_parts > 1 && (r1 - r0) < 8 * (NT / 32)) {   // fewer than two 4-row groups per warp (strict mode, k-sharded sweeps): spread (group, kz block) units over the warps
         if (nterm <= 4) recip_groups<1, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
         else if (nterm <= 8) recip_groups<2, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);
         else recip_groups<0, TRI, true>(dc, s, A, An, r0, r1, warp, NT / 32, nterm, acc);

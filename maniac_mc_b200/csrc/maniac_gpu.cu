@@ -41,6 +41,8 @@ struct mmc_handle {
     size_t sk_smem = 0;
     size_t sweep_smem = 0, chain_smem = 0;  // dynamic shared memory of k_sweep / k_chain_run
     int chain_threads = 256;                // CTA size of k_chain_run (256 x4, 512 x2 or 1024 x1 per SM)
+    int cluster_p = 0;                      // > 1: few chains -> k_chain_run_cl, a cluster of cluster_p CTAs of CLUSTER_THREADS per chain
+    size_t cluster_smem = 0;
     int n_sm = 148;
     std::vector<void*> allocs;
     std::vector<int> h_res_is_fw;          // per residue: 1 = inactive (framework)
@@ -431,6 +433,18 @@ static int build_sweep_layout(mmc_handle* h, const mmc_desc* d) {
     CK(cudaFuncSetAttribute(k_chain_run<256, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     CK(cudaFuncSetAttribute(k_chain_run<512, 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
     CK(cudaFuncSetAttribute(k_chain_run<1024, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    {   // Few chains: a thread-block cluster per chain (k_chain_run_cl).  Measured on B200 (tools/few_chains.py,
+        // profiles/r2n_few_chains.log): it wins only while chains <= SMs / 2 (64 chains: +9 % at P = 4; 32 chains: +26 % at P = 8;
+        // c4_large_k at 64 chains: +31 %), with P = the largest of 8, 4, 2 that keeps P x chains CTAs resident (two 512-thread
+        // CTAs per SM); at 128 chains and above one CTA per chain is faster.  MANIAC_CLUSTER=<P> overrides (0 = off).
+        int P = 0;
+        if (2 * dc.n_chains <= h->n_sm) for (int q = 8; q >= 2; q >>= 1) if ((long long)q * dc.n_chains <= 2LL * h->n_sm) { P = q; break; }
+        if (const char* e = getenv("MANIAC_CLUSTER")) { P = atoi(e); if (P != 2 && P != 4 && P != 8) P = 0; }
+        h->cluster_p = P > 1 ? P : 0;
+        h->cluster_smem = sweep_smem_layout(dc.max_nat, dc.ntypes, dc.kmax, CLUSTER_THREADS, off);
+        CK(cudaFuncSetAttribute(k_chain_run_cl<CLUSTER_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+        CK(cudaFuncSetAttribute(k_chain_run_cl<CLUSTER_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap));
+    }
     CK(dalloc(h, &h->cs.part, (size_t)dc.n_chains * dc.sweep_parts * 6));
     return 0;
 }
@@ -1153,9 +1167,25 @@ extern "C" int mmc_trial_commit(mmc_t* h, int c, int accept) {
 #define GRAPH_CHUNK 128
 #endif
 
-// one launch of the chain-per-CTA kernel: every chain advances n steps
-static void launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases) {
+// one launch of the chain kernel: every chain advances n steps.  philox: the random numbers are device Philox draws (not a
+// recorded tape): with few chains the cluster-per-chain kernel is used then
+static int launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases, bool philox = true) {
     const int C = h->dc.n_chains;
+    if (h->cluster_p > 1 && philox) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(C * h->cluster_p)); cfg.blockDim = dim3(CLUSTER_THREADS);
+        cfg.dynamicSmemBytes = h->cluster_smem; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)h->cluster_p; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        const BatchCtl* ctl = h->d_ctl;
+        cudaError_t e = h->dc.tri ? cudaLaunchKernelEx(&cfg, k_chain_run_cl<CLUSTER_THREADS, true>, h->dc, h->cs, ctl, 0, n, phases)
+                                  : cudaLaunchKernelEx(&cfg, k_chain_run_cl<CLUSTER_THREADS, false>, h->dc, h->cs, ctl, 0, n, phases);
+        h->launches++;
+        if (e != cudaSuccess) return fail("cluster launch of k_chain_run_cl (P = %d) failed: %s", h->cluster_p, cudaGetErrorString(e));
+        return 0;
+    }
     if (h->dc.tri) {   // the tilted-cell build of the same kernel
         if (h->chain_threads == 256) k_chain_run<256, 4, true><<<C, 256, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
         else if (h->chain_threads == 512) k_chain_run<512, 2, true><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
@@ -1165,11 +1195,13 @@ static void launch_chain_run(mmc_handle* h, cudaStream_t st, int n, int phases) 
     else if (h->chain_threads == 512) k_chain_run<512, 2, false><<<C, 512, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
     else k_chain_run<1024, 1, false><<<C, 1024, h->chain_smem, st>>>(h->dc, h->cs, h->d_ctl, 0, n, phases);
     h->launches++;
+    return 0;
 }
-static void enqueue_steps(mmc_handle* h, cudaStream_t st, int n) {
-    launch_chain_run(h, st, n, 3);
+static int enqueue_steps(mmc_handle* h, cudaStream_t st, int n, bool philox = true) {
+    if (launch_chain_run(h, st, n, 3, philox)) return 1;
     k_advance<<<1, 1, 0, st>>>(h->d_ctl, n);
     h->launches++;
+    return 0;
 }
 
 static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const double* d_tape, int64_t tape_stride,
@@ -1184,13 +1216,18 @@ static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const do
     CK(cudaMemsetAsync(h->cs.tape_pos, 0, h->dc.n_chains * sizeof(long long), st));
     // cs.error_flag is NOT cleared here: it stays set until a host entry point reports it (report_error_flag)
     int64_t done = 0;
-    if (n_steps >= GRAPH_CHUNK) {
+    // the cached graph holds the kernel chosen for Philox runs; a tape replay on a cluster handle runs the one-CTA kernel directly
+    const bool philox = d_tape == nullptr, use_graph = philox || h->cluster_p <= 1;
+    if (!use_graph)
+        for (; n_steps - done >= GRAPH_CHUNK; done += GRAPH_CHUNK) if (enqueue_steps(h, st, GRAPH_CHUNK, false)) return 1;
+    if (use_graph && n_steps >= GRAPH_CHUNK) {
         if (!h->graph) {
             cudaGraph_t g;
             const int64_t l0 = h->launches;
             CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            enqueue_steps(h, st, GRAPH_CHUNK);
+            const int cap_rc = enqueue_steps(h, st, GRAPH_CHUNK);
             CK(cudaStreamEndCapture(st, &g));
+            if (cap_rc) return 1;
             h->launches = l0;
             CK(cudaGraphInstantiate(&h->graph, g, 0));
             CK(cudaGraphDestroy(g));
@@ -1202,7 +1239,7 @@ static int enqueue_batch(mmc_handle* h, int64_t n_steps, uint64_t seed, const do
             done += GRAPH_CHUNK;
         }
     }
-    if (n_steps - done > 0) enqueue_steps(h, st, (int)(n_steps - done));
+    if (n_steps - done > 0 && enqueue_steps(h, st, (int)(n_steps - done), philox)) return 1;
     CK(cudaGetLastError());
     h->steps_done += (unsigned long long)n_steps;
     h->pending_chain = -1;
@@ -1243,7 +1280,7 @@ extern "C" int mmc_profile_kernels(mmc_t* h, int n_steps, uint64_t seed, double 
     for (int k = 0; k < 3; k++) {
         if (k == 2) CK(cudaMemcpyAsync(h->cs.counters, d_save, h->dc.n_chains * sizeof(mmc_counters), cudaMemcpyDeviceToDevice, st));
         CK(cudaEventRecord(ev[k], st));
-        launch_chain_run(h, st, n_steps, phases[k]);
+        if (launch_chain_run(h, st, n_steps, phases[k])) return 1;
     }
     CK(cudaEventRecord(ev[3], st));
     CK(cudaGetLastError());
@@ -1524,6 +1561,12 @@ extern "C" int mmc_erfc_noalloc(mmc_t* h, const double* x, int n, double* out) {
 }
 extern "C" void* mmc_stream(mmc_t* h) { return h ? (void*)h->stream : nullptr; }
 extern "C" int64_t mmc_launch_count(const mmc_t* h) { return h ? h->launches : -1; }
+extern "C" int mmc_chain_launch_config(const mmc_t* h, int* threads, int* cluster) {
+    if (!h) return fail("null handle");
+    if (threads) *threads = h->cluster_p > 1 ? CLUSTER_THREADS : h->chain_threads;
+    if (cluster) *cluster = h->cluster_p > 1 ? h->cluster_p : 1;
+    return 0;
+}
 extern "C" int mmc_pair_work(mmc_t* h, int64_t out[2]) {
     if (!h || !out) return fail("mmc_pair_work: null argument");
     CK(cudaSetDevice(h->device));

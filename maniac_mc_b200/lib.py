@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop", "mmc_erfc_noalloc",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop", "mmc_erfc_noalloc", "mmc_chain_launch_config",
 ]
 
 _lib = None
@@ -101,6 +101,7 @@ def load():
     L.mmc_dbg_phase_cycles.argtypes = [vp, C.POINTER(C.c_int64)]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
+    L.mmc_chain_launch_config.argtypes = [vp, ip, ip]
     L.mmc_pair_work.argtypes = [vp, C.POINTER(C.c_int64)]
     L.mmc_shard_step_begin.argtypes = [vp, C.c_uint64, vp]
     L.mmc_shard_step_end.argtypes = [vp, vp, vp]
@@ -390,6 +391,15 @@ class ManiacGPU:
 
     def stream(self):
         return load().mmc_stream(self.h)
+
+    def chain_launch_config(self):
+        """(CTA threads, CTAs per chain) of the batched kernel; CTAs per chain > 1 = the cluster-per-chain kernel"""
+        a, b = C.c_int(), C.c_int()
+        _ck(load().mmc_chain_launch_config(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def chain_threads(self):
+        return self.chain_launch_config()
 
     def launch_count(self):
         return load().mmc_launch_count(self.h)

@@ -202,6 +202,56 @@ def test_batched_philox_matches_oracle_and_graph_path():
     g.close()
 
 
+@pytest.mark.parametrize("which,P", [("zif8_h2o", 2), ("zif8_h2o", 4), ("zif8_h2o", 8), ("zif8_ch4o_h2o", 4), ("tilted_framework", 4), ("water_box", 8)])
+def test_cluster_per_chain_kernel(which, P, monkeypatch):
+    """k_chain_run_cl: a thread-block cluster of P CTAs shares one chain (few chains must still fill the GPU).  Same Philox
+    streams through (a) the cluster kernel, (b) the one-CTA kernel (MANIAC_CLUSTER=0) and (c) the oracle: identical accept
+    sequences, records within 1e-12 of the one-CTA kernel (only the association of the P partial sums differs) and 1e-10 of
+    the oracle; 300 steps = 2 graph replays of 128 + 44 direct; then a tape replay on the SAME cluster handle, which must
+    take the one-CTA kernel and still continue the chain correctly."""
+    if which == "zif8_h2o":
+        s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    elif which == "zif8_ch4o_h2o":
+        s = load_system("zif8_ch4o_h2o", init_sk=1, deletion_mode=1); s.p_translation, s.p_rotation, s.p_swap = 0.25, 0.25, 0.3
+    elif which == "water_box":
+        s = water_box_500(); s.init_sk, s.deletion_mode = 1, 1
+    else:
+        s = tilted_framework(n_fw=3000, box=48.0, tilt=(7.0, -5.0, 9.0))
+    n, seed, C = 300, 4242, 3
+    monkeypatch.setenv("MANIAC_CLUSTER", str(P))
+    g = ManiacGPU(s, n_chains=C)
+    assert g.chain_launch_config() == (512, P)
+    monkeypatch.setenv("MANIAC_CLUSTER", "0")
+    g1 = ManiacGPU(s, n_chains=C)
+    assert g1.chain_launch_config()[1] == 1
+    g.system_energy_all(); g1.system_energy_all()
+    rc, r1 = g.run_batch(n, seed=seed, records=True), g1.run_batch(n, seed=seed, records=True)
+    ctr_c, ctr_1 = list(g.counters), list(g1.counters)
+    oracles = []
+    for c in range(C):
+        compare_records(rc[c], r1[c], tol=1e-12)
+        assert ctr_c[c] == ctr_1[c]
+        o = orc.Oracle(s); o.system_energy()
+        compare_records(rc[c], o.run(n, seed=seed, chain=c, step0=0))
+        cnt, com, off, e = g.sync_to_host(c); c2, com2, off2 = o.state()
+        assert np.array_equal(cnt, c2)
+        np.testing.assert_allclose(com, com2, atol=1e-11); np.testing.assert_allclose(off, off2, atol=1e-12)
+        assert rel_err(e, o.energy()) < TOL
+        np.testing.assert_allclose(g.sk(c), o.sk(), atol=1e-9)
+        oracles.append(o)
+    # tape replay continues every chain on the cluster handle (one-CTA kernel): 140 steps = 1 chunk of 128 + 12
+    tape = np.random.default_rng(3).random((C, 13 * 140))
+    rt = g.run_batch(140, tape=tape, records=True)
+    for c in range(C):
+        compare_records(rt[c], oracles[c].run(140, tape=tape[c]))
+        assert g.tape_used(c) == oracles[c].tape_used
+    # ... and a Philox batch after it goes back to the cluster kernel with the step counter carried on
+    r3 = g.run_batch(60, seed=seed, records=True)
+    compare_records(r3[1], oracles[1].run(60, seed=seed, chain=1, step0=n + 140))
+    assert (rc["accepted"] == 1).sum() > n // 4
+    g.close(); g1.close()
+
+
 def test_per_chain_parameters():
     """Isotherm sweep: each chain has its own fugacity/temperature."""
     s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
