@@ -42,6 +42,7 @@ struct DevConst {
     int n_k_tiles;                 // ceil(nk / RECIP_THREADS)
     int nk, kmax[3], kstride;      // kstride = max(kmax)+1 : row length of a 1-D phase table
     int deletion_mode, use_table;
+    int fw_cache;                  // 1: cache the framework part of every guest molecule's pair energy (ChainState.fw_pair)
     double q[MMC_MAX_RES][MMC_MAX_MOL_ATOMS];  // active residues only
     int type[MMC_MAX_RES][MMC_MAX_MOL_ATOMS];  // 0-based atom types
     double self_e[MMC_MAX_RES];                // ComputeEwaldSelfInteractionSingleMol per residue (K)
@@ -96,6 +97,11 @@ struct Trial {
     int excl;              // 1: exclude slot (res, mol) from the sweep
     int accepted, error, draw;
     int rsv;               // creation with a reservoir: pool slot the geometry was copied from
+    // Framework-energy cache (ChainState.fw_pair): fw_old = cached {LJ, Coulomb (reduced units)} of the selected molecule with the
+    // framework at its current geometry, fw_old_ok = it was valid when the trial was built; after the sweep fw_new / fw_old hold
+    // the sums of THIS trial when fw_new_ok / fw_old_fresh say so (one-CTA batched kernel only), for commit_trial to store
+    int fw_old_ok, fw_new_ok, fw_old_fresh;
+    double fw_old[2], fw_new[2];
     double prob;
     double q[MMC_MAX_MOL_ATOMS];          // OLD atom set (the selected molecule)
     int type[MMC_MAX_MOL_ATOMS];
@@ -130,6 +136,11 @@ struct ChainState {
     unsigned int* chain_id;  // [C] Philox stream of each chain (default: the chain index); global ids make a sweep independent of how chains are dealt to GPUs
     unsigned long long* pair_count;  // [10] executed real-space work since mmc_init: distances formed, pairs inside reach; [2..9] = phase cycles of -DMMC_PHASE_TIMING builds
     int* error_flag;      // [1] MMC_ERRF_* bits, sticky until read by the host
+    // [C][g_mols] framework part {LJ, Coulomb (reduced units)} of the pair energy of every guest molecule at its CURRENT geometry;
+    // NaN = unknown.  The framework never moves, so the old-geometry framework sum of a translation / rotation / deletion is the
+    // value summed when the molecule last moved: stored on accept, reused instead of re-summed (the reference re-sums it,
+    // ComputeOldEnergy monte_carlo_utils.f90:347-396 -> energy_utils.f90:374-442).  Guest-guest terms are always re-summed.
+    double2* fw_pair;
 };
 
 struct RngSrc {
@@ -177,15 +188,21 @@ __device__ __forceinline__ double warp_sum(double v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
     return v;
 }
-// deterministic block sum of NV values per thread; result valid in thread 0
+// deterministic block sum of NV values per thread, in two halves so that a caller can park one set of partial sums (rows
+// row0 .. row0+NV-1 of smem[rows][NT/32]) and free its registers before it accumulates the next set
 template <int NV, int NT>
-__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * NT/32 */) {
+__device__ __forceinline__ void block_sum_park(const double (&v)[NV], double* smem, int row0) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll
     for (int i = 0; i < NV; i++) {
-        v[i] = warp_sum(v[i]);
-        if (lane == 0) smem[i * (NT / 32) + w] = v[i];
+        const double x = warp_sum(v[i]);
+        if (lane == 0) smem[(row0 + i) * (NT / 32) + w] = x;
     }
+}
+// sums rows 0..NV-1 over the warps; result valid in thread 0.  Barrier before and after
+template <int NV, int NT>
+__device__ __forceinline__ void block_sum_gather(double (&v)[NV], const double* smem) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     __syncthreads();
     if (w == 0) {
 #pragma unroll
@@ -195,6 +212,12 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * 
         }
     }
     __syncthreads();
+}
+// result valid in thread 0
+template <int NV, int NT>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* NV * NT/32 */) {
+    block_sum_park<NV, NT>(v, smem, 0);
+    block_sum_gather<NV, NT>(v, smem);
 }
 
 // ---- real-space Coulomb kernel g(s) = erfc(alpha sqrt(s)) / sqrt(s), s = r^2 ----------------------------

@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         }
         __syncthreads();
         MMC_TSTAMP(0);
-        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, 0, 1, phases);
+        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, 0, 1, phases, s.trial);
         if (threadIdx.x == 0) {
             Trial& t = *s.trial;   // shared memory: the single-thread sections no longer round-trip ~2 kB through global memory
             const int kind = t.kind;

@@ -55,6 +55,11 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
     if (kind != MMC_SWAP) r2 = r;
     const int nat2 = dc.natoms[r2];
     t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.res2 = r2; t.nat2 = nat2; t.accepted = 0; t.prob = 0.0; t.rsv = -1;
+    t.fw_new_ok = 0; t.fw_old_fresh = 0;
+    // issued first, consumed last: the stores to `t` below do not have to wait for it
+    double2 fwv = make_double2(__longlong_as_double(-1LL), 0.0);
+    if (dc.fw_cache && (kind == MMC_TRANSLATION || kind == MMC_ROTATION || kind == MMC_DELETION))
+        fwv = cs.fw_pair[(size_t)c * dc.g_mols + dc.g_mol_base[r] + m];
     for (int a = 0; a < nat; a++) { t.q[a] = dc.q[r][a]; t.type[a] = dc.type[r][a]; }
     for (int a = 0; a < nat2; a++) { t.q2[a] = dc.q[r2][a]; t.type2[a] = dc.type[r2][a]; }
     const int cnt = cs.count[c * MMC_MAX_RES + r];
@@ -125,6 +130,8 @@ __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int
             }
             break;
     }
+    t.fw_old[0] = fwv.x; t.fw_old[1] = fwv.y;
+    t.fw_old_ok = !(isnan(fwv.x) || isnan(fwv.y));
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -315,7 +322,14 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
 __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, int accept) {
     if (t.kind <= 0) return;
     t.accepted = accept;
-    if (!accept) { t.kind = -t.kind; return; }  // negative kind = finished trial (cannot be committed twice)
+    const double2 nan2 = make_double2(__longlong_as_double(-1LL), __longlong_as_double(-1LL));
+    double2* fwc = cs.fw_pair + (size_t)c * dc.g_mols;
+    if (!accept) {
+        // a rejected move leaves the geometry: remember the old geometry's framework sums if this trial had to form them
+        if (dc.fw_cache && t.fw_old_fresh && t.kind != MMC_CREATION && t.kind != MMC_SWAP)
+            fwc[dc.g_mol_base[t.res] + t.mol] = make_double2(t.fw_old[0], t.fw_old[1]);
+        t.kind = -t.kind; return;  // negative kind = finished trial (cannot be committed twice)
+    }
     double* E = cs.energy + c * MMC_NE;
     const double* o = t.old_e; const double* n = t.new_e;
     mmc_counters& ctr = cs.counters[c];
@@ -327,6 +341,7 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
         E[MMC_E_COUL] = E[MMC_E_COUL] + n[1] - o[1];
         E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
         if (t.kind == MMC_TRANSLATION) ctr.translations++; else ctr.rotations++;
+        if (dc.fw_cache) fwc[dc.g_mol_base[r] + m] = t.fw_new_ok ? make_double2(t.fw_new[0], t.fw_new[1]) : nan2;   // the new geometry's framework sums
         double* com = g_com(dc, cs, c, r, m);
         for (int d = 0; d < 3; d++) com[d] = t.com_new[d];
         for (int a = 0; a < nat; a++) {
@@ -343,6 +358,7 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
         E[MMC_E_TOTAL] = E[MMC_E_TOTAL] + n[5] - o[5];
         if (t.kind == MMC_CREATION) {
             ctr.creations++; cnt = cnt + 1;  // geometry already in the slot
+            if (dc.fw_cache) fwc[dc.g_mol_base[r] + m] = t.fw_new_ok ? make_double2(t.fw_new[0], t.fw_new[1]) : nan2;
             int& nr = cs.rcount[c * MMC_MAX_RES + r];
             if (dc.has_reservoir && nr > 0 && t.rsv >= 0) {  // (strict mode: the host owns the pool, rsv < 0)  AcceptCreationMove create_molecule.f90:118-130: pool slot <- last pool slot
                 double* ro = cs.roff + ((size_t)c * dc.r_atoms + dc.r_atom_base[r]) * 3;
@@ -350,7 +366,10 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
                 nr = nr - 1;
             }
         } else {
-            if (t.kind == MMC_SWAP) { ctr.swaps++; cs.count[c * MMC_MAX_RES + t.res2] += 1; }  // inserted geometry already in its slot
+            if (t.kind == MMC_SWAP) {   // inserted geometry already in its slot
+                if (dc.fw_cache) fwc[dc.g_mol_base[t.res2] + cs.count[c * MMC_MAX_RES + t.res2]] = nan2;
+                ctr.swaps++; cs.count[c * MMC_MAX_RES + t.res2] += 1;
+            }
             else ctr.deletions++;
             const int last = cnt - 1;  // RemoveMolecule delete_molecule.f90:99-118: slot[m] <- slot[last]
             if (t.kind == MMC_DELETION && dc.has_reservoir) {
@@ -364,6 +383,7 @@ __device__ inline void commit_trial(const DevConst& dc, const ChainState& cs, in
                 }
             }
             if (m != last) {
+                if (dc.fw_cache) fwc[dc.g_mol_base[r] + m] = fwc[dc.g_mol_base[r] + last];   // the cache entry moves with the molecule
                 double* com = g_com(dc, cs, c, r, m); const double* cl = g_com(dc, cs, c, r, last);
                 for (int d = 0; d < 3; d++) com[d] = cl[d];
                 for (int a = 0; a < nat; a++) {

@@ -33,6 +33,11 @@ struct MolS {
     double q[MMC_MAX_MOL_ATOMS];
     double cen[2][4];   // bounding sphere {x, y, z, radius + reach} of the old / new geometry
     double cc[4];       // common sphere of the geometries swept: {x, y, z, (radius + reach)^2}
+    double ccf[4];      // the same for the FRAMEWORK sweep (new geometry only when the old one's framework energy is cached)
+    double fw_old[2];   // framework part {LJ, Coulomb (reduced)} of the old geometry: from the cache, or summed in this trial
+    int shift_okf;      // shift_ok of the sphere ccf
+    int fo;             // framework sweep evaluates the old geometry (do_old and not cached)
+    int fw_cached;      // fw_old came from the cache
     int shift_ok;       // reach + radius < L/2 on every axis: one periodic shift per other atom is exact
     int type[MMC_MAX_MOL_ATOMS];
     int nat, kind, do_old, do_new, excl, res, mol, nterm, nlist, cur;
@@ -63,7 +68,7 @@ struct SweepCtx {
     uint32_t* mask;  // [CULL_CHUNK / 32]
     int* prefix;     // [CULL_CHUNK / 32]
     uint16_t* list;  // [CULL_CHUNK]
-    double* red;     // [6 * warps]
+    double* red;     // [8 * warps]
     MolS* mol;
     Trial* trial;         // the pending trial of this CTA's chain (batched kernel, fused strict-mode kernel)
     unsigned char* cscr;  // [warps][32] lane ids exchanged by compact_push
@@ -89,7 +94,7 @@ __host__ __device__ inline size_t sweep_smem_layout(int max_nat, int ntypes, con
 #else
     off[4] = o; o += (size_t)nz * zs * sizeof(double2);
 #endif
-    off[5] = o; o += (size_t)6 * (threads / 32) * sizeof(double);
+    off[5] = o; o += (size_t)8 * (threads / 32) * sizeof(double);
     off[6] = o; o += (sizeof(MolS) + 15) / 16 * 16;
     off[7] = o; o += (CULL_CHUNK / 32) * sizeof(uint32_t) * 2;
     off[8] = o; o += CULL_CHUNK * sizeof(uint16_t);
@@ -137,7 +142,7 @@ __device__ __forceinline__ void sweep_load_tables(const DevConst& dc, const Swee
 //   pass 0: both sets in one sweep (every move but the swap)
 //   pass 1: swap, removed molecule only (old geometry)      pass 2: swap, inserted molecule only (new geometry)
 // All threads; ends with a barrier.
-__device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int pass) {
+__device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int pass, bool use_cache = false) {
     MolS& m = *s.mol;
     const int tid = threadIdx.x;
     const bool use_new_set = pass == 2;
@@ -148,6 +153,9 @@ __device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainSt
     if (tid == 0) {
         m.nat = nat; m.kind = t.kind; m.do_old = uo; m.do_new = un; m.excl = t.excl; m.res = t.res; m.mol = t.mol;
         m.cur = cs.cur[c];
+        const bool cached = use_cache && pass == 0 && uo && t.fw_old_ok;
+        m.fw_cached = cached; m.fo = uo && !cached;
+        m.fw_old[0] = cached ? t.fw_old[0] : 0.0; m.fw_old[1] = cached ? t.fw_old[1] : 0.0;
     }
     if (t.kind <= 0) { __syncthreads(); return; }
     if (tid < nat) {
@@ -166,21 +174,24 @@ __device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainSt
         }
         m.cen[tid][0] = cx; m.cen[tid][1] = cy; m.cen[tid][2] = cz; m.cen[tid][3] = sqrt(r2) * (1.0 + 1e-12) + dc.reach;
     }
-    if (tid == 32) {  // common sphere of the swept geometries, and whether the single-shift path is exact
+    if (tid == 32 || tid == 64) {  // common sphere of the swept geometries (32: all atoms; 64, another warp: the framework sweep,
+        // which skips a cached old geometry), and whether the single-shift path is exact
+        const bool uof = tid == 32 ? uo : (uo && !(use_cache && pass == 0 && t.fw_old_ok));
         double cx = 0, cy = 0, cz = 0; int n = 0;
         for (int a = 0; a < nat; a++) {
-            if (uo) { cx += t.p_old[a][0]; cy += t.p_old[a][1]; cz += t.p_old[a][2]; n++; }
+            if (uof) { cx += t.p_old[a][0]; cy += t.p_old[a][1]; cz += t.p_old[a][2]; n++; }
             if (un) { cx += t.p_new[a][0]; cy += t.p_new[a][1]; cz += t.p_new[a][2]; n++; }
         }
         if (n) { cx /= n; cy /= n; cz /= n; }
         double r2 = 0;
         for (int a = 0; a < nat; a++) {
-            if (uo) { const double dx = t.p_old[a][0] - cx, dy = t.p_old[a][1] - cy, dz = t.p_old[a][2] - cz; r2 = fmax(r2, dx * dx + dy * dy + dz * dz); }
+            if (uof) { const double dx = t.p_old[a][0] - cx, dy = t.p_old[a][1] - cy, dz = t.p_old[a][2] - cz; r2 = fmax(r2, dx * dx + dy * dy + dz * dz); }
             if (un) { const double dx = t.p_new[a][0] - cx, dy = t.p_new[a][1] - cy, dz = t.p_new[a][2] - cz; r2 = fmax(r2, dx * dx + dy * dy + dz * dz); }
         }
         const double R = sqrt(r2) * (1.0 + 1e-12) + 1e-9 + dc.reach;
-        m.cc[0] = cx; m.cc[1] = cy; m.cc[2] = cz; m.cc[3] = R * R;
-        m.shift_ok = R < 0.4999 * fmin(dc.L[0], fmin(dc.L[1], dc.L[2]));
+        double* cc = tid == 32 ? m.cc : m.ccf;
+        cc[0] = cx; cc[1] = cy; cc[2] = cz; cc[3] = R * R;
+        (tid == 32 ? m.shift_ok : m.shift_okf) = R < 0.4999 * fmin(dc.L[0], fmin(dc.L[1], dc.L[2]));
     }
     for (int i = tid; i < nat * dc.ntypes; i += blockDim.x) {
         const int a = i / dc.ntypes, tj = i % dc.ntypes;
@@ -356,29 +367,29 @@ __device__ __forceinline__ void pair_two(const DevConst& dc, const PairConst& pc
 // SHIFT path, step 1: move the other atom to the periodic image nearest the molecule's centre (exact for every pair within
 // reach, shift_ok) and test it against the molecule's sphere.  Returns false when it is beyond reach of every moved atom.
 template <bool TRI>
-__device__ __forceinline__ bool pair_shift(const DevConst& dc, const PairConst& pc, const MolS& m, double& xj, double& yj, double& zj) {
-    double dx = xj - m.cc[0], dy = yj - m.cc[1], dz = zj - m.cc[2];
+__device__ __forceinline__ bool pair_shift(const DevConst& dc, const PairConst& pc, const double* cc, double& xj, double& yj, double& zj) {
+    double dx = xj - cc[0], dy = yj - cc[1], dz = zj - cc[2];
     if (TRI) {   // the image inside the brick around the molecule's centre
         min_image_tri_brick(dc, dx, dy, dz);
-        xj = m.cc[0] + dx; yj = m.cc[1] + dy; zj = m.cc[2] + dz;
+        xj = cc[0] + dx; yj = cc[1] + dy; zj = cc[2] + dz;
     } else {
         const double big = 6755399441055744.0;
         const double nx = fma(dx, pc.iLx, big) - big, ny = fma(dy, pc.iLy, big) - big, nz = fma(dz, pc.iLz, big) - big;
         xj = fma(-nx, pc.Lx, xj); yj = fma(-ny, pc.Ly, yj); zj = fma(-nz, pc.Lz, zj);
-        dx = xj - m.cc[0]; dy = yj - m.cc[1]; dz = zj - m.cc[2];
+        dx = xj - cc[0]; dy = yj - cc[1]; dz = zj - cc[2];
     }
-    return !(fma(dx, dx, fma(dy, dy, dz * dz)) > m.cc[3]);
+    return !(fma(dx, dx, fma(dy, dy, dz * dz)) > cc[3]);
 }
 
 // PREP: the atom was already shifted and sphere-tested by pair_shift (compacted sweep)
 template <bool OLD, bool NEW, bool SHIFT, bool TRI, bool PREP = false>
 __device__ __forceinline__ void pair_atom(const DevConst& dc, const PairConst& pc, const SweepCtx& s, int ntypes, double xj, double yj, double zj,
-                                          double qj, int tj, double (&acc)[4], unsigned& cnt) {
+                                          double qj, int tj, bool uo, bool un, const double* cc, double (&acc)[4], unsigned& cnt) {
     const MolS& m = *s.mol;
     if (SHIFT && !PREP) {
-        if (!pair_shift<TRI>(dc, pc, m, xj, yj, zj)) return;  // beyond reach of every atom of the molecule
+        if (!pair_shift<TRI>(dc, pc, cc, xj, yj, zj)) return;  // beyond reach of every atom of the molecule
     }
-    const bool use_old = OLD && (!TRI || m.do_old), use_new = NEW && (!TRI || m.do_new);
+    const bool use_old = OLD && uo, use_new = NEW && un;   // uo / un: run-time masks (compile-time true where the instantiation fixes the set)
     const bool qj_ok = fabs(qj) >= MMC_ERR;
     const int nat = m.nat;
 #pragma unroll 2
@@ -415,7 +426,7 @@ struct CompactQ { double x, y, z, q; int t, n; };
 // per-warp shared scratch (each survivor writes its lane id at its rank), the data moves by warp shuffles.
 template <bool OLD, bool NEW, bool TRI>
 __device__ __forceinline__ void compact_push(const DevConst& dc, const PairConst& pc, const SweepCtx& s, CompactQ& cq, bool in, double xj, double yj,
-                                             double zj, double qj, int tj, bool flush, double (&acc)[4], unsigned& cnt) {
+                                             double zj, double qj, int tj, bool flush, bool uo, bool un, const double* cc, double (&acc)[4], unsigned& cnt) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     unsigned char* scr = s.cscr + (threadIdx.x >> 5) * 32;
@@ -436,7 +447,7 @@ __device__ __forceinline__ void compact_push(const DevConst& dc, const PairConst
             n += take; consumed += take;
         }
         if (n == 32 || (flush && consumed == c && n > 0)) {
-            if (lane < n) pair_atom<OLD, NEW, true, TRI, true>(dc, pc, s, dc.ntypes, cq.x, cq.y, cq.z, cq.q, cq.t, acc, cnt);
+            if (lane < n) pair_atom<OLD, NEW, true, TRI, true>(dc, pc, s, dc.ntypes, cq.x, cq.y, cq.z, cq.q, cq.t, uo, un, cc, acc, cnt);
             __syncwarp();
             n = 0;
         }
@@ -481,22 +492,24 @@ __device__ __forceinline__ bool tile_in_reach(const DevConst& dc, const MolS& m,
 // Real-space phase of one trial.  Work items = framework tiles in reach (ordered compaction of the cull
 // result, so the item -> warp assignment and hence the summation order is deterministic) followed by tiles
 // of 32 guest atoms.  Item i goes to global warp i mod (n_parts * warps).  All threads of the block.
+// OLD / NEW: geometries this instantiation can evaluate; uo / un: run-time masks on top (true where the instantiation fixes the
+// set); fw / guests: sweep the framework tiles / this chain's guests; cc: the sphere {x, y, z, R^2} of the geometries swept.
 template <int NT, bool OLD, bool NEW, bool SHIFT, bool TRI>
 __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                    double (&acc)[4], unsigned& cnt) {
+                                    bool uo, bool un, bool fw, bool guests, const double* cc, double (&acc)[4], unsigned& cnt, int& item0) {
     const MolS& m = *s.mol;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int gw = part * (NT / 32) + warp, gstride = n_parts * (NT / 32);
     PairConst pc = {dc.L[0], dc.L[1], dc.L[2], dc.invL[0], dc.invL[1], dc.invL[2], dc.reach2, dc.alpha, dc.rc2, dc.gtab_smin, dc.gtab_smax, dc.gtab_base, dc.gtab_deg_start[0], dc.gtab_deg_start[1]};
     const bool cull = dc.reach2 < 1e300;
     CompactQ cq = {0.0, 0.0, 0.0, 0.0, 0, 0};   // compacted sweep (SHIFT): survivors carried between tiles
-    int item0 = 0;
-    for (int base = 0; base < dc.n_tiles; base += CULL_CHUNK) {
+    // item0 (in / out): items dealt so far in this trial -- a second call goes on dealing where the first one stopped
+    for (int base = 0; fw && base < dc.n_tiles; base += CULL_CHUNK) {
         const int n = min(CULL_CHUNK, dc.n_tiles - base);
         const int nwords = (n + 31) >> 5;
         for (int i0 = warp * 32; i0 < n; i0 += NT) {
             const int i = i0 + lane;
-            const bool hit = i < n && (!cull || tile_in_reach<TRI>(dc, m, base + i, OLD && (!TRI || m.do_old), NEW && (!TRI || m.do_new)));
+            const bool hit = i < n && (!cull || tile_in_reach<TRI>(dc, m, base + i, OLD && uo, NEW && un));
             const unsigned b = __ballot_sync(0xffffffffu, hit);
             if (lane == 0) s.mask[i0 >> 5] = b;
         }
@@ -533,9 +546,9 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
                 double xj = 0.0, yj = 0.0, zj = 0.0, qj = 0.0; int tj = 0; bool in = false;
                 if (j < dc.n_fw) {
                     xj = dc.sx[j]; yj = dc.sy[j]; zj = dc.sz[j]; qj = dc.sq[j]; tj = dc.stype[j];
-                    in = pair_shift<TRI>(dc, pc, m, xj, yj, zj);
+                    in = pair_shift<TRI>(dc, pc, cc, xj, yj, zj);
                 }
-                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, acc, cnt);
+                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, uo, un, cc, acc, cnt);
             }
         } else
 #endif
@@ -556,20 +569,20 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
                     vn = j < dc.n_fw;
                     if (vn) { xn = dc.sx[j]; yn = dc.sy[j]; zn = dc.sz[j]; qn = dc.sq[j]; tn = dc.stype[j]; }
                 }
-                if (v) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, xj, yj, zj, qj, tj, acc, cnt);
+                if (v) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, xj, yj, zj, qj, tj, uo, un, cc, acc, cnt);
             }
         }
 #else
         for (int it = (gw + gstride - item0 % gstride) % gstride; it < nlist; it += gstride) {
             const int j = (base + (int)s.list[it]) * TILE + lane;
-            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], acc, cnt);
+            if (j < dc.n_fw) pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, dc.sx[j], dc.sy[j], dc.sz[j], dc.sq[j], dc.stype[j], uo, un, cc, acc, cnt);
         }
 #endif
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
     }
     // guests of this chain: slots [0, count) of every active residue, the moved slot excluded
-    for (int ia = 0; ia < dc.n_active; ia++) {
+    for (int ia = 0; guests && ia < dc.n_active; ia++) {
         const int r = dc.active_list[ia], na = dc.natoms[r];
         const int n_at = cs.count[c * MMC_MAX_RES + r] * na;
         const int ntile = (n_at + 31) >> 5;
@@ -584,10 +597,10 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
                     if (!(m.excl && r == m.res && mol == m.mol)) {
                         xj = cs.gx[base + i]; yj = cs.gy[base + i]; zj = cs.gz[base + i];
                         qj = dc.res_q[r * MMC_MAX_MOL_ATOMS + a]; tj = dc.res_type[r * MMC_MAX_MOL_ATOMS + a];
-                        in = pair_shift<TRI>(dc, pc, m, xj, yj, zj);
+                        in = pair_shift<TRI>(dc, pc, cc, xj, yj, zj);
                     }
                 }
-                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, acc, cnt);
+                compact_push<OLD, NEW, TRI>(dc, pc, s, cq, in, xj, yj, zj, qj, tj, false, uo, un, cc, acc, cnt);
                 continue;
             }
 #endif
@@ -595,30 +608,32 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
                 const int mol = i / na, a = i - mol * na;
                 if (!(m.excl && r == m.res && mol == m.mol))
                     pair_atom<OLD, NEW, SHIFT, TRI>(dc, pc, s, dc.ntypes, cs.gx[base + i], cs.gy[base + i], cs.gz[base + i], dc.res_q[r * MMC_MAX_MOL_ATOMS + a],
-                                        dc.res_type[r * MMC_MAX_MOL_ATOMS + a], acc, cnt);
+                                        dc.res_type[r * MMC_MAX_MOL_ATOMS + a], uo, un, cc, acc, cnt);
             }
         }
         item0 += ntile;
     }
 #ifdef MMC_COMPACT
-    if (SHIFT) compact_push<OLD, NEW, TRI>(dc, pc, s, cq, false, 0.0, 0.0, 0.0, 0.0, 0, true, acc, cnt);   // the partial last batch
+    if (SHIFT) compact_push<OLD, NEW, TRI>(dc, pc, s, cq, false, 0.0, 0.0, 0.0, 0.0, 0, true, uo, un, cc, acc, cnt);   // the partial last batch
 #endif
 }
 
+// uo / un: geometries wanted; fw / guests: which atoms to sweep; cc: their sphere.  rt: use the one instantiation that masks
+// OLD / NEW at run time (tilted cells always; the guests-only pass, which is small, so that it adds one inlined copy, not three)
 template <int NT, bool TRI>
 __device__ __forceinline__ void pair_phase(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, int part, int n_parts,
-                                  double (&acc)[4], unsigned& cnt) {
+                                  bool uo, bool un, bool fw, bool guests, bool rt, const double* cc, double (&acc)[4], unsigned& cnt, int& item0) {
     const MolS& m = *s.mol;
-    if (m.kind <= 0) return;
-    const bool sh = m.shift_ok && dc.reach2 < 1e300;
-    if (TRI) {   // tilted cell (kernels compiled for it): one instantiation per shift mode, OLD / NEW masked at run time
-        if (sh) pair_phase_t<NT, true, true, true, true>(dc, cs, c, s, part, n_parts, acc, cnt);
-        else pair_phase_t<NT, true, true, false, true>(dc, cs, c, s, part, n_parts, acc, cnt);
+    if (m.kind <= 0 || !(uo || un) || !(fw || guests)) return;
+    const bool sh = (cc == m.ccf ? m.shift_okf : m.shift_ok) && dc.reach2 < 1e300;
+    if (TRI || rt) {
+        if (sh) pair_phase_t<NT, true, true, true, TRI>(dc, cs, c, s, part, n_parts, uo, un, fw, guests, cc, acc, cnt, item0);
+        else pair_phase_t<NT, true, true, false, TRI>(dc, cs, c, s, part, n_parts, uo, un, fw, guests, cc, acc, cnt, item0);
         return;
     }
-    if (m.do_old && m.do_new) { if (sh) pair_phase_t<NT, true, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
-    else if (m.do_old) { if (sh) pair_phase_t<NT, true, false, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, true, false, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
-    else if (m.do_new) { if (sh) pair_phase_t<NT, false, true, true, false>(dc, cs, c, s, part, n_parts, acc, cnt); else pair_phase_t<NT, false, true, false, false>(dc, cs, c, s, part, n_parts, acc, cnt); }
+    if (uo && un) { if (sh) pair_phase_t<NT, true, true, true, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); else pair_phase_t<NT, true, true, false, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); }
+    else if (uo) { if (sh) pair_phase_t<NT, true, false, true, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); else pair_phase_t<NT, true, false, false, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); }
+    else { if (sh) pair_phase_t<NT, false, true, true, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); else pair_phase_t<NT, false, true, false, false>(dc, cs, c, s, part, n_parts, true, true, fw, guests, cc, acc, cnt, item0); }
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -757,8 +772,9 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
     if (nterm == 0) {
         // no charged atom moved: A' = A.  The energies are still summed and A copied (the reference re-sums it, ewald_energy.f90:259-272)
     }
-    const double2* A = cs.A + ((size_t)c * 2 + m.cur) * dc.nk;
-    double2* An = cs.A + ((size_t)c * 2 + (m.cur ^ 1)) * dc.nk;
+    const int cur = __shfl_sync(0xffffffffu, m.cur, 0);
+    const double2* A = cs.A + ((size_t)c * 2 + cur) * dc.nk;
+    double2* An = cs.A + ((size_t)c * 2 + (cur ^ 1)) * dc.nk;
     const int nrows = s.nx * s.ny;
     const int rpp = (nrows + n_parts - 1) / n_parts;
     const int r0 = min(nrows, part * rpp), r1 = min(nrows, r0 + rpp);
@@ -914,27 +930,57 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
 // the reciprocal sweep so that its item loop does not carry them in registers (64 registers per thread at 4 CTAs/SM).
 // TRI: compiled for tilted cells (dc.tri); the orthorhombic kernels carry none of that code
 template <int NT, bool TRI>
-__device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int part, int n_parts, int phases) {
+__device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int part, int n_parts, int phases,
+                                            Trial* tw = nullptr) {
+    // tw != nullptr (the one-CTA batched kernel, which owns the Trial): the framework-energy cache is read and its next
+    // values are left in *tw for commit_trial
     const bool swap = t.kind == MMC_SWAP;
+    const bool cache = tw != nullptr && dc.fw_cache && !swap && (phases & 1);
     stage_terms<TRI>(dc, cs, c, s, t);
-    stage_molecule(dc, cs, c, s, t, swap ? 1 : 0);
+    stage_molecule(dc, cs, c, s, t, swap ? 1 : 0, cache);
     MMC_TSTAMP(1);
     {
+        // pa[0..3]: {LJ, Coulomb} of the old and of the new geometry.  With the cache the framework part is summed on its own, so
+        // that the new geometry's can be stored (the old geometry's is skipped when it is known), and parked as rows 4..7 of
+        // s.red before the guests are swept: the two sets of partial sums never hold registers at the same time
         double pa[4] = {0, 0, 0, 0};
         unsigned cnt = 0u;   // executed work of this thread in this trial: low 16 bits = distances formed, high 16 = pairs inside reach
-        if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
-        if (swap) {   // second real-space sweep: the inserted molecule (different atom set), the removed one still excluded
-            __syncthreads();
-            stage_molecule(dc, cs, c, s, t, 2);
-            if (phases & 1) pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, pa, cnt);
+        int item0 = 0;       // work items dealt to the warps so far (the guests' tiles go on where the framework's stopped)
+        const MolS& m = *s.mol;
+        // one call site per sweep flavour (each is a fully inlined copy of the pair loop): a swap runs it twice, first for the
+        // removed molecule, then for the inserted one (different atom set, the removed one still excluded)
+        for (int pass = 0; pass < (swap ? 2 : 1); pass++) {
+            if (pass) { __syncthreads(); stage_molecule(dc, cs, c, s, t, 2); }
+            if (!(phases & 1)) continue;
+            // framework (and, without the cache, the guests as well): m.fo / m.ccf equal do_old / cc when nothing is cached
+            pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, m.fo != 0, m.do_new != 0, true, !cache, false, m.ccf, pa, cnt, item0);
+            if (cache) {
+                block_sum_park<4, NT>(pa, s.red, 4);
+                for (int i = 0; i < 4; i++) pa[i] = 0.0;
+                pair_phase<NT, TRI>(dc, cs, c, s, part, n_parts, m.do_old != 0, m.do_new != 0, false, true, true, m.cc, pa, cnt, item0);
+            }
         }
         const unsigned w0 = __reduce_add_sync(0xffffffffu, cnt & 0xffffu), w1 = __reduce_add_sync(0xffffffffu, cnt >> 16);
         if ((threadIdx.x & 31) == 0 && (w0 | w1)) { atomicAdd(&s.mol->work[0], w0); atomicAdd(&s.mol->work[1], w1); }
 #ifdef MMC_PHASE_TIMING
         __syncthreads(); MMC_TSTAMP(2);
 #endif
-        block_sum<4, NT>(pa, s.red);
-        if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];
+        if (cache) {
+            block_sum_park<4, NT>(pa, s.red, 0);
+            double v[8];
+            block_sum_gather<8, NT>(v, s.red);
+            if (threadIdx.x == 0) {
+                const bool cached = m.fw_cached != 0;
+                const double fo0 = cached ? m.fw_old[0] : v[4], fo1 = cached ? m.fw_old[1] : v[5];
+                s.mol->sums[0] = v[0] + fo0; s.mol->sums[1] = v[1] + fo1;
+                s.mol->sums[2] = v[2] + v[6]; s.mol->sums[3] = v[3] + v[7];
+                tw->fw_new_ok = m.do_new != 0; tw->fw_new[0] = v[6]; tw->fw_new[1] = v[7];
+                tw->fw_old_fresh = m.fo != 0; tw->fw_old[0] = fo0; tw->fw_old[1] = fo1;
+            }
+        } else {
+            block_sum<4, NT>(pa, s.red);
+            if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];
+        }
         MMC_TSTAMP(3);
     }
     {

@@ -193,6 +193,7 @@ static int upload_chain(mmc_handle* h, int c, const int* count, const double* co
     CK(cudaMemcpyAsync(h->cs.gy + (size_t)c * dc.g_atoms, s_y, (size_t)dc.g_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.gz + (size_t)c * dc.g_atoms, s_z, (size_t)dc.g_atoms * sizeof(double), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.count + (size_t)c * MMC_MAX_RES, s_cnt, MMC_MAX_RES * sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(h->cs.fw_pair + (size_t)c * dc.g_mols, 0xFF, (size_t)dc.g_mols * sizeof(double2), st));   // new geometry: cached framework sums are void
     CK(cudaStreamSynchronize(st));
     if (h->h_count.size() != (size_t)dc.n_chains * MMC_MAX_RES) h->h_count.assign((size_t)dc.n_chains * MMC_MAX_RES, 0);
     for (int r = 0; r < MMC_MAX_RES; r++) h->h_count[(size_t)c * MMC_MAX_RES + r] = s_cnt[r];
@@ -477,6 +478,8 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     memset(&dc, 0, sizeof dc);
     dc.nres = d->nres; dc.ntypes = d->ntypes; dc.n_chains = d->n_chains;
     dc.deletion_mode = d->deletion_mode; dc.use_table = d->use_table;
+    dc.fw_cache = 1;   // MANIAC_FW_CACHE=0: re-sum the framework part of the old geometry in every trial, as the reference does (A/B switch)
+    if (const char* e = getenv("MANIAC_FW_CACHE")) dc.fw_cache = atoi(e) != 0;
     dc.shard_count = d->shard_count > 1 ? d->shard_count : 1;
     dc.shard_rank = d->shard_count > 1 ? d->shard_rank : 0;
     if (dc.shard_rank < 0 || dc.shard_rank >= dc.shard_count) { delete h; return fail("mmc_init: shard_rank %d outside [0,%d)", d->shard_rank, dc.shard_count); }
@@ -597,6 +600,7 @@ extern "C" int mmc_init(mmc_t** out, const mmc_desc* d) {
     CKB(dalloc(h, &cs.energy, C * MMC_NE)); CKB(dalloc(h, &cs.fug, C * MMC_MAX_RES));
     CKB(dalloc(h, &cs.temp, C)); CKB(dalloc(h, &cs.tstep, C)); CKB(dalloc(h, &cs.rstep, C));
     CKB(dalloc(h, &cs.counters, C)); CKB(dalloc(h, &cs.trial, C));
+    CKB(dalloc(h, &cs.fw_pair, C * dc.g_mols)); CKB(cudaMemset(cs.fw_pair, 0xFF, C * dc.g_mols * sizeof(double2)));   // all NaN: nothing known yet
     {   // reservoir pools (mmc_desc.reservoir_*): one per chain, every chain starts from the same pool
         dc.has_reservoir = (d->reservoir_count && d->reservoir_offsets) ? 1 : 0;
         int ra = 0;
@@ -801,6 +805,7 @@ extern "C" int mmc_upload_chains(mmc_t* h, const int* count, const double* com, 
     CK(cudaMemcpy2DAsync(h->cs.count, MMC_MAX_RES * sizeof(int), count, dc.nres * sizeof(int), dc.nres * sizeof(int), C, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.gcom, com, C * dc.g_mols * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.goff, offsets, C * dc.g_atoms * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(h->cs.fw_pair, 0xFF, C * dc.g_mols * sizeof(double2), st));
     k_rebuild_positions<<<dim3((dc.g_atoms + 255) / 256, (unsigned)C), 256, 0, st>>>(dc, h->cs);
     h->launches++;
     CK(cudaGetLastError());

@@ -252,6 +252,73 @@ def test_cluster_per_chain_kernel(which, P, monkeypatch):
     g.close(); g1.close()
 
 
+@pytest.mark.parametrize("which", ["zif8_h2o", "zif8_ch4o_h2o", "tilted"])
+def test_framework_energy_cache(which, monkeypatch):
+    """ChainState.fw_pair: the one-CTA batched kernel keeps, per guest molecule, the framework part of its pair energy and
+    re-sums only the guest-guest part of the old geometry (the framework never moves).  The same Philox streams with the
+    cache (default) and without it (MANIAC_FW_CACHE=0, the reference's re-summation, ComputeOldEnergy
+    monte_carlo_utils.f90:347-396): identical accept sequences and counters, records within 1e-12 of each other (the split
+    changes only the association of the sums) and 1e-10 of the oracle.  Then every path that changes a geometry behind the
+    cache's back -- a strict-mode move (mmc_trial_step), a re-upload of one chain, mmc_upload_chains -- followed by another
+    batch: a stale entry would show up as an energy difference between the two handles and against a fresh total."""
+    if which == "zif8_h2o":
+        s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
+    elif which == "zif8_ch4o_h2o":
+        s = load_system("zif8_ch4o_h2o", init_sk=1, deletion_mode=1); s.p_translation, s.p_rotation, s.p_swap = 0.25, 0.25, 0.3
+    else:
+        s = tilted_framework(n_fw=3000, box=48.0, tilt=(7.0, -5.0, 9.0))
+    n, seed, C = 400, 777, 3
+    g = ManiacGPU(s, n_chains=C)
+    monkeypatch.setenv("MANIAC_FW_CACHE", "0")
+    g0 = ManiacGPU(s, n_chains=C)
+    monkeypatch.delenv("MANIAC_FW_CACHE")
+    handles = (g, g0)
+    for h in handles:
+        h.system_energy_all()
+    step0 = 0
+
+    def batch(k):
+        nonlocal step0
+        ra, rb = g.run_batch(k, seed=seed, records=True), g0.run_batch(k, seed=seed, records=True)
+        for c in range(C):
+            compare_records(ra[c], rb[c], tol=1e-12)
+        assert list(g.counters) == list(g0.counters)
+        step0 += k
+        return ra
+
+    ra = batch(n)
+    assert (ra["accepted"] == 1).sum() > n // 4 and set(np.unique(ra["kind"])) >= {1, 2, 3, 4}
+    o = orc.Oracle(s); o.system_energy()
+    compare_records(ra[1], o.run(n, seed=seed, chain=1, step0=0))
+    # (a) strict-mode moves on chain 0 of both handles: translate molecule 0 of the first populated active residue, always accepted (u = 0)
+    for k in range(3):
+        for h in handles:
+            cnt, com, off, e = h.sync_to_host(0)
+            r = int(np.flatnonzero((s.is_active == 1) & (cnt > 0))[0])
+            mo, ao, na = int(cnt[:r].sum()), int((cnt[:r] * s.natoms[:r]).sum()), int(s.natoms[r])
+            old, new, prob, acc = h.trial_step(MMC_TRANSLATION, r, 0, com_new=com[mo] + np.array([0.31, -0.22, 0.17]) * (k + 1),
+                                               offs_new=off[ao:ao + na], u=0.0, chain=0)
+            assert acc or prob == 0.0
+    batch(150)
+    # (b) chain 1's state uploaded into chain 2 (mmc_set_chain_state), totals recomputed
+    for h in handles:
+        cnt, com, off, e = h.sync_to_host(1)
+        h.set_chain_state(2, cnt, com, off); h.system_energy(2)
+    batch(150)
+    # (c) every chain re-uploaded at once (mmc_upload_chains): chains rotated by one
+    gm, ga = g.chain_capacity()
+    for h in handles:
+        cnt = np.zeros((C, s.nres), dtype=np.int32); com = np.zeros((C, gm, 3)); off = np.zeros((C, ga, 3))
+        h.download_chains(cnt, com, off, None, None)
+        h.upload_chains(np.roll(cnt, 1, axis=0), np.roll(com, 1, axis=0), np.roll(off, 1, axis=0)); h.system_energy_all()
+    batch(150)
+    for c in range(C):
+        e_tracked = g.sync_to_host(c)[3]
+        assert rel_err(e_tracked, g0.sync_to_host(c)[3]) < 1e-12
+        assert rel_err(e_tracked, g.system_energy(c)) < TOL
+    g.close(); g0.close()
+
+
 def test_per_chain_parameters():
     """Isotherm sweep: each chain has its own fugacity/temperature."""
     s = load_system("zif8_h2o", init_sk=1, deletion_mode=1)
