@@ -89,6 +89,10 @@ def workload_config(args, s, world):
             "quirks": "deletion=physical; init_sk=full on the device arm, init_sk=zero (reference default: no O(N K) start-up) on the CPU arm -- "
                       "the per-move work is the same",
             "rng": "Philox4x32-10 keyed by (seed; step, global chain id, draw), same generator in both arms",
+            "real_space": "device arm: the framework part of a guest molecule's pair energy is kept per molecule (the framework never "
+                          "moves) and reused as the old geometry's, everything else is summed every move; CPU arm: every pair re-summed "
+                          "every move as in the reference -- same energies to 1e-10 (tests/test_gpu_parity.py::test_framework_energy_cache); "
+                          "MANIAC_FW_CACHE=0 switches the device arm to the reference's re-summation",
             "l2": "256 MiB write between steps (inside the timed region, device arm)"}
 
 

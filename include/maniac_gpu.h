@@ -336,6 +336,11 @@ int mmc_profile_kernels(mmc_t* handle, int n_steps, uint64_t seed, double ms[3],
  * out[0..6] = propose, stage, cull + real-space sweep, block sum, reciprocal sweep, block sum, finalize + commit;
  * out[7] = trials counted.  All zero in production builds. */
 int mmc_dbg_phase_cycles(mmc_t* handle, int64_t out[8]);
+/* The framework-energy cache of one chain (no counterpart in the reference, which re-sums the framework part of the old
+ * geometry's pair energy in every move, ComputeOldEnergy monte_carlo_utils.f90:347-396): out[2 * slot + {0, 1}] = {LJ,
+ * Coulomb before the 1/(4 pi eps0) factor} of the guest molecule in device slot `slot` with the framework, for the g_mols
+ * slots of mmc_chain_capacity; NaN where nothing is cached.  Tests only. */
+int mmc_dbg_fw_cache(mmc_t* handle, int chain, double* out);
 /* FP64 FMA peak micro-benchmark (register-resident DFMA chains): returns TFLOP/s */
 int mmc_measure_fp64_peak(int device, double* tflops);
 

@@ -509,6 +509,11 @@ __global__ void k_rebuild_positions(DevConst dc, ChainState cs) {
     const size_t ia = (size_t)c * dc.g_atoms + g;
     const double* com = cs.gcom + ((size_t)c * dc.g_mols + dc.g_mol_base[r] + m) * 3;
     const double* off = cs.goff + ia * 3;
-    cs.gx[ia] = com[0] + off[0]; cs.gy[ia] = com[1] + off[1]; cs.gz[ia] = com[2] + off[2];
+    const double x = com[0] + off[0], y = com[1] + off[1], z = com[2] + off[2];
+    // framework-energy cache: an entry stays valid exactly when every atom of its molecule is, bit for bit, where it was (the
+    // same sum com + off as build_trial's p_new): a host that uploads what it downloaded keeps the cache
+    if (dc.fw_cache && (x != cs.gx[ia] || y != cs.gy[ia] || z != cs.gz[ia]))
+        cs.fw_pair[(size_t)c * dc.g_mols + dc.g_mol_base[r] + m] = make_double2(__longlong_as_double(-1LL), __longlong_as_double(-1LL));
+    cs.gx[ia] = x; cs.gy[ia] = y; cs.gz[ia] = z;
 }
 __global__ void k_advance(BatchCtl* ctl, int g) { ctl->rng.step += (unsigned long long)g; ctl->rec_base += g; }

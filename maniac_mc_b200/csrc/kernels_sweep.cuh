@@ -534,6 +534,9 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
         }
         __syncthreads();
         const int nlist = m.nlist;
+#ifdef MMC_RS_SPLIT   // diagnostic (with MMC_PHASE_TIMING): slot 3 = tile cull, slot 5 = framework tiles, slot 2 = the rest of the real-space phase
+        MMC_TSTAMP(3);
+#endif
 #ifdef MMC_COMPACT
         if (SHIFT) {
             // Compacted sweep: only ~half of the lanes of a visited tile hold an atom inside the molecule's sphere (tile boxes
@@ -580,6 +583,9 @@ __device__ __forceinline__ void pair_phase_t(const DevConst& dc, const ChainStat
 #endif
         item0 += nlist;
         __syncthreads();  // list is rebuilt by the next chunk
+#ifdef MMC_RS_SPLIT
+        MMC_TSTAMP(5);
+#endif
     }
     // guests of this chain: slots [0, count) of every active residue, the moved slot excluded
     for (int ia = 0; guests && ia < dc.n_active; ia++) {

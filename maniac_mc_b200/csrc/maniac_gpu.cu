@@ -805,7 +805,6 @@ extern "C" int mmc_upload_chains(mmc_t* h, const int* count, const double* com, 
     CK(cudaMemcpy2DAsync(h->cs.count, MMC_MAX_RES * sizeof(int), count, dc.nres * sizeof(int), dc.nres * sizeof(int), C, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.gcom, com, C * dc.g_mols * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(h->cs.goff, offsets, C * dc.g_atoms * 3 * sizeof(double), cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(h->cs.fw_pair, 0xFF, C * dc.g_mols * sizeof(double2), st));
     k_rebuild_positions<<<dim3((dc.g_atoms + 255) / 256, (unsigned)C), 256, 0, st>>>(dc, h->cs);
     h->launches++;
     CK(cudaGetLastError());
@@ -1591,6 +1590,17 @@ extern "C" int mmc_dbg_phase_cycles(mmc_t* h, int64_t out[8]) {
     unsigned long long v[8];
     CK(cudaMemcpy(v, h->cs.pair_count + 2, sizeof v, cudaMemcpyDeviceToHost));
     for (int i = 0; i < 8; i++) out[i] = (int64_t)v[i];
+    return 0;
+}
+
+// the framework-energy cache of one chain (ChainState.fw_pair): out[2 * slot + {0, 1}] = {LJ, Coulomb in reduced units} of the
+// molecule in device slot `slot` (slots of mmc_chain_capacity's g_mols), NaN where nothing is cached
+extern "C" int mmc_dbg_fw_cache(mmc_t* h, int chain, double* out) {
+    CHECK_CHAIN(h, chain);
+    if (!out) return fail("mmc_dbg_fw_cache: null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(out, h->cs.fw_pair + (size_t)chain * h->dc.g_mols, (size_t)h->dc.g_mols * sizeof(double2), cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "mmc_dbg_erfc", "mmc_stream", "mmc_launch_count", "mmc_measure_fp64_peak",
     "mmc_chain_capacity", "mmc_upload_chains", "mmc_download_chains", "mmc_profile_kernels", "mmc_pair_work",
     "mmc_shard_step_begin", "mmc_shard_step_end", "mmc_shard_trial_begin", "mmc_shard_trial_end", "mmc_shard_range",
-    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_trial_step", "mmc_dbg_strict_loop", "mmc_erfc_noalloc", "mmc_chain_launch_config",
+    "mmc_snapshot_begin", "mmc_snapshot_wait", "mmc_dbg_set_tracked", "mmc_system_energy_all", "mmc_dbg_phase_cycles", "mmc_dbg_fw_cache", "mmc_trial_step", "mmc_dbg_strict_loop", "mmc_erfc_noalloc", "mmc_chain_launch_config",
 ]
 
 _lib = None
@@ -99,6 +99,7 @@ def load():
     L.mmc_dbg_set_tracked.argtypes = [vp, C.c_int, dp, dp]
     L.mmc_dbg_strict_loop.argtypes = [vp, C.c_int, C.c_int, C.c_uint64, C.c_int, dp, C.POINTER(C.c_int64)]
     L.mmc_dbg_phase_cycles.argtypes = [vp, C.POINTER(C.c_int64)]
+    L.mmc_dbg_fw_cache.argtypes = [vp, C.c_int, dp]
     L.mmc_stream.argtypes = [vp]; L.mmc_stream.restype = vp
     L.mmc_launch_count.argtypes = [vp]; L.mmc_launch_count.restype = C.c_int64
     L.mmc_chain_launch_config.argtypes = [vp, ip, ip]
@@ -441,6 +442,13 @@ class ManiacGPU:
         _ck(load().mmc_dbg_phase_cycles(self.h, v))
         names = ("propose", "stage", "real_space", "sum4", "reciprocal", "sum2", "finalize_commit", "trials")
         return dict(zip(names, (int(x) for x in v)))
+
+    def fw_cache(self, chain=0):
+        """[g_mols, 2] framework-energy cache of one chain by device slot (NaN = nothing cached)"""
+        gm, _ = self.chain_capacity()
+        out = np.zeros((gm, 2))
+        _ck(load().mmc_dbg_fw_cache(self.h, chain, _dp(out)))
+        return out
 
     def pair_work(self):
         """(distances formed, pairs inside reach) by the per-move sweeps since mmc_init"""

@@ -268,7 +268,9 @@ def test_framework_energy_cache(which, monkeypatch):
     else:
         s = tilted_framework(n_fw=3000, box=48.0, tilt=(7.0, -5.0, 9.0))
     n, seed, C = 400, 777, 3
+    monkeypatch.setenv("MANIAC_CLUSTER", "0")      # the cache lives in the one-CTA kernel; so few chains would get the cluster kernel
     g = ManiacGPU(s, n_chains=C)
+    assert g.chain_launch_config()[1] == 1
     monkeypatch.setenv("MANIAC_FW_CACHE", "0")
     g0 = ManiacGPU(s, n_chains=C)
     monkeypatch.delenv("MANIAC_FW_CACHE")
@@ -305,12 +307,25 @@ def test_framework_energy_cache(which, monkeypatch):
         cnt, com, off, e = h.sync_to_host(1)
         h.set_chain_state(2, cnt, com, off); h.system_energy(2)
     batch(150)
-    # (c) every chain re-uploaded at once (mmc_upload_chains): chains rotated by one
+    # (c) every chain re-uploaded at once (mmc_upload_chains).  First WHAT WAS DOWNLOADED: the geometry is bit for bit the
+    # device's, so every cache entry survives (this is bench.py's end-to-end step); then the chains rotated by one: every
+    # entry of a populated slot whose geometry changed is dropped
     gm, ga = g.chain_capacity()
+    known = [g.fw_cache(c) for c in range(C)]
+    assert sum(int(np.isfinite(k[:, 0]).sum()) for k in known) > 3 and not np.isfinite(g0.fw_cache(0)).any()
     for h in handles:
         cnt = np.zeros((C, s.nres), dtype=np.int32); com = np.zeros((C, gm, 3)); off = np.zeros((C, ga, 3))
         h.download_chains(cnt, com, off, None, None)
+        h.upload_chains(cnt, com, off)
+    for c in range(C):
+        assert np.array_equal(g.fw_cache(c), known[c], equal_nan=True)
+    batch(100)
+    for h in handles:
+        h.download_chains(cnt, com, off, None, None)
         h.upload_chains(np.roll(cnt, 1, axis=0), np.roll(com, 1, axis=0), np.roll(off, 1, axis=0)); h.system_energy_all()
+    moved = np.any(np.roll(com, 1, axis=0) != com, axis=2)                       # [C, g_mols]: slot geometry changed by the rotation
+    for c in range(C):
+        assert not np.isfinite(g.fw_cache(c)[moved[c], 0]).any()
     batch(150)
     for c in range(C):
         e_tracked = g.sync_to_host(c)[3]

@@ -23,9 +23,9 @@ for c in range(chains):
     g.set_chain_params(c, bench.chain_fugacity(s, c), s.temperature); g.set_chain_id(c, c)
 g.system_energy_all()
 g.run_batch_async(256, seed=7); g.synchronize()          # warm-up: the chains relax towards their loading
-p0 = g.phase_cycles()
+p0 = g.phase_cycles(); w0 = g.pair_work()
 g.run_batch_async(256, seed=7); g.synchronize()
-p1 = g.phase_cycles()
+p1 = g.phase_cycles(); w1 = g.pair_work()
 n = p1["trials"] - p0["trials"]
 print(f"# {chains} chains x 256 steps, {n} trials timed; cycles per trial of one CTA (thread 0's clock64 between barriers)")
 tot = 0
@@ -33,4 +33,6 @@ for k in ("propose", "stage", "real_space", "sum4", "reciprocal", "sum2", "final
     v = (p1[k] - p0[k]) / max(n, 1); tot += v
     print(f"{k:18s} {v:12.0f} cycles")
 print(f"{'total':18s} {tot:12.0f} cycles = {tot / 1.965e3:.1f} us at 1965 MHz")
+print(f"# per trial: {(w1[0] - w0[0]) / max(n, 1):.0f} distances formed, {(w1[1] - w0[1]) / max(n, 1):.0f} pairs inside reach"
+      "   (-DMMC_RS_SPLIT builds: sum4 = tile cull, sum2 = framework tiles, real_space = the rest of that phase)")
 g.close()
