@@ -50,16 +50,18 @@ __device__ inline void rotate_offsets(int axis, double theta, int nat, const dou
 // the k-sharded path.  write_slot: also write the proposed geometry of a creation / swap into its slot (done by ONE CTA when
 // several build the same trial).
 __device__ inline void build_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, int kind, int r, int m,
-                                   const double* com_new, const double (*off_new)[3], int r2 = -1, bool write_slot = true) {
+                                   const double* com_new, const double (*off_new)[3], int r2 = -1, bool write_slot = true,
+                                   const double2* fw_pre = nullptr) {
     const int nat = dc.natoms[r];
     if (kind != MMC_SWAP) r2 = r;
     const int nat2 = dc.natoms[r2];
     t.kind = kind; t.res = r; t.mol = m; t.nat = nat; t.res2 = r2; t.nat2 = nat2; t.accepted = 0; t.prob = 0.0; t.rsv = -1;
     t.fw_new_ok = 0; t.fw_old_fresh = 0;
     // issued first, consumed last: the stores to `t` below do not have to wait for it
+    // (fw_pre: the caller loaded the entry of (r, m) already, together with the molecule's geometry)
     double2 fwv = make_double2(__longlong_as_double(-1LL), 0.0);
     if (dc.fw_cache && (kind == MMC_TRANSLATION || kind == MMC_ROTATION || kind == MMC_DELETION))
-        fwv = cs.fw_pair[(size_t)c * dc.g_mols + dc.g_mol_base[r] + m];
+        fwv = fw_pre ? *fw_pre : cs.fw_pair[(size_t)c * dc.g_mols + dc.g_mol_base[r] + m];
     for (int a = 0; a < nat; a++) { t.q[a] = dc.q[r][a]; t.type[a] = dc.type[r][a]; }
     for (int a = 0; a < nat2; a++) { t.q2[a] = dc.q[r2][a]; t.type2[a] = dc.type[r2][a]; }
     const int cnt = cs.count[c * MMC_MAX_RES + r];
@@ -162,6 +164,9 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
     const double draw = rng.next();
     mmc_counters& ctr = cs.counters[c];
     double com_new[3]; double off_new[MMC_MAX_MOL_ATOMS][3];
+    // the selected molecule's framework-energy cache entry: requested here, next to the loads of its geometry, used by build_trial
+    double2 fwv = make_double2(__longlong_as_double(-1LL), 0.0);
+    if (dc.fw_cache && m >= 0) fwv = cs.fw_pair[(size_t)c * dc.g_mols + dc.g_mol_base[r] + m];
     if (draw <= dc.p_translation) {
         if (m >= 0) {  // Translation translation.f90:36-112
             if (lead) ctr.trial_translations++;
@@ -181,7 +186,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
                 com_new[d] = dc.lo[d] + f_modulo(x - dc.lo[d], dc.L[d], dc.invL[d]);  // ApplyPBC
             }
             for (int a = 0; a < nat; a++) for (int d = 0; d < 3; d++) off_new[a][d] = cs.goff[g_atom(dc, c, r, m, a) * 3 + d];
-            build_trial(dc, cs, c, t, MMC_TRANSLATION, r, m, com_new, off_new, -1, lead);
+            build_trial(dc, cs, c, t, MMC_TRANSLATION, r, m, com_new, off_new, -1, lead, &fwv);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation) {
         if (nat != 1 && m >= 0) {  // Rotation rotation.f90:34-75
@@ -193,7 +198,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             rotate_offsets(axis, theta, nat, off_old, off_new);
             const double* com = g_com(dc, cs, c, r, m);
             for (int d = 0; d < 3; d++) com_new[d] = com[d];
-            build_trial(dc, cs, c, t, MMC_ROTATION, r, m, com_new, off_new, -1, lead);
+            build_trial(dc, cs, c, t, MMC_ROTATION, r, m, com_new, off_new, -1, lead, &fwv);
         }
     } else if (draw <= dc.p_rotation + dc.p_translation + dc.p_swap) {
         // swap (identity exchange): remove (r, m), insert a molecule of another active type at the same
@@ -252,7 +257,7 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
             }
         } else if (cnt != 0) {  // DeleteMolecule delete_molecule.f90:41-199
             if (lead) ctr.trial_deletions++;
-            build_trial(dc, cs, c, t, MMC_DELETION, r, m, nullptr, nullptr, -1, lead);
+            build_trial(dc, cs, c, t, MMC_DELETION, r, m, nullptr, nullptr, -1, lead, &fwv);
         }
     }
     t.draw = rng.draw;
