@@ -99,7 +99,7 @@ struct Trial {
     int rsv;               // creation with a reservoir: pool slot the geometry was copied from
     // Framework-energy cache (ChainState.fw_pair): fw_old = cached {LJ, Coulomb (reduced units)} of the selected molecule with the
     // framework at its current geometry, fw_old_ok = it was valid when the trial was built; after the sweep fw_new / fw_old hold
-    // the sums of THIS trial when fw_new_ok / fw_old_fresh say so (one-CTA batched kernel only), for commit_trial to store
+    // the sums of THIS trial when fw_new_ok / fw_old_fresh say so (the batched kernels only: fold_fw_cache), for commit_trial to store
     int fw_old_ok, fw_new_ok, fw_old_fresh;
     double fw_old[2], fw_new[2];
     double prob;

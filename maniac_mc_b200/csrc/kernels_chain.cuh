@@ -42,11 +42,12 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
         }
         __syncthreads();
         MMC_TSTAMP(0);
-        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, 0, 1, phases, s.trial);
+        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, 0, 1, phases, true);
         if (threadIdx.x == 0) {
             Trial& t = *s.trial;   // shared memory: the single-thread sections no longer round-trip ~2 kB through global memory
             const int kind = t.kind;
             if (kind > 0) {
+                fold_fw_cache(t, *s.mol, s.mol->sums, s.mol->fws);
                 finalize_trial(dc, cs, c, t, s.mol->sums);
                 RngSrc rs = ctl->rng;
                 rs.step += (unsigned long long)st;
@@ -114,17 +115,20 @@ __global__ void __launch_bounds__(NT, 2048 / NT / 2) k_chain_run_cl(DevConst dc,
             }
         }
         __syncthreads();
-        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, rank, P, phases);
+        sweep_trial<NT, TRI>(dc, cs, c, s, *s.trial, rank, P, phases, true);
         cluster.sync();                                   // every CTA's s.mol->sums is final
         if (lead && threadIdx.x == 0) {
             Trial& t = *s.trial;
             const int kind = t.kind;
             if (kind > 0) {
-                double v[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                double v[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, fw[4] = {0.0, 0.0, 0.0, 0.0};
                 for (int r = 0; r < P; r++) {             // fixed order: deterministic
                     const double* ps = cluster.map_shared_rank(s.mol->sums, r);
                     for (int i = 0; i < 6; i++) v[i] += ps[i];
+                    const double* pf = cluster.map_shared_rank(s.mol->fws, r);
+                    for (int i = 0; i < 4; i++) fw[i] += pf[i];
                 }
+                fold_fw_cache(t, *s.mol, v, fw);          // the framework-energy cache (every rank took the same decision)
                 finalize_trial(dc, cs, c, t, v);
                 RngSrc rs = ctl->rng;
                 rs.tape = nullptr;

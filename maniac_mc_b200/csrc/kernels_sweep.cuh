@@ -35,6 +35,9 @@ struct MolS {
     double cc[4];       // common sphere of the geometries swept: {x, y, z, (radius + reach)^2}
     double ccf[4];      // the same for the FRAMEWORK sweep (new geometry only when the old one's framework energy is cached)
     double fw_old[2];   // framework part {LJ, Coulomb (reduced)} of the old geometry: from the cache, or summed in this trial
+    double fws[4];      // framework-energy cache on (cache_on): this CTA's FRAMEWORK partial sums {lj_old, coul_old, lj_new, coul_new};
+                        // sums[0..3] then hold the guests' part only (fold_fw_cache puts them together)
+    int cache_on;
     int shift_okf;      // shift_ok of the sphere ccf
     int fo;             // framework sweep evaluates the old geometry (do_old and not cached)
     int fw_cached;      // fw_old came from the cache
@@ -929,6 +932,18 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
 
 #endif  // MMC_RECIP_DMMA
 
+// After sweep_trial(allow_cache) and the sum over the CTAs that shared the trial: v[0..3] = the guests' part of the real-space
+// sums, fw[0..3] = the framework's.  Puts them together (the old geometry's framework part from the cache when it was known)
+// and leaves the cache's next values in the Trial for commit_trial.  Single thread.
+__device__ __forceinline__ void fold_fw_cache(Trial& t, const MolS& m, double* v, const double* fw) {
+    if (!m.cache_on) return;
+    const bool cached = m.fw_cached != 0;
+    const double fo0 = cached ? m.fw_old[0] : fw[0], fo1 = cached ? m.fw_old[1] : fw[1];
+    v[0] += fo0; v[1] += fo1; v[2] += fw[2]; v[3] += fw[3];
+    t.fw_new_ok = m.do_new != 0; t.fw_new[0] = fw[2]; t.fw_new[1] = fw[3];
+    t.fw_old_fresh = m.fo != 0; t.fw_old[0] = fo0; t.fw_old[1] = fo1;
+}
+
 // One trial of chain c, all threads of the CTA: stage, real-space sweep(s), reciprocal sweep.  `part` of `n_parts`
 // CTAs share the trial (1 of 1 in batched mode).  phases: bit 0 real space, bit 1 reciprocal.
 // Result: s.mol->sums = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2} of this CTA (block sums in a
@@ -937,11 +952,11 @@ __device__ __forceinline__ void recip_phase(const DevConst& dc, const ChainState
 // TRI: compiled for tilted cells (dc.tri); the orthorhombic kernels carry none of that code
 template <int NT, bool TRI>
 __device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState& cs, int c, const SweepCtx& s, const Trial& t, int part, int n_parts, int phases,
-                                            Trial* tw = nullptr) {
-    // tw != nullptr (the one-CTA batched kernel, which owns the Trial): the framework-energy cache is read and its next
-    // values are left in *tw for commit_trial
+                                            bool allow_cache = false) {
+    // allow_cache (the batched kernels, which own the Trial and commit it themselves): the framework-energy cache is read; the
+    // caller then runs fold_fw_cache on the (cluster-wide) sums
     const bool swap = t.kind == MMC_SWAP;
-    const bool cache = tw != nullptr && dc.fw_cache && !swap && (phases & 1);
+    const bool cache = allow_cache && dc.fw_cache && !swap && (phases & 1);
     stage_terms<TRI>(dc, cs, c, s, t);
     stage_molecule(dc, cs, c, s, t, swap ? 1 : 0, cache);
     MMC_TSTAMP(1);
@@ -976,16 +991,12 @@ __device__ __forceinline__ void sweep_trial(const DevConst& dc, const ChainState
             double v[8];
             block_sum_gather<8, NT>(v, s.red);
             if (threadIdx.x == 0) {
-                const bool cached = m.fw_cached != 0;
-                const double fo0 = cached ? m.fw_old[0] : v[4], fo1 = cached ? m.fw_old[1] : v[5];
-                s.mol->sums[0] = v[0] + fo0; s.mol->sums[1] = v[1] + fo1;
-                s.mol->sums[2] = v[2] + v[6]; s.mol->sums[3] = v[3] + v[7];
-                tw->fw_new_ok = m.do_new != 0; tw->fw_new[0] = v[6]; tw->fw_new[1] = v[7];
-                tw->fw_old_fresh = m.fo != 0; tw->fw_old[0] = fo0; tw->fw_old[1] = fo1;
+                for (int i = 0; i < 4; i++) { s.mol->sums[i] = v[i]; s.mol->fws[i] = v[4 + i]; }
+                s.mol->cache_on = 1;
             }
         } else {
             block_sum<4, NT>(pa, s.red);
-            if (threadIdx.x == 0) for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i];
+            if (threadIdx.x == 0) { for (int i = 0; i < 4; i++) s.mol->sums[i] = pa[i]; s.mol->cache_on = 0; }
         }
         MMC_TSTAMP(3);
     }

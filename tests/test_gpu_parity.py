@@ -252,9 +252,9 @@ def test_cluster_per_chain_kernel(which, P, monkeypatch):
     g.close(); g1.close()
 
 
-@pytest.mark.parametrize("which", ["zif8_h2o", "zif8_ch4o_h2o", "tilted"])
-def test_framework_energy_cache(which, monkeypatch):
-    """ChainState.fw_pair: the one-CTA batched kernel keeps, per guest molecule, the framework part of its pair energy and
+@pytest.mark.parametrize("which,P", [("zif8_h2o", 0), ("zif8_ch4o_h2o", 0), ("tilted", 0), ("zif8_h2o", 4), ("zif8_ch4o_h2o", 2)])
+def test_framework_energy_cache(which, P, monkeypatch):
+    """ChainState.fw_pair: the batched kernels (one CTA per chain, P = 0, and a cluster of P CTAs per chain) keep, per guest molecule, the framework part of its pair energy and
     re-sums only the guest-guest part of the old geometry (the framework never moves).  The same Philox streams with the
     cache (default) and without it (MANIAC_FW_CACHE=0, the reference's re-summation, ComputeOldEnergy
     monte_carlo_utils.f90:347-396): identical accept sequences and counters, records within 1e-12 of each other (the split
@@ -268,9 +268,9 @@ def test_framework_energy_cache(which, monkeypatch):
     else:
         s = tilted_framework(n_fw=3000, box=48.0, tilt=(7.0, -5.0, 9.0))
     n, seed, C = 400, 777, 3
-    monkeypatch.setenv("MANIAC_CLUSTER", "0")      # the cache lives in the one-CTA kernel; so few chains would get the cluster kernel
+    monkeypatch.setenv("MANIAC_CLUSTER", str(P))   # both kernels, whatever the library would pick for so few chains
     g = ManiacGPU(s, n_chains=C)
-    assert g.chain_launch_config()[1] == 1
+    assert g.chain_launch_config()[1] == max(P, 1)
     monkeypatch.setenv("MANIAC_FW_CACHE", "0")
     g0 = ManiacGPU(s, n_chains=C)
     monkeypatch.delenv("MANIAC_FW_CACHE")
