@@ -689,13 +689,25 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
     const int ngroups = (r1 - r0 + 3) >> 2, nzb = s.nzb;
     const int nunits = SPLIT ? ngroups * nzb : ngroups;
     const int kbn = (nterm + 3) >> 2;
+    const float inv_ny = 1.0f / (float)s.ny;
+    // the k range of this lane's row is fetched one unit ahead (r2z: 3.9 % of the kernel's stall samples sat on these two
+    // dependent loads at the head of every unit)
+    int k0n = 0, nn = 0;
+    if (!SPLIT && unit0 < nunits && r0 + 4 * unit0 + t < r1) { k0n = dc.row_kstart[r0 + 4 * unit0 + t]; nn = dc.row_kstart[r0 + 4 * unit0 + t + 1] - k0n; }
     for (int u = unit0; u < nunits; u += ustride) {
         const int q = SPLIT ? u / nzb : u;
         const int rg = r0 + 4 * q;
         // the row this lane updates: k range [k0, k1) = kz -m .. m
         const int r = rg + t;
         int k0 = 0, n = 0;
-        if (r < r1) { k0 = dc.row_kstart[r]; n = dc.row_kstart[r + 1] - k0; }
+        if (SPLIT) {
+            if (r < r1) { k0 = dc.row_kstart[r]; n = dc.row_kstart[r + 1] - k0; }
+        } else {
+            k0 = k0n; n = nn;
+            const int rr = r + 4 * ustride;
+            k0n = 0; nn = 0;
+            if (u + ustride < nunits && rr < r1) { k0n = dc.row_kstart[rr]; nn = dc.row_kstart[rr + 1] - k0n; }
+        }
         const int m = n >> 1, has0 = n & 1;
         const int mmax = __reduce_max_sync(0xffffffffu, n > 0 ? m : -1);
         if (mmax < 0) continue;                                   // four empty rows (outside the k sphere)
@@ -724,7 +736,9 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
         // B fragments: row rg + g / 2, component g % 2
         const int rb = rg + (g >> 1);
         const bool rb_ok = rb < r1;
-        const int ix = rb_ok ? rb / s.ny : 0, iy = rb_ok ? rb - ix * s.ny : 0;
+        // rb / ny without the integer-division sequence: (rb + 1/2) / ny is at least 1 / (2 ny) away from an integer, the
+        // single-precision error of a quotient below nx (a few hundred at most) is orders of magnitude smaller
+        const int ix = rb_ok ? __float2int_rd(((float)rb + 0.5f) * inv_ny) : 0, iy = rb_ok ? rb - ix * s.ny : 0;
         double bf[KB > 0 ? KB : 1];
         if (KB > 0) {
 #pragma unroll
