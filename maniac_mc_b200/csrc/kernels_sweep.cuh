@@ -713,15 +713,6 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
         if (mmax < 0) continue;                                   // four empty rows (outside the k sphere)
         const int jlo = SPLIT ? u - q * nzb : 0, jhi = SPLIT ? jlo + 1 : (mmax >> 3) + 1;
         if (SPLIT && 8 * jlo > mmax) continue;
-        if (!SPLIT && lane == 0) {
-            // pull the group this warp takes next from HBM into L2 while this one is computed: one bulk prefetch (no LSU
-            // data wavefronts, unlike a prefetch per line)
-            const int rn = rg + 4 * ustride;
-            if (rn < r1) {
-                const int ka = dc.row_kstart[rn], kb = dc.row_kstart[min(r1, rn + 4)];
-                if (kb > ka) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + ka), "r"((kb - ka) * 16) : "memory");
-            }
-        }
         const int base_p = k0 + m - (1 - has0);                   // k(+kz) = base_p + kz, k(-kz) = k0 + m - kz
         // Software pipeline over the kz blocks: the A(k) / f W loads of block j + 1 are issued BEFORE block j is computed, so
         // two blocks' worth of memory requests are in flight per warp.  (r2c phase timing: 1 090 cycles per block with one
@@ -743,6 +734,14 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
         if (KB > 0) {
 #pragma unroll
             for (int kb = 0; kb < KB; kb++) bf[kb] = recip_bfrag(s, nterm, 4 * kb + t, rb_ok, ix, iy, g & 1);
+        }
+        if (!SPLIT) {
+            // pull the group this warp takes next from HBM into L2 while this one is computed: one bulk prefetch (no LSU
+            // data wavefronts, unlike a prefetch per line).  Its k range [ka, kb) comes from the row ranges lanes 0..3 just
+            // fetched for the next unit (rows are contiguous in k, rows beyond r1 hold (0, 0))
+            int kb = k0n + nn;
+            kb = max(kb, __shfl_xor_sync(0xffffffffu, kb, 1)); kb = max(kb, __shfl_xor_sync(0xffffffffu, kb, 2));
+            if (lane == 0 && kb > k0n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + k0n), "r"((kb - k0n) * 16) : "memory");
         }
         for (int j = jlo; j < jhi; j++) {
             const int kzn = kz + 8;                                  // >= 8: never the kz = 0 column
