@@ -692,8 +692,8 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
     const float inv_ny = 1.0f / (float)s.ny;
     // the k range of this lane's row is fetched one unit ahead (r2z: 3.9 % of the kernel's stall samples sat on these two
     // dependent loads at the head of every unit)
-    int k0n = 0, nn = 0;
-    if (!SPLIT && unit0 < nunits && r0 + 4 * unit0 + t < r1) { k0n = dc.row_kstart[r0 + 4 * unit0 + t]; nn = dc.row_kstart[r0 + 4 * unit0 + t + 1] - k0n; }
+    int k0n = 0, k1n = 0;   // raw loads: nothing consumes them before the next unit starts (a difference formed here would wait for them)
+    if (!SPLIT && unit0 < nunits && r0 + 4 * unit0 + t < r1) { k0n = dc.row_kstart[r0 + 4 * unit0 + t]; k1n = dc.row_kstart[r0 + 4 * unit0 + t + 1]; }
     for (int u = unit0; u < nunits; u += ustride) {
         const int q = SPLIT ? u / nzb : u;
         const int rg = r0 + 4 * q;
@@ -703,10 +703,10 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
         if (SPLIT) {
             if (r < r1) { k0 = dc.row_kstart[r]; n = dc.row_kstart[r + 1] - k0; }
         } else {
-            k0 = k0n; n = nn;
+            k0 = k0n; n = k1n - k0n;
             const int rr = r + 4 * ustride;
-            k0n = 0; nn = 0;
-            if (u + ustride < nunits && rr < r1) { k0n = dc.row_kstart[rr]; nn = dc.row_kstart[rr + 1] - k0n; }
+            k0n = 0; k1n = 0;
+            if (u + ustride < nunits && rr < r1) { k0n = dc.row_kstart[rr]; k1n = dc.row_kstart[rr + 1]; }
         }
         const int m = n >> 1, has0 = n & 1;
         const int mmax = __reduce_max_sync(0xffffffffu, n > 0 ? m : -1);
@@ -739,7 +739,7 @@ __device__ __forceinline__ void recip_groups(const DevConst& dc, const SweepCtx&
             // pull the group this warp takes next from HBM into L2 while this one is computed: one bulk prefetch (no LSU
             // data wavefronts, unlike a prefetch per line).  Its k range [ka, kb) comes from the row ranges lanes 0..3 just
             // fetched for the next unit (rows are contiguous in k, rows beyond r1 hold (0, 0))
-            int kb = k0n + nn;
+            int kb = k1n;
             kb = max(kb, __shfl_xor_sync(0xffffffffu, kb, 1)); kb = max(kb, __shfl_xor_sync(0xffffffffu, kb, 2));
             if (lane == 0 && kb > k0n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A + k0n), "r"((kb - k0n) * 16) : "memory");
         }
