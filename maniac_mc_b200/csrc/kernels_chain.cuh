@@ -48,7 +48,7 @@ __global__ void __launch_bounds__(NT, MINB) k_chain_run(DevConst dc, ChainState 
             const int kind = t.kind;
             if (kind > 0) {
                 fold_fw_cache(t, *s.mol, s.mol->sums, s.mol->fws);
-                finalize_trial(dc, cs, c, t, s.mol->sums);
+                finalize_trial(dc, cs, c, t, s.mol->sums, s.mol->intra_ok ? s.mol->intra : nullptr);
                 RngSrc rs = ctl->rng;
                 rs.step += (unsigned long long)st;
                 Rng rng{&rs, cs, c, t.draw, rs.tape ? nullptr : s.mol->u};  // the accept draw follows the proposal's draws
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(NT, 2048 / NT / 2) k_chain_run_cl(DevConst dc,
                     for (int i = 0; i < 4; i++) fw[i] += pf[i];
                 }
                 fold_fw_cache(t, *s.mol, v, fw);          // the framework-energy cache (every rank took the same decision)
-                finalize_trial(dc, cs, c, t, v);
+                finalize_trial(dc, cs, c, t, v, s.mol->intra_ok ? s.mol->intra : nullptr);
                 RngSrc rs = ctl->rng;
                 rs.tape = nullptr;
                 rs.step += (unsigned long long)st;

@@ -265,25 +265,32 @@ __device__ inline void propose_move(const DevConst& dc, const ChainState& cs, co
 
 // ----------------------------------------------------------------------------------------------
 // ComputeIntraResidueRealCoulombEnergySingleMol ewald_energy.f90:371-411 on explicit positions
-__device__ inline double intra_energy(const DevConst& dc, int nat, const double* q, const double (*p)[3]) {
+// one pair of ComputeIntraResidueRealCoulombEnergySingleMol (ewald_energy.f90:371-411), without the 1/(4 pi eps0) factor
+__device__ inline double intra_pair_term(const DevConst& dc, double qa, double qb, const double* pa, const double* pb) {
+    double dx = pb[0] - pa[0], dy = pb[1] - pa[1], dz = pb[2] - pa[2];
+    if (dc.tri) min_image_tri_brick(dc, dx, dy, dz);   // sites of one molecule are closer than half the shortest cell edge:
+    else {                                             // the brick image is the nearest one, no 27-image search (and no call here)
+        dx = min_image(dx, dc.L[0], dc.invL[0]); dy = min_image(dy, dc.L[1], dc.invL[1]); dz = min_image(dz, dc.L[2], dc.invL[2]);
+    }
+    const double r = sqrt(dx * dx + dy * dy + dz * dz);
+    return r > MMC_ERR ? qa * qb * (erfc(dc.alpha * r) - 1.0) / r : 0.0;
+}
+// pre != nullptr: the pair terms were formed in parallel while the molecule was staged (stage_molecule), in the order of the
+// loops below; the sum is the same, bit for bit
+__device__ inline double intra_energy(const DevConst& dc, int nat, const double* q, const double (*p)[3], const double* pre = nullptr) {
     double e = 0.0;
+    int k = 0;
     for (int a1 = 0; a1 < nat - 1; a1++)
-        for (int a2 = a1 + 1; a2 < nat; a2++) {
-            double dx = p[a2][0] - p[a1][0], dy = p[a2][1] - p[a1][1], dz = p[a2][2] - p[a1][2];
-            if (dc.tri) min_image_tri_brick(dc, dx, dy, dz);   // sites of one molecule are closer than half the shortest cell edge:
-            else {                                             // the brick image is the nearest one, no 27-image search (and no call here)
-                dx = min_image(dx, dc.L[0], dc.invL[0]); dy = min_image(dy, dc.L[1], dc.invL[1]); dz = min_image(dz, dc.L[2], dc.invL[2]);
-            }
-            const double r = sqrt(dx * dx + dy * dy + dz * dz);
-            if (r > MMC_ERR) e += q[a1] * q[a2] * (erfc(dc.alpha * r) - 1.0) / r;
-        }
+        for (int a2 = a1 + 1; a2 < nat; a2++, k++)
+            e += pre ? pre[k] : intra_pair_term(dc, q[a1], q[a2], p[a1], p[a2]);
     return e * dc.coul_const;
 }
 
 // Assembles type(energy_state) old/new from the six sweep sums exactly as ComputeOldEnergy /
 // ComputeNewEnergy do for each move type (monte_carlo_utils.f90:275-396) and the acceptance probability.
 // v = {lj_old, coul_old, lj_new, coul_new, sum fW|A|^2, sum fW|A'|^2}.  Single thread.
-__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, const double* v) {
+__device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, int c, Trial& t, const double* v, const double* intra_pre = nullptr) {
+    // intra_pre: pair terms of the created / deleted molecule's intra-residue sum, formed by stage_molecule (batched kernels)
     if (t.kind <= 0) return;
     const double lj_o = v[0], c_o = v[1] * dc.coul_const, lj_n = v[2], c_n = v[3] * dc.coul_const;
     const double rec_o = v[4] * dc.recip_const, rec_n = v[5] * dc.recip_const;
@@ -292,7 +299,7 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
     if (t.kind == MMC_CREATION) {
         o[0] = 0; o[1] = 0; o[3] = 0; o[4] = 0; o[2] = e_recip_tracked;
         o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
-        n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res]; n[4] = intra_energy(dc, t.nat, t.q, t.p_new);
+        n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res]; n[4] = intra_energy(dc, t.nat, t.q, t.p_new, intra_pre);
         n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
     } else if (t.kind == MMC_SWAP) {
         o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
@@ -300,7 +307,7 @@ __device__ inline void finalize_trial(const DevConst& dc, const ChainState& cs, 
         n[2] = rec_n; n[0] = lj_n; n[1] = c_n; n[3] = dc.self_e[t.res2]; n[4] = intra_energy(dc, t.nat2, t.q2, t.p_new);
         n[5] = n[0] + n[1] + n[2] + n[3] + n[4];
     } else if (t.kind == MMC_DELETION) {
-        o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
+        o[3] = dc.self_e[t.res]; o[4] = intra_energy(dc, t.nat, t.q, t.p_old, intra_pre); o[0] = lj_o; o[1] = c_o; o[2] = e_recip_tracked;
         o[5] = o[0] + o[1] + o[2] + o[3] + o[4];
         n[0] = 0; n[1] = 0; n[3] = 0; n[4] = 0; n[2] = rec_n;
         n[5] = n[0] + n[1] + n[2] + n[3] + n[4];

@@ -35,6 +35,11 @@ struct MolS {
     double cc[4];       // common sphere of the geometries swept: {x, y, z, (radius + reach)^2}
     double ccf[4];      // the same for the FRAMEWORK sweep (new geometry only when the old one's framework energy is cached)
     double fw_old[2];   // framework part {LJ, Coulomb (reduced)} of the old geometry: from the cache, or summed in this trial
+    // pair terms of the intra-residue sum of a created / deleted molecule (intra_ok), formed by threads 96.. while the molecule is
+    // staged instead of by thread 0 in finalize_trial (6 erfc + sqrt + division sequences for TIP4P: r2zk, ~20 k cycles of the
+    // single-thread section of every insertion / deletion)
+    double intra[MMC_MAX_MOL_ATOMS * (MMC_MAX_MOL_ATOMS - 1) / 2];
+    int intra_ok;
     double fws[4];      // framework-energy cache on (cache_on): this CTA's FRAMEWORK partial sums {lj_old, coul_old, lj_new, coul_new};
                         // sums[0..3] then hold the guests' part only (fold_fw_cache puts them together)
     int cache_on;
@@ -160,7 +165,15 @@ __device__ __forceinline__ void stage_molecule(const DevConst& dc, const ChainSt
         m.fw_cached = cached; m.fo = uo && !cached;
         m.fw_old[0] = cached ? t.fw_old[0] : 0.0; m.fw_old[1] = cached ? t.fw_old[1] : 0.0;
     }
+    if (tid == 0) m.intra_ok = pass == 0 && (t.kind == MMC_CREATION || t.kind == MMC_DELETION);
     if (t.kind <= 0) { __syncthreads(); return; }
+    if (pass == 0 && (t.kind == MMC_CREATION || t.kind == MMC_DELETION) && tid >= 96 && tid - 96 < nat * (nat - 1) / 2) {
+        int k = tid - 96, a1 = 0;
+        while (k >= nat - 1 - a1) { k -= nat - 1 - a1; a1++; }     // pair index -> (a1, a2) in intra_energy's loop order
+        const int a2 = a1 + 1 + k;
+        const double (*p)[3] = t.kind == MMC_CREATION ? t.p_new : t.p_old;
+        m.intra[tid - 96] = intra_pair_term(dc, q[a1], q[a2], p[a1], p[a2]);
+    }
     if (tid < nat) {
         for (int d = 0; d < 3; d++) { m.po[tid][d] = t.p_old[tid][d]; m.pn[tid][d] = t.p_new[tid][d]; }
         m.q[tid] = q[tid]; m.type[tid] = type[tid];
