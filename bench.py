@@ -37,8 +37,8 @@ B_K_BYTES = 40.0     # HBM bytes per k-eval: A(k) read 16 + A'(k) write 16 + f*W
 FUG_LO_ATM, FUG_HI_ATM, N_POINTS = 1.0e-2, 1.0e4, 64
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_chain_run launch from the committed `ncu --set full` capture,
 # divided by that launch's k-evals (592 chains x 32 steps x 37 782 k); bench.py scales it to its own launch.
-NCU_DRAM_BYTES_PER_K_EVAL = 23409552000.0 / (592 * 32 * 37782)
-NCU_TRAFFIC_SOURCE = "profiles/r2z_ncu_summary.txt (23.41 GB per launch of 592 chains x 32 steps), scaled by k-evals"
+NCU_DRAM_BYTES_PER_K_EVAL = 23464590000.0 / (592 * 32 * 37782)
+NCU_TRAFFIC_SOURCE = "profiles/r2zp_ncu_summary.txt (23.46 GB per launch of 592 chains x 32 steps), scaled by k-evals"
 
 
 def parse_args():
