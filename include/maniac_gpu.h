@@ -256,7 +256,13 @@ int mmc_get_sk(mmc_t* handle, int chain, double* sk);
  * tape[c*tape_stride ...] (strict replay of a recorded stream, draw order of SURVEY 3.8);
  * otherwise Philox4x32-10 keyed by seed with counter (step, chain, draw).
  * records (optional, may be NULL): n_chains*n_steps entries, chain-major.
- * counters (optional): n_chains entries, accumulated since mmc_init. */
+ * counters (optional): n_chains entries, accumulated since mmc_init.
+ * One deliberate difference from ComputeOldEnergy (monte_carlo_utils.f90:347-396), which re-sums the selected molecule's
+ * pair energy with every other atom for the old geometry: the framework never moves, so these kernels keep, per guest
+ * molecule, the framework part of that sum from the move that put the molecule where it is and re-sum only the guest-guest
+ * part; entries they do not know (start-up, strict-mode accepts, mmc_set_chain_state, changed coordinates in
+ * mmc_upload_chains) are re-summed.  Same energies, probabilities and accept sequences to 1e-10; MANIAC_FW_CACHE=0 in the
+ * environment at mmc_init restores the re-summation. */
 int mmc_run_batch(mmc_t* handle, int64_t n_steps, uint64_t seed,
                   const double* tape, int64_t tape_stride,
                   mmc_move_record* records, mmc_counters* counters);
